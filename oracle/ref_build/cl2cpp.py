@@ -1,0 +1,55 @@
+#!/usr/bin/env python3
+"""cl2cpp.py -- TEST INFRASTRUCTURE (oracle/_ref build step). Not part of the product path.
+
+Reads the reference's OpenCL-C sources where they lie under /root/reference and writes
+C++-compilable copies to oracle/_ref/gen/ (git-ignored; never committed).  The rewrite is
+purely mechanical -- no arithmetic, control flow or constant is touched:
+
+  1. OpenCL vector literals   `(float3)(a,b,c)` -> `make_float3(a,b,c)`   (not valid C++)
+     for float2/3/4, int2/3, uint2.
+  2. `#ifdef __cplusplus` in kernel_data.h -> `#ifdef MCRT_REF_HOST_BRANCH` so that the
+     OpenCL branch of that shared header (the device-side struct layouts) is the one compiled.
+  3. `#include <../RadeonRays/src/kernels/CL/common.cl>` -> `#include "common.cl"`.
+
+Everything else (swizzles, address-space qualifiers, builtins) is supplied by clshim.hpp.
+"""
+import os
+import re
+import sys
+
+REF = os.environ.get("MCRT_REFERENCE", "/root/reference")
+APP_KERNELS = ["PathTracing.cl", "BDPT.cl", "bxdfs.cl", "materials.cl", "lights.cl", "geometry.cl",
+               "textures.cl", "samplers.cl", "rng.cl", "cameras.cl", "math.cl", "matrix.cl",
+               "image_samplers.cl", "kernel_data.h", "reconstruction.cl", "filters.cl"]
+RR_KERNELS = ["common.cl", "intersect_bvh2_lds.cl"]
+
+VEC_LITERAL = re.compile(r"\((float[234]|int[23]|uint2)\)\s*\(")
+
+
+def rewrite(text: str) -> str:
+    text = VEC_LITERAL.sub(lambda m: "make_%s(" % m.group(1), text)
+    text = text.replace("#ifdef __cplusplus", "#ifdef MCRT_REF_HOST_BRANCH")
+    text = text.replace("#include <../RadeonRays/src/kernels/CL/common.cl>", '#include "common.cl"')
+    return text
+
+
+def main(out_dir: str) -> int:
+    app_dir = os.path.join(REF, "assets", "kernels")
+    rr_dir = os.path.join(REF, "third_party", "RadeonRays", "RadeonRays", "src", "kernels", "CL")
+    os.makedirs(os.path.join(out_dir, "app"), exist_ok=True)
+    os.makedirs(os.path.join(out_dir, "rr"), exist_ok=True)
+    for name in APP_KERNELS:
+        with open(os.path.join(app_dir, name), "r", encoding="latin-1") as f:
+            src = f.read()
+        with open(os.path.join(out_dir, "app", name), "w", encoding="latin-1") as f:
+            f.write(rewrite(src))
+    for name in RR_KERNELS:
+        with open(os.path.join(rr_dir, name), "r", encoding="latin-1") as f:
+            src = f.read()
+        with open(os.path.join(out_dir, "rr", name), "w", encoding="latin-1") as f:
+            f.write(rewrite(src))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main(sys.argv[1]))
