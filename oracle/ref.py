@@ -1,0 +1,177 @@
+"""oracle/ref.py -- TEST INFRASTRUCTURE.  Python driver of oracle/_ref/libmcrt_ref.so.
+
+libmcrt_ref.so is the reference's OWN source (assets/kernels/*.cl, Radeon Rays' Bvh2 builder and
+intersect_bvh2_lds.cl) compiled for the host by oracle/ref_build/Makefile.  This module restates
+only the reference's host loops around those kernels:
+
+  * RTPrimaryRaysPass::update            (renderPasses/RTPrimaryRaysPass.cpp:32-66)
+  * RTPathTracingPass::update            (renderPasses/RTPathTracingPass.cpp:40-114)
+  * IntersectorLDS::Process / Intersect  (RadeonRays/src/intersector/intersector_lds.cpp:163-326)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  It never runs on the product path.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+import mcrt_b200  # noqa: F401  (registers the package)
+from mcrt_b200 import layouts as L
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+class RefSceneDesc(ctypes.Structure):
+    _fields_ = [("shapes", ctypes.c_void_p), ("indices", ctypes.c_void_p), ("positions", ctypes.c_void_p),
+                ("uvs", ctypes.c_void_p), ("normals", ctypes.c_void_p), ("textures", ctypes.c_void_p),
+                ("texdata", ctypes.c_void_p), ("sobol", ctypes.c_void_p), ("lights", ctypes.c_void_p),
+                ("materials", ctypes.c_void_p), ("camera", ctypes.c_void_p),
+                ("num_shapes", ctypes.c_int32), ("num_textures", ctypes.c_int32), ("num_lights", ctypes.c_int32),
+                ("num_materials", ctypes.c_int32), ("num_indices", ctypes.c_int64), ("num_vertices", ctypes.c_int64),
+                ("texdata_bytes", ctypes.c_int64)]
+
+
+def lib_path(fast: bool = False) -> str:
+    return os.path.join(_HERE, "_ref", "libmcrt_ref_fast.so" if fast else "libmcrt_ref.so")
+
+
+def available(fast: bool = False) -> bool:
+    return os.path.exists(lib_path(fast))
+
+
+def _ptr(a):
+    return None if a is None or a.size == 0 else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class RefOracle:
+    """The compiled reference, one NDRange per call."""
+
+    def __init__(self, fast: bool = False):
+        self.lib = ctypes.CDLL(lib_path(fast))
+        lib = self.lib
+        lib.ref_rr_world_create.restype = ctypes.c_void_p
+        lib.ref_rr_world_destroy.argtypes = [ctypes.c_void_p]
+        lib.ref_rr_world_add_mesh.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_void_p, ctypes.c_void_p]
+        lib.ref_rr_world_add_instance.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                                  ctypes.c_void_p]
+        lib.ref_rr_world_build.argtypes = [ctypes.c_void_p, ctypes.c_float, ctypes.c_int, ctypes.c_int]
+        lib.ref_rr_world_build.restype = ctypes.c_longlong
+        lib.ref_rr_world_nodes.argtypes = [ctypes.c_void_p]
+        lib.ref_rr_world_nodes.restype = ctypes.c_void_p
+        lib.ref_rr_intersect.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p]
+        lib.ref_rr_occluded.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p]
+        lib.ref_pt_generate_rays.argtypes = [ctypes.c_void_p] * 3
+        lib.ref_pt_shade.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                     ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                     ctypes.c_void_p]
+        lib.ref_pt_shadow_pass.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                           ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+
+    # ------------------------------------------------------------------ Radeon Rays side
+    def build_bvh(self, meshes, use_sah=True, traversal_cost=10.0, num_bins=64):
+        """meshes: iterable of (positions(V,3) f32, indices(T,3) i32, shape_id, transform or None).
+        Returns the Bvh2 node array as raw bytes (n,64) -- engine defaults: FatBVH + SAH, cost 10,
+        64 bins (GUI/PathTracingSettings.h:241-249)."""
+        w = self.lib.ref_rr_world_create()
+        keep = []
+        try:
+            for pos, idx, sid, xf in meshes:
+                pos = np.ascontiguousarray(pos, np.float32)
+                idx = np.ascontiguousarray(idx, np.int32)
+                m = None if xf is None else np.ascontiguousarray(xf, np.float32)
+                minv = None if xf is None else np.ascontiguousarray(np.linalg.inv(m.astype(np.float64)), np.float32)
+                keep += [pos, idx, m, minv]
+                self.lib.ref_rr_world_add_mesh(w, _ptr(pos), pos.shape[0], 12, _ptr(idx), 12, idx.shape[0], int(sid),
+                                               _ptr(m), _ptr(minv))
+            n = self.lib.ref_rr_world_build(w, traversal_cost, num_bins, 1 if use_sah else 0)
+            src = self.lib.ref_rr_world_nodes(w)
+            nodes = np.frombuffer(ctypes.string_at(src, n * 64), dtype=np.uint8).reshape(n, 64).copy()
+        finally:
+            self.lib.ref_rr_world_destroy(w)
+        return nodes
+
+    def build_scene_bvh(self, scene, **kw):
+        return self.build_bvh([(m.positions, m.indices, i, m.transform) for i, m in enumerate(scene.meshes)], **kw)
+
+    def intersect(self, nodes, rays, hits=None):
+        """intersect_main; `hits` (prefilled) is updated in place like the device buffer would be."""
+        if hits is None:
+            hits = np.zeros(rays.shape[0], dtype=L.INTERSECTION)
+            hits["shapeid"] = -1
+            hits["primid"] = -1
+        self.lib.ref_rr_intersect(_ptr(nodes), _ptr(rays), rays.shape[0], _ptr(hits))
+        return hits
+
+    def occluded(self, nodes, rays, out=None):
+        if out is None:
+            out = np.zeros(rays.shape[0], dtype=np.int32)
+        self.lib.ref_rr_occluded(_ptr(nodes), _ptr(rays), rays.shape[0], _ptr(out))
+        return out
+
+    # ------------------------------------------------------------------ path tracer side
+    def scene_desc(self, scene, camera):
+        d = RefSceneDesc()
+        d.shapes, d.indices, d.positions = _ptr(scene.shapes), _ptr(scene.indices), _ptr(scene.positions)
+        d.uvs, d.normals = _ptr(scene.uvs), _ptr(scene.normals)
+        d.textures, d.texdata, d.sobol = _ptr(scene.textures), _ptr(scene.texdata), None
+        d.lights, d.materials, d.camera = _ptr(scene.lights), _ptr(scene.materials), _ptr(camera)
+        d.num_shapes, d.num_textures = len(scene.shapes), len(scene.textures)
+        d.num_lights, d.num_materials = len(scene.lights), len(scene.materials)
+        d.num_indices, d.num_vertices = scene.indices.size, scene.positions.shape[0]
+        d.texdata_bytes = scene.texdata.size
+        return d
+
+    def generate_rays(self, camera):
+        w, h = int(camera["width"][0]), int(camera["height"][0])
+        rays = np.zeros(w * h, dtype=L.RAY)
+        diffs = np.zeros(w * h, dtype=L.RAYDIFF)
+        self.lib.ref_pt_generate_rays(_ptr(rays), _ptr(diffs), _ptr(camera))
+        return rays
+
+
+class RefPathTracer:
+    """RTPrimaryRaysPass + RTPathTracingPass state for one image size: the buffers live across
+    frames exactly like the reference's device buffers (zero-filled at creation)."""
+
+    def __init__(self, oracle: RefOracle, scene, nodes, width, height):
+        self.o, self.scene, self.nodes, self.w, self.h = oracle, scene, nodes, width, height
+        n = width * height
+        self.rays = np.zeros(n, dtype=L.RAY)
+        self.diffs = np.zeros(n, dtype=L.RAYDIFF)
+        self.isect = np.zeros(n, dtype=L.INTERSECTION)
+        self.shadow_rays = np.zeros(n, dtype=L.RAY)
+        self.occlusion = np.zeros(n, dtype=np.int32)
+        self.temp_radiance = np.zeros((n, 4), np.float32)
+        self.radiance = np.zeros((n, 4), np.float32)
+        self.throughput = np.zeros(n, dtype=L.THROUGHPUT)
+        self.rays_traced = 0
+        self.shadow_rays_traced = 0
+
+    def render_sample(self, camera, frame, max_depth, trace=None):
+        """One frame = one sample per pixel.  `trace`, if a dict, receives copies of the primary
+        hits and of every bounce's temp radiance (for per-stage parity checks)."""
+        lib, o = self.o.lib, self.o
+        desc = o.scene_desc(self.scene, camera)
+        lib.ref_pt_generate_rays(_ptr(self.rays), _ptr(self.diffs), _ptr(camera))
+        o.intersect(self.nodes, self.rays, self.isect)
+        self.rays_traced += int((self.rays["extra"][:, 1] != 0).sum())
+        if trace is not None:
+            trace["primary_rays"] = self.rays.copy()
+            trace["primary_hits"] = self.isect.copy()
+            trace["bounce_radiance"] = []
+        for b in range(max_depth):
+            lib.ref_pt_shade(ctypes.byref(desc), self.w, self.h, _ptr(self.shadow_rays), _ptr(self.rays),
+                             _ptr(self.isect), frame, max_depth, b, _ptr(self.temp_radiance), _ptr(self.throughput))
+            o.occluded(self.nodes, self.shadow_rays, self.occlusion)
+            self.shadow_rays_traced += int((self.shadow_rays["extra"][:, 1] != 0).sum())
+            lib.ref_pt_shadow_pass(_ptr(self.shadow_rays), _ptr(self.occlusion), self.w, self.h, b,
+                                   _ptr(self.throughput), _ptr(self.temp_radiance), _ptr(self.radiance))
+            if trace is not None:
+                trace["bounce_radiance"].append(self.radiance.copy())
+            if b + 1 < max_depth:
+                o.intersect(self.nodes, self.rays, self.isect)
+                self.rays_traced += int((self.rays["extra"][:, 1] != 0).sum())
+        return self.radiance
