@@ -1,0 +1,60 @@
+// bvh8.h -- compressed 8-wide BVH: host-side build interface and the HBM layout shared with the
+// traversal kernels.
+//
+// Replaces Radeon Rays' Bvh2 (RadeonRays/src/accelerator/bvh2.{h,cpp}: binary tree, 64-byte
+// nodes, one triangle per leaf stored inside the node) with an 8-wide tree of 80-byte nodes
+// whose child boxes are quantised to 8 bits per plane relative to the node's origin
+// (Ylitie, Karras, Laine: "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide
+// BVHs", HPG 2017), plus a separate array of 48-byte triangle records.  The tree shape is not
+// a parity requirement; the hit results are.
+//
+// HBM layout
+//   nodes:     uint4[5 * num_nodes]           80 B per node
+//     [0] p.x p.y p.z (fp32 origin) | e.x e.y e.z imask (4 x u8: per-axis exponent, internal mask)
+//     [1] child_base_idx | tri_base_idx | meta[0..3] | meta[4..7]
+//     [2] qlo_x[0..7] | qlo_y[0..7]     (u8 each)
+//     [3] qlo_z[0..7] | qhi_x[0..7]
+//     [4] qhi_y[0..7] | qhi_z[0..7]
+//     meta[i]: empty 0; internal child 001_11sss (sss = slot); leaf ccc_ooooo with ccc the
+//     unary triangle count (001,011,111) and ooooo < 24 the first triangle relative to tri_base.
+//   triangles: float4[3 * num_tris]           48 B per triangle
+//     [0] v0.xyz | shape id (int bits)   [1] v1.xyz | prim id (int bits)   [2] v2.xyz | 0
+//     World-space vertices computed exactly as Bvh2::SetPrimitive does (bvh2.h:346-369,
+//     math/mathutils.h:111-118): ((m00*x + m01*y) + m02*z) + m03, fp32, no contraction.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace mcrt {
+
+struct BuildInputMesh {
+    const float* vertices;   // object space, xyz at `vstride` bytes
+    int vnum;
+    int vstride;             // bytes
+    const int* indices;      // 3 per face at `istride` bytes
+    int istride;             // bytes
+    int numfaces;
+    int shape_id;
+    float m[16];             // row-major object -> world
+};
+
+struct Bvh8 {
+    std::vector<uint32_t> nodes;       // 20 words per node
+    std::vector<float> triangles;      // 12 floats per triangle
+    int64_t num_nodes = 0;
+    int64_t num_tris = 0;
+    float scene_min[3] = {0, 0, 0};
+    float scene_max[3] = {0, 0, 0};
+};
+
+struct BuildOptions {
+    bool use_sah = true;          // bvh.builder = sah | median
+    int num_bins = 16;            // bins per axis for the binned SAH sweep
+    float traversal_cost = 1.2f;  // relative to one triangle test, for the BVH2 leaf decision
+    int num_threads = 0;          // 0 = hardware concurrency
+};
+
+// Builds the compressed wide BVH over all faces of all meshes.  Throws std::runtime_error.
+void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& opt, Bvh8& out);
+
+}  // namespace mcrt

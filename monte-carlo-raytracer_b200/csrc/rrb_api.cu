@@ -1,0 +1,693 @@
+// rrb_api.cu -- implementation of include/rrb.h: the object model behind the C ABI.
+//
+// Mirrors IntersectionApiImpl / World / Mesh / Instance / Options
+// (RadeonRays/src/api/radeon_rays_impl.cpp:43-191, src/world/world.cpp:28-56,
+// src/primitive/mesh.cpp:31-113, src/util/options.cpp) with CUDA streams / events / cudaMalloc
+// in the role of Calc (RadeonRays/Calc).  No CPU fallback: every query needs the CUDA device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/rrb.h"
+#include "bvh8.h"
+#include "rrb_kernels.h"
+
+namespace {
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+int cuda_fail(cudaError_t e, const char* where) {
+    return fail(RRB_ERROR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+#define RRB_CUDA(call)                                        \
+    do {                                                      \
+        cudaError_t e__ = (call);                             \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+    } while (0)
+
+const float kIdentity[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+}  // namespace
+
+struct rrb_shape {
+    bool is_instance = false;
+    const rrb_shape* base = nullptr;          // instances only
+    std::vector<float> vertices;              // xyz tightly packed (meshes only)
+    std::vector<int> indices;                 // 3 per face
+    float m[16], minv[16];
+    float linear_velocity[3] = {0, 0, 0};
+    float angular_velocity[4] = {0, 0, 0, 1};
+    int id = 0;
+    bool changed = true;                      // ShapeImpl::statechange_
+    rrb_shape() {
+        std::memcpy(m, kIdentity, sizeof(m));
+        std::memcpy(minv, kIdentity, sizeof(minv));
+    }
+};
+
+struct rrb_buffer {
+    void* dptr = nullptr;
+    size_t size = 0;
+    bool owning = false;
+    void* host_map = nullptr;   // pinned staging while mapped
+    size_t map_offset = 0, map_size = 0;
+    int map_type = 0;
+};
+
+struct rrb_event {
+    cudaEvent_t ev = nullptr;
+    bool recorded = false;
+};
+
+struct rrb_api {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::vector<const rrb_shape*> world;      // World::shapes_, attach order
+    bool world_changed = true;
+    std::map<std::string, std::string> str_options;
+    std::map<std::string, float> f32_options;
+    int next_id = 1;                          // IntersectionApiImpl::m_nextid, ResetIdCounter -> 1
+    // committed acceleration structure
+    void* d_nodes = nullptr;
+    void* d_tris = nullptr;
+    int64_t num_nodes = 0, num_tris = 0;
+    double build_seconds = 0.0;
+    int64_t launches = 0;
+    unsigned int* d_counter = nullptr;
+    std::vector<rrb_event*> event_pool;
+    // staging for the host-buffer entry points
+    void* d_stage_rays = nullptr;
+    void* d_stage_out = nullptr;
+    size_t stage_rays_bytes = 0, stage_out_bytes = 0;
+};
+
+namespace {
+
+int set_device(const rrb_api* api) {
+    cudaError_t e = cudaSetDevice(api->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    return RRB_OK;
+}
+
+rrb_event* acquire_event(rrb_api* api) {
+    rrb_event* ev;
+    if (!api->event_pool.empty()) {
+        ev = api->event_pool.back();
+        api->event_pool.pop_back();
+    } else {
+        ev = new rrb_event();
+        if (cudaEventCreateWithFlags(&ev->ev, cudaEventDisableTiming) != cudaSuccess) {
+            delete ev;
+            return nullptr;
+        }
+    }
+    ev->recorded = false;
+    return ev;
+}
+
+int record_done(rrb_api* api, rrb_event** done) {
+    if (!done) return RRB_OK;
+    rrb_event* ev = acquire_event(api);
+    if (!ev) return fail(RRB_ERROR_CUDA, "cudaEventCreate failed");
+    RRB_CUDA(cudaEventRecord(ev->ev, api->stream));
+    ev->recorded = true;
+    *done = ev;
+    return RRB_OK;
+}
+
+int wait_on(rrb_api* api, const rrb_event* wait) {
+    if (wait && wait->recorded) RRB_CUDA(cudaStreamWaitEvent(api->stream, wait->ev, 0));
+    return RRB_OK;
+}
+
+void free_bvh(rrb_api* api) {
+    if (api->d_nodes) cudaFree(api->d_nodes);
+    if (api->d_tris) cudaFree(api->d_tris);
+    api->d_nodes = api->d_tris = nullptr;
+    api->num_nodes = api->num_tris = 0;
+}
+
+int query_common(rrb_api* api, bool any_hit, const rrb_buffer* rays, const rrb_buffer* numrays_buf, int numrays,
+                 rrb_buffer* out, rrb_buffer* counts, const rrb_event* wait, rrb_event** done) {
+    if (!api || !rays || !out) return fail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    if (numrays < 0) return fail(RRB_ERROR_INVALID_ARGUMENT, "negative ray count");
+    if (!api->d_nodes) return fail(RRB_ERROR_NOT_COMMITTED, "Commit() has not been called on a non-empty world");
+    if ((size_t)numrays * 48 > rays->size) return fail(RRB_ERROR_INVALID_ARGUMENT, "ray buffer too small");
+    if ((size_t)numrays * (any_hit ? 4 : 32) > out->size) return fail(RRB_ERROR_INVALID_ARGUMENT, "result buffer too small");
+    if (counts && (size_t)numrays * 8 > counts->size) return fail(RRB_ERROR_INVALID_ARGUMENT, "count buffer too small");
+    int rc = set_device(api);
+    if (rc) return rc;
+    rc = wait_on(api, wait);
+    if (rc) return rc;
+    cudaError_t e = mcrt::launch_query(any_hit, counts != nullptr, api->d_nodes, api->d_tris, rays->dptr,
+                                       numrays_buf ? (const int*)numrays_buf->dptr : nullptr, numrays, out->dptr,
+                                       api->d_counter, counts ? (int*)counts->dptr : nullptr, api->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "traversal kernel launch");
+    if (numrays > 0) api->launches++;
+    return record_done(api, done);
+}
+
+int ensure_stage(rrb_api* api, size_t rays_bytes, size_t out_bytes) {
+    if (rays_bytes > api->stage_rays_bytes) {
+        if (api->d_stage_rays) cudaFree(api->d_stage_rays);
+        api->d_stage_rays = nullptr;
+        api->stage_rays_bytes = 0;
+        RRB_CUDA(cudaMalloc(&api->d_stage_rays, rays_bytes));
+        api->stage_rays_bytes = rays_bytes;
+    }
+    if (out_bytes > api->stage_out_bytes) {
+        if (api->d_stage_out) cudaFree(api->d_stage_out);
+        api->d_stage_out = nullptr;
+        api->stage_out_bytes = 0;
+        RRB_CUDA(cudaMalloc(&api->d_stage_out, out_bytes));
+        api->stage_out_bytes = out_bytes;
+    }
+    return RRB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rrb_last_error(void) { return g_last_error.c_str(); }
+
+int rrb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+int rrb_device_info(int devidx, char* name, size_t name_len, char* vendor, size_t vendor_len, int* type) {
+    cudaDeviceProp p;
+    RRB_CUDA(cudaGetDeviceProperties(&p, devidx));
+    if (name && name_len) std::snprintf(name, name_len, "%s", p.name);
+    if (vendor && vendor_len) std::snprintf(vendor, vendor_len, "NVIDIA Corporation");
+    if (type) *type = 1; /* DeviceInfo::kGpu */
+    return RRB_OK;
+}
+
+int rrb_create(int cuda_device, void* cuda_stream, rrb_api** out) {
+    if (!out) return fail(RRB_ERROR_INVALID_ARGUMENT, "out is null");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(RRB_ERROR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                        " (this library has no CPU fallback)");
+    if (cuda_device < 0 || cuda_device >= n) return fail(RRB_ERROR_INVALID_ARGUMENT, "device index out of range");
+    std::unique_ptr<rrb_api> api(new rrb_api());
+    api->device = cuda_device;
+    RRB_CUDA(cudaSetDevice(cuda_device));
+    if (cuda_stream) {
+        api->stream = (cudaStream_t)cuda_stream;
+    } else {
+        RRB_CUDA(cudaStreamCreateWithFlags(&api->stream, cudaStreamNonBlocking));
+        api->own_stream = true;
+    }
+    RRB_CUDA(cudaMalloc((void**)&api->d_counter, 256));
+    *out = api.release();
+    return RRB_OK;
+}
+
+int rrb_destroy(rrb_api* api) {
+    if (!api) return RRB_OK;
+    cudaSetDevice(api->device);
+    cudaStreamSynchronize(api->stream);
+    free_bvh(api);
+    if (api->d_counter) cudaFree(api->d_counter);
+    if (api->d_stage_rays) cudaFree(api->d_stage_rays);
+    if (api->d_stage_out) cudaFree(api->d_stage_out);
+    for (rrb_event* ev : api->event_pool) {
+        cudaEventDestroy(ev->ev);
+        delete ev;
+    }
+    if (api->own_stream) cudaStreamDestroy(api->stream);
+    delete api;
+    return RRB_OK;
+}
+
+int rrb_create_mesh(rrb_api* api, const float* vertices, int vnum, int vstride, const int* indices, int istride,
+                    const int* numfacevertices, int numfaces, rrb_shape** out) {
+    if (!api || !out || !vertices || !indices || vnum < 0 || numfaces < 0)
+        return fail(RRB_ERROR_INVALID_ARGUMENT, "CreateMesh: bad argument");
+    if (vstride == 0) vstride = 3 * (int)sizeof(float);
+    std::unique_ptr<rrb_shape> s(new rrb_shape());
+    s->vertices.resize(3 * (size_t)vnum);
+    for (int i = 0; i < vnum; ++i) {
+        const float* v = (const float*)((const char*)vertices + (size_t)i * vstride);
+        s->vertices[3 * (size_t)i + 0] = v[0];
+        s->vertices[3 * (size_t)i + 1] = v[1];
+        s->vertices[3 * (size_t)i + 2] = v[2];
+    }
+    s->indices.resize(3 * (size_t)numfaces);
+    if (!numfacevertices) {
+        if (istride == 0) istride = 3 * (int)sizeof(int);
+        for (int f = 0; f < numfaces; ++f) {
+            const int* id = (const int*)((const char*)indices + (size_t)f * istride);
+            s->indices[3 * (size_t)f + 0] = id[0];
+            s->indices[3 * (size_t)f + 1] = id[1];
+            s->indices[3 * (size_t)f + 2] = id[2];
+        }
+    } else {
+        const char* p = (const char*)indices;
+        for (int f = 0; f < numfaces; ++f) {
+            if (numfacevertices[f] == 4)
+                return fail(RRB_ERROR_UNSUPPORTED, "quads are not supported (Bvh2 asserts pure triangle meshes)");
+            if (numfacevertices[f] != 3) return fail(RRB_ERROR_INVALID_ARGUMENT, "Wrong number of vertices per face");
+            const int* id = (const int*)p;
+            s->indices[3 * (size_t)f + 0] = id[0];
+            s->indices[3 * (size_t)f + 1] = id[1];
+            s->indices[3 * (size_t)f + 2] = id[2];
+            p += istride == 0 ? 3 * sizeof(int) : (size_t)istride;
+        }
+    }
+    for (int v : s->indices)
+        if (v < 0 || v >= vnum) return fail(RRB_ERROR_INVALID_ARGUMENT, "CreateMesh: vertex index out of range");
+    s->id = api->next_id++;
+    *out = s.release();
+    return RRB_OK;
+}
+
+int rrb_create_instance(rrb_api* api, const rrb_shape* base, rrb_shape** out) {
+    if (!api || !base || !out) return fail(RRB_ERROR_INVALID_ARGUMENT, "CreateInstance: null argument");
+    rrb_shape* s = new rrb_shape();
+    s->is_instance = true;
+    s->base = base->is_instance ? base->base : base;
+    s->id = api->next_id++;
+    *out = s;
+    return RRB_OK;
+}
+
+int rrb_delete_shape(rrb_api* api, rrb_shape* shape) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    if (!shape) return RRB_OK;
+    auto it = std::find(api->world.begin(), api->world.end(), (const rrb_shape*)shape);
+    if (it != api->world.end()) {
+        api->world.erase(it);
+        api->world_changed = true;
+    }
+    delete shape;
+    return RRB_OK;
+}
+
+int rrb_attach(rrb_api* api, const rrb_shape* shape) {
+    if (!api || !shape) return fail(RRB_ERROR_INVALID_ARGUMENT, "AttachShape: null argument");
+    if (std::find(api->world.begin(), api->world.end(), shape) == api->world.end()) {
+        api->world.push_back(shape);
+        api->world_changed = true;
+    }
+    return RRB_OK;
+}
+
+int rrb_detach(rrb_api* api, const rrb_shape* shape) {
+    if (!api || !shape) return fail(RRB_ERROR_INVALID_ARGUMENT, "DetachShape: null argument");
+    auto it = std::find(api->world.begin(), api->world.end(), shape);
+    if (it != api->world.end()) {
+        api->world.erase(it);
+        api->world_changed = true;
+    }
+    return RRB_OK;
+}
+
+int rrb_detach_all(rrb_api* api) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    api->world.clear();
+    api->world_changed = true;
+    return RRB_OK;
+}
+
+int rrb_commit(rrb_api* api) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    if (api->world.empty()) return fail(RRB_ERROR_EMPTY_SCENE, "Scene is empty.");
+    bool dirty = api->world_changed || !api->d_nodes;
+    for (const rrb_shape* s : api->world) dirty = dirty || s->changed || (s->base && s->base->changed);
+    if (!dirty) return RRB_OK;
+    int rc = set_device(api);
+    if (rc) return rc;
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<mcrt::BuildInputMesh> meshes;
+    meshes.reserve(api->world.size());
+    for (const rrb_shape* s : api->world) {
+        const rrb_shape* g = s->is_instance ? s->base : s;
+        if (!g || g->indices.empty()) continue;   // Intersection_1Ray_InstanceNoShape: nothing to add
+        mcrt::BuildInputMesh m;
+        m.vertices = g->vertices.data();
+        m.vnum = (int)(g->vertices.size() / 3);
+        m.vstride = 12;
+        m.indices = g->indices.data();
+        m.istride = 12;
+        m.numfaces = (int)(g->indices.size() / 3);
+        m.shape_id = s->id;
+        std::memcpy(m.m, s->m, sizeof(m.m));
+        meshes.push_back(m);
+    }
+    mcrt::BuildOptions opt;
+    auto b = api->str_options.find("bvh.builder");
+    opt.use_sah = !(b != api->str_options.end() && b->second == "median");
+    mcrt::Bvh8 bvh;
+    try {
+        mcrt::build_bvh8(meshes, opt, bvh);
+    } catch (const std::exception& ex) {
+        bool empty = std::string(ex.what()) == "Scene is empty.";
+        return fail(empty ? RRB_ERROR_EMPTY_SCENE : RRB_ERROR_INVALID_ARGUMENT, ex.what());
+    }
+    RRB_CUDA(cudaStreamSynchronize(api->stream));
+    free_bvh(api);
+    RRB_CUDA(cudaMalloc(&api->d_nodes, bvh.nodes.size() * sizeof(uint32_t)));
+    RRB_CUDA(cudaMalloc(&api->d_tris, bvh.triangles.size() * sizeof(float)));
+    RRB_CUDA(cudaMemcpyAsync(api->d_nodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(uint32_t),
+                             cudaMemcpyHostToDevice, api->stream));
+    RRB_CUDA(cudaMemcpyAsync(api->d_tris, bvh.triangles.data(), bvh.triangles.size() * sizeof(float),
+                             cudaMemcpyHostToDevice, api->stream));
+    RRB_CUDA(cudaStreamSynchronize(api->stream));
+    api->num_nodes = bvh.num_nodes;
+    api->num_tris = bvh.num_tris;
+    api->world_changed = false;
+    for (const rrb_shape* s : api->world) {
+        const_cast<rrb_shape*>(s)->changed = false;
+        if (s->base) const_cast<rrb_shape*>(s->base)->changed = false;
+    }
+    api->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return RRB_OK;
+}
+
+int rrb_reset_id_counter(rrb_api* api) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    api->next_id = 1;
+    return RRB_OK;
+}
+
+int rrb_is_world_empty(rrb_api* api, int* out_empty) {
+    if (!api || !out_empty) return fail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    *out_empty = api->world.empty() ? 1 : 0;
+    return RRB_OK;
+}
+
+int rrb_shape_set_transform(rrb_shape* shape, const float m[16], const float minv[16]) {
+    if (!shape || !m) return fail(RRB_ERROR_INVALID_ARGUMENT, "SetTransform: null argument");
+    std::memcpy(shape->m, m, sizeof(shape->m));
+    if (minv) std::memcpy(shape->minv, minv, sizeof(shape->minv));
+    shape->changed = true;
+    return RRB_OK;
+}
+
+int rrb_shape_get_transform(const rrb_shape* shape, float m[16], float minv[16]) {
+    if (!shape) return fail(RRB_ERROR_INVALID_ARGUMENT, "GetTransform: null shape");
+    if (m) std::memcpy(m, shape->m, sizeof(shape->m));
+    if (minv) std::memcpy(minv, shape->minv, sizeof(shape->minv));
+    return RRB_OK;
+}
+
+int rrb_shape_set_id(rrb_shape* shape, int id) {
+    if (!shape) return fail(RRB_ERROR_INVALID_ARGUMENT, "SetId: null shape");
+    shape->id = id;
+    shape->changed = true;
+    return RRB_OK;
+}
+
+int rrb_shape_get_id(const rrb_shape* shape, int* out_id) {
+    if (!shape || !out_id) return fail(RRB_ERROR_INVALID_ARGUMENT, "GetId: null argument");
+    *out_id = shape->id;
+    return RRB_OK;
+}
+
+int rrb_shape_set_linear_velocity(rrb_shape* shape, const float v[3]) {
+    if (!shape || !v) return fail(RRB_ERROR_INVALID_ARGUMENT, "SetLinearVelocity: null argument");
+    std::memcpy(shape->linear_velocity, v, sizeof(shape->linear_velocity));
+    return RRB_OK;
+}
+
+int rrb_shape_set_angular_velocity(rrb_shape* shape, const float q[4]) {
+    if (!shape || !q) return fail(RRB_ERROR_INVALID_ARGUMENT, "SetAngularVelocity: null argument");
+    std::memcpy(shape->angular_velocity, q, sizeof(shape->angular_velocity));
+    return RRB_OK;
+}
+
+int rrb_set_option_str(rrb_api* api, const char* name, const char* value) {
+    if (!api || !name || !value) return fail(RRB_ERROR_INVALID_ARGUMENT, "SetOption: null argument");
+    auto it = api->str_options.find(name);
+    if (it == api->str_options.end() || it->second != value) {
+        api->str_options[name] = value;
+        api->world_changed = true;   // options feed the builder
+    }
+    return RRB_OK;
+}
+
+int rrb_set_option_f32(rrb_api* api, const char* name, float value) {
+    if (!api || !name) return fail(RRB_ERROR_INVALID_ARGUMENT, "SetOption: null argument");
+    api->f32_options[name] = value;
+    return RRB_OK;
+}
+
+int rrb_create_buffer(rrb_api* api, size_t size, const void* initdata, rrb_buffer** out) {
+    if (!api || !out) return fail(RRB_ERROR_INVALID_ARGUMENT, "CreateBuffer: null argument");
+    int rc = set_device(api);
+    if (rc) return rc;
+    std::unique_ptr<rrb_buffer> b(new rrb_buffer());
+    b->size = size;
+    b->owning = true;
+    if (size) {
+        cudaError_t e = cudaMalloc(&b->dptr, size);
+        if (e != cudaSuccess) return fail(RRB_ERROR_OUT_OF_MEMORY, std::string("cudaMalloc: ") + cudaGetErrorString(e));
+        if (initdata) {
+            RRB_CUDA(cudaMemcpyAsync(b->dptr, initdata, size, cudaMemcpyHostToDevice, api->stream));
+            RRB_CUDA(cudaStreamSynchronize(api->stream));
+        }
+    }
+    *out = b.release();
+    return RRB_OK;
+}
+
+int rrb_wrap_device_ptr(rrb_api* api, void* device_ptr, size_t size, rrb_buffer** out) {
+    if (!api || !out || (!device_ptr && size)) return fail(RRB_ERROR_INVALID_ARGUMENT, "wrap: null argument");
+    rrb_buffer* b = new rrb_buffer();
+    b->dptr = device_ptr;
+    b->size = size;
+    b->owning = false;
+    *out = b;
+    return RRB_OK;
+}
+
+int rrb_delete_buffer(rrb_api* api, rrb_buffer* buffer) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    if (!buffer) return RRB_OK;
+    if (buffer->host_map) cudaFreeHost(buffer->host_map);
+    if (buffer->owning && buffer->dptr) {
+        cudaSetDevice(api->device);
+        cudaStreamSynchronize(api->stream);
+        cudaFree(buffer->dptr);
+    }
+    delete buffer;
+    return RRB_OK;
+}
+
+int rrb_buffer_device_ptr(const rrb_buffer* buffer, void** out_ptr, size_t* out_size) {
+    if (!buffer) return fail(RRB_ERROR_INVALID_ARGUMENT, "null buffer");
+    if (out_ptr) *out_ptr = buffer->dptr;
+    if (out_size) *out_size = buffer->size;
+    return RRB_OK;
+}
+
+int rrb_map(rrb_api* api, rrb_buffer* buffer, int map_type, size_t offset, size_t size, void** data, rrb_event** ev) {
+    if (!api || !buffer || !data) return fail(RRB_ERROR_INVALID_ARGUMENT, "MapBuffer: null argument");
+    if (offset + size > buffer->size) return fail(RRB_ERROR_INVALID_ARGUMENT, "MapBuffer: range out of bounds");
+    if (buffer->host_map) return fail(RRB_ERROR_INVALID_ARGUMENT, "MapBuffer: buffer is already mapped");
+    int rc = set_device(api);
+    if (rc) return rc;
+    RRB_CUDA(cudaMallocHost(&buffer->host_map, size ? size : 1));
+    buffer->map_offset = offset;
+    buffer->map_size = size;
+    buffer->map_type = map_type;
+    if ((map_type & RRB_MAP_READ) && size)
+        RRB_CUDA(cudaMemcpyAsync(buffer->host_map, (const char*)buffer->dptr + offset, size, cudaMemcpyDeviceToHost,
+                                 api->stream));
+    *data = buffer->host_map;
+    return record_done(api, ev);
+}
+
+int rrb_unmap(rrb_api* api, rrb_buffer* buffer, void* ptr, rrb_event** ev) {
+    if (!api || !buffer) return fail(RRB_ERROR_INVALID_ARGUMENT, "UnmapBuffer: null argument");
+    if (!buffer->host_map || (ptr && ptr != buffer->host_map))
+        return fail(RRB_ERROR_INVALID_ARGUMENT, "UnmapBuffer: pointer was not returned by MapBuffer");
+    int rc = set_device(api);
+    if (rc) return rc;
+    if ((buffer->map_type & RRB_MAP_WRITE) && buffer->map_size)
+        RRB_CUDA(cudaMemcpyAsync((char*)buffer->dptr + buffer->map_offset, buffer->host_map, buffer->map_size,
+                                 cudaMemcpyHostToDevice, api->stream));
+    // the staging block must outlive the copy: release it once the stream has passed this point
+    RRB_CUDA(cudaStreamSynchronize(api->stream));
+    cudaFreeHost(buffer->host_map);
+    buffer->host_map = nullptr;
+    return record_done(api, ev);
+}
+
+int rrb_event_complete(rrb_event* ev, int* out_complete) {
+    if (!ev || !out_complete) return fail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    if (!ev->recorded) {
+        *out_complete = 1;
+        return RRB_OK;
+    }
+    cudaError_t e = cudaEventQuery(ev->ev);
+    if (e == cudaSuccess) *out_complete = 1;
+    else if (e == cudaErrorNotReady) *out_complete = 0;
+    else return cuda_fail(e, "cudaEventQuery");
+    return RRB_OK;
+}
+
+int rrb_event_wait(rrb_event* ev) {
+    if (!ev) return fail(RRB_ERROR_INVALID_ARGUMENT, "null event");
+    if (ev->recorded) RRB_CUDA(cudaEventSynchronize(ev->ev));
+    return RRB_OK;
+}
+
+int rrb_event_delete(rrb_api* api, rrb_event* ev) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    if (ev) api->event_pool.push_back(ev);
+    return RRB_OK;
+}
+
+int rrb_query_intersection(rrb_api* api, const rrb_buffer* rays, int numrays, rrb_buffer* hits,
+                           const rrb_event* wait, rrb_event** done) {
+    return query_common(api, false, rays, nullptr, numrays, hits, nullptr, wait, done);
+}
+
+int rrb_query_occlusion(rrb_api* api, const rrb_buffer* rays, int numrays, rrb_buffer* hitresults,
+                        const rrb_event* wait, rrb_event** done) {
+    return query_common(api, true, rays, nullptr, numrays, hitresults, nullptr, wait, done);
+}
+
+int rrb_query_intersection_indirect(rrb_api* api, const rrb_buffer* rays, const rrb_buffer* numrays, int maxrays,
+                                    rrb_buffer* hits, const rrb_event* wait, rrb_event** done) {
+    if (!numrays) return fail(RRB_ERROR_INVALID_ARGUMENT, "null ray-count buffer");
+    return query_common(api, false, rays, numrays, maxrays, hits, nullptr, wait, done);
+}
+
+int rrb_query_occlusion_indirect(rrb_api* api, const rrb_buffer* rays, const rrb_buffer* numrays, int maxrays,
+                                 rrb_buffer* hitresults, const rrb_event* wait, rrb_event** done) {
+    if (!numrays) return fail(RRB_ERROR_INVALID_ARGUMENT, "null ray-count buffer");
+    return query_common(api, true, rays, numrays, maxrays, hitresults, nullptr, wait, done);
+}
+
+int rrb_query_intersection_counted(rrb_api* api, const rrb_buffer* rays, int numrays, rrb_buffer* hits,
+                                   rrb_buffer* counts) {
+    if (!counts) return fail(RRB_ERROR_INVALID_ARGUMENT, "null count buffer");
+    return query_common(api, false, rays, nullptr, numrays, hits, counts, nullptr, nullptr);
+}
+
+static int query_host(rrb_api* api, bool any_hit, const void* host_rays, int numrays, void* host_out) {
+    if (!api || !host_rays || !host_out || numrays < 0) return fail(RRB_ERROR_INVALID_ARGUMENT, "bad argument");
+    if (numrays == 0) return RRB_OK;
+    int rc = set_device(api);
+    if (rc) return rc;
+    const size_t rb = (size_t)numrays * 48, ob = (size_t)numrays * (any_hit ? 4 : 32);
+    rc = ensure_stage(api, rb, ob);
+    if (rc) return rc;
+    RRB_CUDA(cudaMemcpyAsync(api->d_stage_rays, host_rays, rb, cudaMemcpyHostToDevice, api->stream));
+    // results of inactive rays are "not written": carry the caller's prefilled values through
+    RRB_CUDA(cudaMemcpyAsync(api->d_stage_out, host_out, ob, cudaMemcpyHostToDevice, api->stream));
+    rrb_buffer r, o;
+    r.dptr = api->d_stage_rays;
+    r.size = rb;
+    o.dptr = api->d_stage_out;
+    o.size = ob;
+    rc = query_common(api, any_hit, &r, nullptr, numrays, &o, nullptr, nullptr, nullptr);
+    if (rc) return rc;
+    RRB_CUDA(cudaMemcpyAsync(host_out, api->d_stage_out, ob, cudaMemcpyDeviceToHost, api->stream));
+    RRB_CUDA(cudaStreamSynchronize(api->stream));
+    return RRB_OK;
+}
+
+int rrb_query_intersection_host(rrb_api* api, const void* host_rays, int numrays, void* host_hits) {
+    return query_host(api, false, host_rays, numrays, host_hits);
+}
+
+int rrb_query_occlusion_host(rrb_api* api, const void* host_rays, int numrays, int* host_results) {
+    return query_host(api, true, host_rays, numrays, host_results);
+}
+
+int rrb_get_stats(rrb_api* api, rrb_stats* out) {
+    if (!api || !out) return fail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    out->num_triangles = api->num_tris;
+    out->num_nodes = api->num_nodes;
+    out->node_bytes = api->num_nodes * 80;
+    out->triangle_bytes = api->num_tris * 48;
+    out->build_seconds = api->build_seconds;
+    out->launches = api->launches;
+    return RRB_OK;
+}
+
+int rrb_get_bvh(rrb_api* api, const void** nodes, const void** triangles, int64_t* num_nodes, int64_t* num_tris) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    if (!api->d_nodes) return fail(RRB_ERROR_NOT_COMMITTED, "Commit() has not been called on a non-empty world");
+    if (nodes) *nodes = api->d_nodes;
+    if (triangles) *triangles = api->d_tris;
+    if (num_nodes) *num_nodes = api->num_nodes;
+    if (num_tris) *num_tris = api->num_tris;
+    return RRB_OK;
+}
+
+struct rrb_host_bvh {
+    mcrt::Bvh8 bvh;
+};
+
+int rrb_host_bvh_build(const float* vertices, int vnum, const int* indices, int numfaces, const int* face_shape_ids,
+                       int use_sah, rrb_host_bvh** out) {
+    if (!vertices || !indices || !out) return fail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    // one input mesh per run of equal shape ids, so prim ids restart with every shape
+    std::vector<mcrt::BuildInputMesh> meshes;
+    int f = 0;
+    while (f < numfaces) {
+        int g = f;
+        const int sid = face_shape_ids ? face_shape_ids[f] : 0;
+        while (g < numfaces && (face_shape_ids ? face_shape_ids[g] : 0) == sid) ++g;
+        mcrt::BuildInputMesh m;
+        m.vertices = vertices;
+        m.vnum = vnum;
+        m.vstride = 12;
+        m.indices = indices + 3 * (size_t)f;
+        m.istride = 12;
+        m.numfaces = g - f;
+        m.shape_id = sid;
+        std::memcpy(m.m, kIdentity, sizeof(m.m));
+        meshes.push_back(m);
+        f = g;
+    }
+    std::unique_ptr<rrb_host_bvh> h(new rrb_host_bvh());
+    mcrt::BuildOptions opt;
+    opt.use_sah = use_sah != 0;
+    try {
+        mcrt::build_bvh8(meshes, opt, h->bvh);
+    } catch (const std::exception& ex) {
+        bool empty = std::string(ex.what()) == "Scene is empty.";
+        return fail(empty ? RRB_ERROR_EMPTY_SCENE : RRB_ERROR_INVALID_ARGUMENT, ex.what());
+    }
+    *out = h.release();
+    return RRB_OK;
+}
+
+int rrb_host_bvh_get(const rrb_host_bvh* bvh, const uint32_t** nodes, int64_t* num_nodes, const float** triangles,
+                     int64_t* num_tris) {
+    if (!bvh) return fail(RRB_ERROR_INVALID_ARGUMENT, "null bvh");
+    if (nodes) *nodes = bvh->bvh.nodes.data();
+    if (num_nodes) *num_nodes = bvh->bvh.num_nodes;
+    if (triangles) *triangles = bvh->bvh.triangles.data();
+    if (num_tris) *num_tris = bvh->bvh.num_tris;
+    return RRB_OK;
+}
+
+int rrb_host_bvh_free(rrb_host_bvh* bvh) {
+    delete bvh;
+    return RRB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,253 @@
+// traverse.cuh -- closest-hit / any-hit traversal of the compressed 8-wide BVH (bvh8.h) for sm_100a.
+//
+// Takes the role of Radeon Rays' intersect_main / occluded_main
+// (RadeonRays/src/kernels/CL/intersect_bvh2_lds.cl:66-226,229-363).  The tree and the walk are
+// different (8-wide quantised nodes, octant-ordered bit-mask stack entries, persistent warps with
+// dynamic ray fetch); the *triangle test* is the reference's Moeller-Trumbore formulation,
+// operation for operation (common.cl:178-218), evaluated in fp32 without contraction, so the
+// accepted set and every t are bit-identical to the reference's strict build:
+//   accept iff denom != 0, 0 <= b1 <= 1, b2 >= 0, b1 + b2 <= 1, 0 <= t <= closest, then t < closest.
+// Ties (equal fp32 t) are broken deterministically by the smallest (shape id, prim id) instead of
+// the reference's tree-order "first found" (SURVEY Appendix A, E1).
+// Barycentrics are recomputed from the hit point with the reference's dot-product method
+// (common.cl:250-277).  Ray mask rule: a leaf triangle is skipped iff ray.extra.x == shape id
+// (intersect_bvh2_lds.cl:164, RR_RAY_MASK on).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mcrt {
+
+#define MCRT_STACK_SIZE 40
+#define MCRT_DYNAMIC_FETCH_THRESHOLD 20
+
+struct Ray {
+    float ox, oy, oz, tmax;
+    float dx, dy, dz;
+    int mask;
+};
+
+struct Hit {
+    float t;
+    int tri;  // absolute triangle index in the triangle array, -1 = miss
+};
+
+__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(r) : "r"(x));
+    return r;
+}
+
+__device__ __forceinline__ uint32_t extract_byte(uint32_t x, uint32_t i) { return (x >> (i * 8)) & 0xffu; }
+
+__device__ __forceinline__ float safe_inv(float d) {
+    return 1.0f / (fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d));
+}
+
+// fp32 helpers that the compiler may not contract into FMAs
+__device__ __forceinline__ float mul_(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub_(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float dot3_(float ax, float ay, float az, float bx, float by, float bz) {
+    return add_(add_(mul_(ax, bx), mul_(ay, by)), mul_(az, bz));
+}
+
+// common.cl:178-218 fast_intersect_triangle; returns true and t when accepted against t_max.
+__device__ __forceinline__ bool intersect_triangle_ref(const Ray& r, const float4 v1, const float4 v2, const float4 v3,
+                                                       float t_max, float& t_out) {
+    const float e1x = sub_(v2.x, v1.x), e1y = sub_(v2.y, v1.y), e1z = sub_(v2.z, v1.z);
+    const float e2x = sub_(v3.x, v1.x), e2y = sub_(v3.y, v1.y), e2z = sub_(v3.z, v1.z);
+    // s1 = cross(d, e2)
+    const float s1x = sub_(mul_(r.dy, e2z), mul_(r.dz, e2y));
+    const float s1y = sub_(mul_(r.dz, e2x), mul_(r.dx, e2z));
+    const float s1z = sub_(mul_(r.dx, e2y), mul_(r.dy, e2x));
+    const float denom = dot3_(s1x, s1y, s1z, e1x, e1y, e1z);
+    if (denom == 0.f) return false;
+    const float invd = __fdiv_rn(1.0f, denom);
+    const float dx = sub_(r.ox, v1.x), dy = sub_(r.oy, v1.y), dz = sub_(r.oz, v1.z);
+    const float b1 = mul_(dot3_(dx, dy, dz, s1x, s1y, s1z), invd);
+    // s2 = cross(d, e1)
+    const float s2x = sub_(mul_(dy, e1z), mul_(dz, e1y));
+    const float s2y = sub_(mul_(dz, e1x), mul_(dx, e1z));
+    const float s2z = sub_(mul_(dx, e1y), mul_(dy, e1x));
+    const float b2 = mul_(dot3_(r.dx, r.dy, r.dz, s2x, s2y, s2z), invd);
+    const float temp = mul_(dot3_(e2x, e2y, e2z, s2x, s2y, s2z), invd);
+    if (b1 < 0.f || b1 > 1.f || b2 < 0.f || add_(b1, b2) > 1.f || temp < 0.f || temp > t_max) return false;
+    t_out = temp;
+    return true;
+}
+
+// common.cl:250-277 triangle_calculate_barycentrics
+__device__ __forceinline__ float2 barycentrics_ref(float px, float py, float pz, const float4 v1, const float4 v2,
+                                                   const float4 v3) {
+    const float e1x = sub_(v2.x, v1.x), e1y = sub_(v2.y, v1.y), e1z = sub_(v2.z, v1.z);
+    const float e2x = sub_(v3.x, v1.x), e2y = sub_(v3.y, v1.y), e2z = sub_(v3.z, v1.z);
+    const float ex = sub_(px, v1.x), ey = sub_(py, v1.y), ez = sub_(pz, v1.z);
+    const float d00 = dot3_(e1x, e1y, e1z, e1x, e1y, e1z);
+    const float d01 = dot3_(e1x, e1y, e1z, e2x, e2y, e2z);
+    const float d11 = dot3_(e2x, e2y, e2z, e2x, e2y, e2z);
+    const float d20 = dot3_(ex, ey, ez, e1x, e1y, e1z);
+    const float d21 = dot3_(ex, ey, ez, e2x, e2y, e2z);
+    const float denom = sub_(mul_(d00, d11), mul_(d01, d01));
+    if (denom == 0.f) return make_float2(0.f, 0.f);
+    const float inv = __fdiv_rn(1.0f, denom);
+    const float b1 = mul_(sub_(mul_(d11, d20), mul_(d01, d21)), inv);
+    const float b2 = mul_(sub_(mul_(d00, d21), mul_(d01, d20)), inv);
+    return make_float2(b1, b2);
+}
+
+// Per-ray traversal state, kept in registers across dynamic-fetch rounds.
+struct TravState {
+    uint2 ngroup;   // x: child node base index, y: [31:24] pending internal children, [7:0] imask
+    uint2 tgroup;   // x: triangle base index,   y: [23:0] pending triangles
+    int sp;
+    float idx, idy, idz;
+    uint32_t octinv4;
+    float closest;
+    int best_tri;
+    int best_sid, best_pid;
+};
+
+template <bool ANY_HIT, bool COUNT>
+struct Traverser {
+    const uint4* __restrict__ nodes;
+    const float4* __restrict__ tris;
+
+    __device__ __forceinline__ void init(TravState& s, const Ray& r) const {
+        s.ngroup = make_uint2(0u, 0x80000000u);   // root node = child slot 7^octinv of a virtual parent
+        s.tgroup = make_uint2(0u, 0u);
+        s.sp = 0;
+        s.idx = safe_inv(r.dx);
+        s.idy = safe_inv(r.dy);
+        s.idz = safe_inv(r.dz);
+        const uint32_t oct = (r.dx < 0.f ? 1u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 4u : 0u);
+        s.octinv4 = (7u - oct) * 0x01010101u;
+        s.closest = r.tmax;
+        s.best_tri = -1;
+        s.best_sid = 0x7fffffff;
+        s.best_pid = 0x7fffffff;
+    }
+
+    // Runs until the ray is finished (returns true) or the warp's active-lane count drops under
+    // the dynamic-fetch threshold (returns false: caller refills idle lanes and calls again).
+    __device__ __forceinline__ bool run(TravState& s, const Ray& r, uint2* stack, int* counters) const {
+        uint2 ngroup = s.ngroup, tgroup = s.tgroup;
+        int sp = s.sp;
+        const uint32_t octinv4 = s.octinv4;
+        const uint32_t octinv = octinv4 & 7u;
+        bool finished = false;
+        while (true) {
+            if (ngroup.y > 0x00FFFFFFu) {
+                const uint32_t hits = ngroup.y;
+                const uint32_t imask = ngroup.y;
+                const uint32_t child_bit = 31u - __clz(hits);
+                ngroup.y &= ~(1u << child_bit);
+                if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
+                const uint32_t slot = (child_bit - 24u) ^ octinv;
+                const uint32_t rel = __popc(imask & ~(0xFFFFFFFFu << slot));
+                const uint32_t ni = ngroup.x + rel;
+                const uint4 n0 = __ldg(nodes + 5 * (size_t)ni + 0);
+                const uint4 n1 = __ldg(nodes + 5 * (size_t)ni + 1);
+                const uint4 n2 = __ldg(nodes + 5 * (size_t)ni + 2);
+                const uint4 n3 = __ldg(nodes + 5 * (size_t)ni + 3);
+                const uint4 n4 = __ldg(nodes + 5 * (size_t)ni + 4);
+                if (COUNT) counters[0]++;
+
+                ngroup.x = n1.x;
+                tgroup.x = n1.y;
+                tgroup.y = 0u;
+                uint32_t hitmask = 0u;
+                const float aix = mul_(__uint_as_float(extract_byte(n0.w, 0) << 23), s.idx);
+                const float aiy = mul_(__uint_as_float(extract_byte(n0.w, 1) << 23), s.idy);
+                const float aiz = mul_(__uint_as_float(extract_byte(n0.w, 2) << 23), s.idz);
+                const float orx = mul_(sub_(__uint_as_float(n0.x), r.ox), s.idx);
+                const float ory = mul_(sub_(__uint_as_float(n0.y), r.oy), s.idy);
+                const float orz = mul_(sub_(__uint_as_float(n0.z), r.oz), s.idz);
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    const uint32_t meta4 = half == 0 ? n1.z : n1.w;
+                    const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                    const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+                    const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+                    const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                    const uint32_t qlx = half == 0 ? n2.x : n2.y, qhx = half == 0 ? n3.z : n3.w;
+                    const uint32_t qly = half == 0 ? n2.z : n2.w, qhy = half == 0 ? n4.x : n4.y;
+                    const uint32_t qlz = half == 0 ? n3.x : n3.y, qhz = half == 0 ? n4.z : n4.w;
+                    const uint32_t xmin = r.dx < 0.f ? qhx : qlx, xmax = r.dx < 0.f ? qlx : qhx;
+                    const uint32_t ymin = r.dy < 0.f ? qhy : qly, ymax = r.dy < 0.f ? qly : qhy;
+                    const uint32_t zmin = r.dz < 0.f ? qhz : qlz, zmax = r.dz < 0.f ? qlz : qhz;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float tminx = __fmaf_rn((float)extract_byte(xmin, j), aix, orx);
+                        const float tminy = __fmaf_rn((float)extract_byte(ymin, j), aiy, ory);
+                        const float tminz = __fmaf_rn((float)extract_byte(zmin, j), aiz, orz);
+                        const float tmaxx = __fmaf_rn((float)extract_byte(xmax, j), aix, orx);
+                        const float tmaxy = __fmaf_rn((float)extract_byte(ymax, j), aiy, ory);
+                        const float tmaxz = __fmaf_rn((float)extract_byte(zmax, j), aiz, orz);
+                        const float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, 0.f));
+                        // 1 + 3 ulp widening keeps the quantised slab test conservative w.r.t. fp32 rounding
+                        const float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, s.closest)) * 1.0000004f;
+                        if (cmin <= cmax) {
+                            hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);
+                        }
+                    }
+                }
+                ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
+                tgroup.y = hitmask & 0x00FFFFFFu;
+            } else {
+                tgroup = ngroup;
+                ngroup = make_uint2(0u, 0u);
+            }
+
+            while (tgroup.y != 0u) {
+                const uint32_t ti = 31u - __clz(tgroup.y);
+                tgroup.y &= ~(1u << ti);
+                const size_t ta = (size_t)tgroup.x + ti;
+                const float4 v0 = __ldg(tris + 3 * ta + 0);
+                const float4 v1 = __ldg(tris + 3 * ta + 1);
+                const float4 v2 = __ldg(tris + 3 * ta + 2);
+                if (COUNT) counters[1]++;
+                const int sid = __float_as_int(v0.w);
+                if (r.mask == sid) continue;
+                float t;
+                if (intersect_triangle_ref(r, v0, v1, v2, s.closest, t)) {
+                    if (ANY_HIT) {
+                        if (t < s.closest) {
+                            s.best_tri = (int)ta;
+                            finished = true;
+                            break;
+                        }
+                    } else {
+                        const int pid = __float_as_int(v1.w);
+                        const bool closer = t < s.closest;
+                        const bool tie = (t == s.closest) && s.best_tri >= 0 &&
+                                         (sid < s.best_sid || (sid == s.best_sid && pid < s.best_pid));
+                        if (closer || tie) {
+                            s.closest = t;
+                            s.best_tri = (int)ta;
+                            s.best_sid = sid;
+                            s.best_pid = pid;
+                        }
+                    }
+                }
+            }
+            if (finished) break;
+
+            if (ngroup.y <= 0x00FFFFFFu) {
+                if (sp == 0) {
+                    finished = true;
+                    break;
+                }
+                ngroup = stack[--sp];
+            }
+            // dynamic fetch: leave when too few lanes of the warp still traverse
+            if (__popc(__activemask()) < MCRT_DYNAMIC_FETCH_THRESHOLD) break;
+        }
+        s.ngroup = ngroup;
+        s.tgroup = tgroup;
+        s.sp = sp;
+        return finished;
+    }
+};
+
+}  // namespace mcrt

@@ -113,3 +113,79 @@ def cornell_box(with_spheres: bool = False) -> Scene:
     lights = tri_mesh_light(light_shape, (17.0, 12.0, 4.0), mesh_area(meshes[light_shape]))
     sc = Scene("cornell_spheres" if with_spheres else "cornell", meshes, np.concatenate(mats), lights, CORNELL_CAMERA)
     return sc.finalize()
+
+
+# ----------------------------------------------------------------------------- C2 / T: torus knot
+def grid_mesh(name, P, N, UV, material, closed_u=False, closed_v=False) -> Mesh:
+    """Triangulate a (nu+1) x (nv+1) lattice of points P[i,j] (2 triangles per quad)."""
+    nu, nv = P.shape[0] - 1, P.shape[1] - 1
+    i, j = np.meshgrid(np.arange(nu), np.arange(nv), indexing="ij")
+    w = nv + 1
+    a = (i * w + j).reshape(-1)
+    b = ((i + 1) * w + j).reshape(-1)
+    c = (i * w + j + 1).reshape(-1)
+    d = ((i + 1) * w + j + 1).reshape(-1)
+    idx = np.empty((2 * a.size, 3), np.int32)
+    idx[0::2] = np.stack([a, b, c], 1)
+    idx[1::2] = np.stack([b, d, c], 1)
+    return Mesh(name, P.reshape(-1, 3).astype(f4), N.reshape(-1, 3).astype(f4), UV.reshape(-1, 2).astype(f4), idx,
+                material)
+
+
+def torus_knot_mesh(nu, nv, seed=2, p=2, q=3, tube=0.45, material=0, fit=10.0) -> Mesh:
+    """(p,q) torus knot tube, nu x nv quads -> 2*nu*nv triangles, smooth normals, radius perturbed
+    by 1 + 0.02*(hash-0.5), scaled to fit a `fit`-unit box resting on y = 0."""
+    u = np.linspace(0.0, 2 * np.pi, nu + 1)
+    v = np.linspace(0.0, 2 * np.pi, nv + 1)
+    r = 2.0 + np.cos(q * u)
+    c = np.stack([r * np.cos(p * u), -np.sin(q * u), r * np.sin(p * u)], 1)
+    dc = np.gradient(c, u, axis=0)
+    t = dc / np.linalg.norm(dc, axis=1, keepdims=True)
+    up = np.array([0.0, 1.0, 0.0])
+    n1 = np.cross(t, up)
+    n1 /= np.linalg.norm(n1, axis=1, keepdims=True)
+    n2 = np.cross(t, n1)
+    ii, jj = np.meshgrid(np.arange(nu + 1) % nu, np.arange(nv + 1) % nv, indexing="ij")
+    pert = 1.0 + 0.02 * (hash01(ii, jj, seed) - 0.5)
+    nrm = n1[:, None, :] * np.cos(v)[None, :, None] + n2[:, None, :] * np.sin(v)[None, :, None]
+    P = c[:, None, :] + nrm * (tube * pert)[:, :, None]
+    lo, hi = P.reshape(-1, 3).min(0), P.reshape(-1, 3).max(0)
+    s = fit / (hi - lo).max()
+    P = (P - np.array([0.5 * (lo[0] + hi[0]), lo[1], 0.5 * (lo[2] + hi[2])])) * s
+    UV = np.stack(np.meshgrid(np.arange(nu + 1) / nu, np.arange(nv + 1) / nv, indexing="ij"), -1)
+    m = grid_mesh("knot", P, nrm, UV, material)
+    m.indices = m.indices[:, [0, 2, 1]].copy()      # geometric normal (reference convention) = outward
+    return m
+
+
+def floor_mesh(name, half, y, material, n=1) -> Mesh:
+    g = np.linspace(-half, half, n + 1)
+    X, Z = np.meshgrid(g, g, indexing="ij")
+    P = np.stack([X, np.full_like(X, y), Z], -1)
+    N = np.zeros_like(P)
+    N[..., 1] = 1.0
+    UV = np.stack([(X + half) / (2 * half), (Z + half) / (2 * half)], -1)
+    m = grid_mesh(name, P, N, UV, material)
+    m.indices = m.indices[:, [0, 2, 1]].copy()      # face up (+y) with the reference's gn convention
+    return m
+
+
+def dragon_class(nu=660, nv=660) -> Scene:
+    """C2: 871,200-triangle glossy-dielectric knot (Trowbridge-Reitz BRDF + glossy BTDF) on a
+    2-triangle floor, one directional + one disk light."""
+    mats = [make_material(kd=(0.05, 0.05, 0.05), ks=(0.9, 0.9, 0.9), kt=(0.9, 0.95, 0.9, 1.0), roughness=(0.1, 0.1),
+                          eta=1.5), lambert((0.5, 0.5, 0.5))]
+    meshes = [torus_knot_mesh(nu, nv, material=0), floor_mesh("floor", 12.0, 0.0, 1)]
+    sc = Scene("dragon_class", meshes, np.concatenate(mats), np.zeros(0, dtype=L.LIGHT),
+               CameraSpec(position=(-11.0, 9.5, -11.0), euler_deg=(27.0, 45.0, 0.0)))
+    lo, hi = sc.world_bounds()
+    sc.lights = np.concatenate([directional_light((72.0, 0.0, 0.0), (40.0, 40.0, 40.0), lo, hi),
+                                disk_light((0.0, 14.0, 0.0), (0.0, -1.0, 0.0), 2.0, (20.0, 20.0, 20.0))])
+    return sc.finalize()
+
+
+def traversal_bench_scene(nq=707) -> Scene:
+    """T: the C2 knot re-tessellated to ~1 M triangles (707 x 707 quads x 2) + a 2-triangle floor."""
+    sc = dragon_class(nq, nq)
+    sc.name = "traversal_1M"
+    return sc

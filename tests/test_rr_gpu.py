@@ -1,0 +1,252 @@
+"""GPU suite: the CUDA traversal behind the IntersectionApi mirror (mcrt_b200.rr -> C ABI), checked
+against the brute-force oracle and -- where it was built -- the compiled reference kernel.
+The cases restate the reference's own API tests (UnitTest/radeon_rays_apitest_cl.h,
+radeon_rays_conformance_test_cl.h, radeon_rays_test_cl.h)."""
+import numpy as np
+import pytest
+
+from mcrt_b200 import rr, layouts as L, scene_library
+from oracle import port
+from raygen import random_rays, camera_rays
+
+pytestmark = pytest.mark.gpu
+
+TRI_VERTS = np.array([[-1, -1, 0], [0, 1, 0], [1, -1, 0]], np.float32)
+TRI_IDX = np.array([[0, 1, 2]], np.int32)
+
+
+@pytest.fixture()
+def api():
+    a = rr.IntersectionApi.Create(0)
+    yield a
+    rr.IntersectionApi.Delete(a)
+
+
+def one_ray(o, d, maxt=10000.0):
+    r = L.make_rays(1)
+    r["o"][0, :3] = o
+    r["o"][0, 3] = maxt
+    r["d"][0, :3] = d
+    return r
+
+
+def single_triangle(api):
+    mesh = api.CreateMesh(TRI_VERTS, 3, 12, TRI_IDX, 0, None, 1)
+    api.AttachShape(mesh)
+    api.Commit()
+    return mesh
+
+
+def test_device_info():
+    assert rr.IntersectionApi.GetDeviceCount() >= 1
+    assert "NVIDIA" in rr.IntersectionApi.GetDeviceInfo(0)["vendor"]
+
+
+def test_empty_scene_commit_throws(api):
+    """EmptyScene (radeon_rays_apitest_cl.h:140): Commit() on an empty world throws."""
+    assert api.IsWorldEmpty()
+    with pytest.raises(rr.RadeonRaysError, match="Scene is empty"):
+        api.Commit()
+
+
+def test_intersection_1ray(api):
+    """Intersection_1Ray (:203-249) through device buffers, map/unmap and events."""
+    mesh = single_triangle(api)
+    ray = one_ray((0, 0, -10), (0, 0, 1))
+    ray_buf = api.CreateBuffer(48, ray)
+    isect_buf = api.CreateBuffer(32, None)
+    ev = api.QueryIntersection(ray_buf, 1, isect_buf)
+    ev.Wait()
+    assert ev.Complete()
+    data, mev = api.MapBuffer(isect_buf, rr.MAP_READ, 0, 32, dtype=L.INTERSECTION)
+    mev.Wait()
+    assert data["shapeid"][0] == mesh.GetId() and data["primid"][0] == 0
+    assert data["uvwt"][0, 3] == np.float32(10.0)
+    api.UnmapBuffer(isect_buf).Wait()
+    api.DeleteEvent(ev)
+    api.DeleteBuffer(ray_buf)
+    api.DeleteBuffer(isect_buf)
+
+
+def test_intersection_1ray_inactive_not_written(api):
+    """Intersection_1Ray_Active (:413-489): inactive ray leaves the pre-filled kNullId hit untouched."""
+    single_triangle(api)
+    ray = one_ray((0, 0, -10), (0, 0, 1))
+    ray["extra"][0, 1] = 0
+    pre = np.zeros(1, dtype=L.INTERSECTION)
+    pre["shapeid"], pre["primid"] = 4242, 77
+    pre["uvwt"] = 3.5
+    got = api.QueryIntersectionHost(ray, pre.copy())
+    assert got.tobytes() == pre.tobytes()
+    assert api.QueryOcclusionHost(ray, np.array([55], np.int32))[0] == 55
+
+
+def test_miss_leaves_uvwt_untouched(api):
+    single_triangle(api)
+    pre = np.zeros(1, dtype=L.INTERSECTION)
+    pre["uvwt"] = 9.25
+    pre["pad"] = 31
+    got = api.QueryIntersectionHost(one_ray((5, 5, -10), (0, 0, 1)), pre.copy())
+    assert got["shapeid"][0] == -1 and got["primid"][0] == -1
+    assert (got["uvwt"] == 9.25).all() and (got["pad"] == 31).all()
+
+
+def test_intersection_3rays(api):
+    """Intersection_3Rays (:491-553)."""
+    mesh = single_triangle(api)
+    rays = np.concatenate([one_ray((0, 0, -10), (0, 0, 1)), one_ray((0, 0.5, -10), (0, 0, 1)),
+                           one_ray((0.5, -0.5, -10), (0, 0, 1))])
+    hits = api.QueryIntersectionHost(rays)
+    assert (hits["shapeid"] == mesh.GetId()).all()
+    assert (api.QueryOcclusionHost(rays) == 1).all()
+
+
+def test_masked_ray_skips_shape(api):
+    """Intersection_1Ray_Masked_* (:251-300)."""
+    mesh = single_triangle(api)
+    ray = one_ray((0, 0, -10), (0, 0, 1))
+    ray["extra"][0, 0] = mesh.GetId()
+    assert api.QueryIntersectionHost(ray)["shapeid"][0] == rr.K_NULL_ID
+    assert api.QueryOcclusionHost(ray)[0] == -1
+
+
+def test_transform_and_dynamic_geometry(api):
+    """Intersection_1Ray_Transformed / _DynamicGeo (:556,:646): SetTransform + Commit moves the shape."""
+    mesh = single_triangle(api)
+    ray0, ray5 = one_ray((0, 0, -10), (0, 0, 1)), one_ray((5, 0, -10), (0, 0, 1))
+    assert api.QueryIntersectionHost(ray0)["shapeid"][0] == mesh.GetId()
+    m = np.eye(4, dtype=np.float32)
+    m[0, 3] = 5.0
+    mesh.SetTransform(m)
+    api.Commit()
+    assert api.QueryIntersectionHost(ray0)["shapeid"][0] == rr.K_NULL_ID
+    assert api.QueryIntersectionHost(ray5)["shapeid"][0] == mesh.GetId()
+    got_m, _ = mesh.GetTransform()
+    assert np.array_equal(got_m, m)
+
+
+def test_instances(api):
+    """Intersection_1Ray_TransformedInstance* / _InstanceNoShape (:844-1082): an instance carries its
+    own id and transform; the base mesh need not be attached."""
+    mesh = api.CreateMesh(TRI_VERTS, 3, 12, TRI_IDX, 0, None, 1)
+    inst = api.CreateInstance(mesh)
+    m = np.eye(4, dtype=np.float32)
+    m[1, 3] = 4.0
+    inst.SetTransform(m)
+    inst.SetId(91)
+    api.AttachShape(inst)
+    api.Commit()
+    assert api.QueryIntersectionHost(one_ray((0, 0, -10), (0, 0, 1)))["shapeid"][0] == rr.K_NULL_ID
+    assert api.QueryIntersectionHost(one_ray((0, 4, -10), (0, 0, 1)))["shapeid"][0] == 91
+    api.AttachShape(mesh)
+    api.AttachShape(mesh)       # idempotent (world.cpp:30)
+    api.Commit()
+    assert api.QueryIntersectionHost(one_ray((0, 0, -10), (0, 0, 1)))["shapeid"][0] == mesh.GetId()
+    api.DetachShape(mesh)
+    api.Commit()
+    assert api.QueryIntersectionHost(one_ray((0, 0, -10), (0, 0, 1)))["shapeid"][0] == rr.K_NULL_ID
+
+
+def test_mesh_strided(api):
+    """MeshStrided (:146): byte strides on vertices and indices."""
+    v = np.zeros((3, 5), np.float32)
+    v[:, :3] = TRI_VERTS
+    ix = np.array([[0, 1, 2, -1]], np.int32)
+    mesh = api.CreateMesh(v, 3, 20, ix, 16, None, 1)
+    api.AttachShape(mesh)
+    api.Commit()
+    assert api.QueryIntersectionHost(one_ray((0, 0, -10), (0, 0, 1)))["shapeid"][0] == mesh.GetId()
+
+
+def test_options_and_id_counter(api):
+    for k, v in [("acc.type", "fatbvh"), ("bvh.builder", "sah"), ("bvh.force2level", 0.0), ("bvh.sah.num_bins", 64.0),
+                 ("bvh.sah.traversal_cost", 10.0), ("some.unknown.key", "x")]:
+        api.SetOption(k, v)
+    a = api.CreateMesh(TRI_VERTS, 3, 12, TRI_IDX, 0, None, 1)
+    b = api.CreateMesh(TRI_VERTS, 3, 12, TRI_IDX, 0, None, 1)
+    assert b.GetId() == a.GetId() + 1
+    api.ResetIdCounter()
+    assert api.CreateMesh(TRI_VERTS, 3, 12, TRI_IDX, 0, None, 1).GetId() == 1
+    with pytest.raises(rr.RadeonRaysError):
+        api.CreateMesh(TRI_VERTS, 3, 12, np.array([[0, 1, 2, 2]], np.int32), 0, np.array([4], np.int32), 1)
+
+
+def test_interop_wrap_and_indirect_count(api):
+    """ApiCl interop cases (radeon_rays_test_cl.h:110-540): caller-owned device memory wrapped without
+    a copy, ray count read from device memory, dependency events."""
+    import torch
+    mesh = single_triangle(api)
+    rays = np.concatenate([one_ray((0, 0, -10), (0, 0, 1))] * 8)
+    t_rays = torch.from_numpy(rays.view(np.uint8).copy()).cuda()
+    t_hits = torch.full((8 * 8,), -7, dtype=torch.int32, device="cuda")
+    t_cnt = torch.tensor([5], dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    rb = api.CreateFromDevicePtr(t_rays.data_ptr(), t_rays.numel())
+    hb = api.CreateFromDevicePtr(t_hits.data_ptr(), t_hits.numel() * 4)
+    cb = api.CreateFromDevicePtr(t_cnt.data_ptr(), 4)
+    ev = api.QueryIntersectionIndirect(rb, cb, 8, hb)
+    ev2 = api.QueryOcclusion(rb, 8, api.CreateBuffer(32), waitevent=ev)
+    ev2.Wait()
+    h = t_hits.cpu().numpy().view(L.INTERSECTION)
+    assert (h["shapeid"][:5] == mesh.GetId()).all()
+    assert (h["shapeid"][5:] == -7).all()          # indices >= *numrays are not written
+
+
+@pytest.mark.parametrize("n", [1, 100, 1000, 10000])
+def test_conformance_cornell(api, cornell, n):
+    """ApiConformanceCL (radeon_rays_conformance_test_cl.h:118-560): random rays against brute force.
+    Bar: ids and t bit-exact, ties resolved to the smallest (shape, prim) -- i.e. identical to the
+    oracle, which applies the same documented rule."""
+    rr.attach_scene(api, cornell)
+    api.SetOption("acc.type", "fatbvh")
+    api.SetOption("bvh.builder", "sah")
+    api.Commit()
+    lo, hi = cornell.world_bounds()
+    rays = random_rays(n, lo - 1.0, hi + 1.0, seed=0xABCDEF12 % (2 ** 31))
+    tris = port.scene_triangles(cornell)
+    got = api.QueryIntersectionHost(rays)
+    want = port.intersect(tris, rays)
+    res = port.compare_hits(got, want, tris, rays)
+    assert res["bad"] == 0 and res["tie_ok"] == 0, res
+    assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
+
+
+def test_primary_hits_bit_exact_vs_oracle_and_reference(api, cornell, request):
+    """BASELINE config 1 primary hits, 512x512: primitive ids bit-exact against the oracle; against
+    the reference's own kernel the only differences allowed are ties."""
+    rr.attach_scene(api, cornell)
+    api.Commit()
+    rays, _ = camera_rays(cornell, 512, 512)
+    tris = port.scene_triangles(cornell)
+    got = api.QueryIntersectionHost(rays)
+    want, ties = port.intersect(tris, rays, want_ties=True)
+    res = port.compare_hits(got, want, tris, rays)
+    assert res["bad"] == 0 and res["tie_ok"] == 0, res
+    from oracle import ref
+    if ref.available():
+        o = ref.RefOracle()
+        ref_hits = o.intersect(o.build_scene_bvh(cornell), rays)
+        r2 = port.compare_hits(got, ref_hits, tris, rays)
+        assert r2["bad"] == 0, r2
+        # every id difference sits on a pixel where the oracle found more than one triangle at that t
+        assert all(ties[i] > 1 for i in r2["tie_idx"])
+
+
+def test_large_soup_bit_exact(api):
+    """200k-triangle random soup, 20k incoherent rays: closest hit and any hit against brute force."""
+    rng = np.random.RandomState(7)
+    n = 200000
+    c = rng.rand(n, 1, 3) * 20.0
+    v = (c + (rng.rand(n, 3, 3) - 0.5) * 0.5).reshape(-1, 3).astype(np.float32)
+    idx = np.arange(3 * n, dtype=np.int32).reshape(n, 3)
+    mesh = api.CreateMesh(v, 3 * n, 12, idx, 12, None, n)
+    mesh.SetId(3)
+    api.AttachShape(mesh)
+    api.Commit()
+    rays = random_rays(20000, np.zeros(3), np.full(3, 20.0), 99, maxt=8.0)
+    tris = port.mesh_triangles([(v, idx, 3, None)])
+    res = port.compare_hits(api.QueryIntersectionHost(rays), port.intersect(tris, rays), tris, rays)
+    assert res["bad"] == 0 and res["tie_ok"] == 0, res
+    assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
+    st = api.GetStats()
+    assert st["num_triangles"] == n and st["num_nodes"] > 0
