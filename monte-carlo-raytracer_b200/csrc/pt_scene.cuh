@@ -1,0 +1,188 @@
+// pt_scene.cuh -- device-side scene view, surface interaction and textures of the shading stages.
+//
+// Data stays in the reference's device layouts (assets/kernels/kernel_data.h:36-152,317-326) so the
+// host uploads RTHostScene arrays unchanged: RTShape 160 B, RTMaterial 128 B, RTLight 80 B,
+// TextureDesc2D 16 B, float3 pools with a 16-byte stride.  tangents / binormals / colors are never
+// read on this path and are not carried.
+// Restates geometry.cl:9-28,177-215, textures.cl:70-125,204-241, materials.cl:14-30.
+#pragma once
+#include "pt_math.cuh"
+
+namespace mcrt {
+
+struct RTShape {            // kernel_data.h:36-52
+    float4 toWorld[4];
+    float4 toWorldInvT[4];
+    uint32_t startIdx, startVertex, numTriangles;
+    int materialId, lightID;
+    float area;
+    int pad[2];
+};
+struct RTMaterial {         // kernel_data.h:87-113
+    float4 kd, ks, kr, kt, opacity;
+    float2 roughness;
+    float eta;
+    int type;
+    int normalMapId, diffuseTexId, glossyTexId, specReflectionTexId, transmissionTexId, opacityTexId,
+        roughnessTexId, iorTexId;
+};
+struct RTLight {            // kernel_data.h:137-152
+    float4 d, p, intensity;
+    float radius, area, choicePdf;
+    int shapeId, type, flags;
+    int pad[2];
+};
+struct TextureDesc2D {      // kernel_data.h:317-326
+    unsigned short width, height, numMipLevels, format, wrap, pad;
+    uint32_t memOffset;
+};
+struct RTPinholeCamera {    // kernel_data.h:246-264
+    float4 worldToClip[4];
+    float4 r00, r10, r11, r01, pos, direction;
+    uint32_t width, height;
+    float area;
+    int padding;
+};
+static_assert(sizeof(RTShape) == 160 && sizeof(RTMaterial) == 128 && sizeof(RTLight) == 80, "layout");
+static_assert(sizeof(TextureDesc2D) == 16 && sizeof(RTPinholeCamera) == 176, "layout");
+
+enum { RT_DIRECTIONAL_LIGHT = 0, RT_POINT_LIGHT = 1, RT_DISK_AREA_LIGHT = 2, RT_TRIANGLE_MESH_AREA_LIGHT = 3 };
+enum { TEX_WRAP_REPEAT = 0, TEX_WRAP_MIRRORED_REPEAT = 1, TEX_WRAP_CLAMP_TO_EDGE = 2, TEX_WRAP_CLAMP_TO_BORDER = 3 };
+enum {
+    RT_LIGHT_FLAG_DELTA_POSITION = 1 << 1, RT_LIGHT_FLAG_DELTA_DIRECTION = 1 << 2, RT_LIGHT_FLAG_AREA = 1 << 3,
+    RT_LIGHT_FLAG_INFINITE = 1 << 4,
+    RT_LIGHT_FLAG_DELTA_LIGHT = RT_LIGHT_FLAG_DELTA_POSITION | RT_LIGHT_FLAG_DELTA_DIRECTION
+};
+
+struct Scene {              // kernel_data.h:353-370 (device pointers)
+    const RTShape* __restrict__ shapes;
+    const uint32_t* __restrict__ indices;
+    const float4* __restrict__ positions;
+    const float2* __restrict__ uvs;
+    const float4* __restrict__ normals;
+    const TextureDesc2D* __restrict__ textures2D;
+    const unsigned char* __restrict__ texData2D;
+    const RTLight* __restrict__ lights;
+    const RTMaterial* __restrict__ materials;
+    const RTPinholeCamera* __restrict__ camera;
+    int numLights;
+};
+
+struct RTInteraction {      // kernel_data.h:162-200, the fields this path uses
+    V3 wo, p;
+    V2 uv;
+    float traceErrorOffset;
+    int shapeIdx;
+    V3 gn, sn, dpdu, dpdv, sdpdu, sdpdv;
+};
+
+// geometry.cl:9-28
+HD void computeTrianglePartialDerivates(V2 uv0, V2 uv1, V2 uv2, V3 p0, V3 p1, V3 p2, V3 normal, V3* dpdu, V3* dpdv) {
+    V2 duv02 = uv0 - uv2;
+    V2 duv12 = uv1 - uv2;
+    V3 dp02 = p0 - p2;
+    V3 dp12 = p1 - p2;
+    float det = duv02.x * duv12.y - duv02.y * duv12.x;
+    if (isNotNearZero(det)) {
+        float invdet = 1.0f / det;
+        *dpdu = (duv12.y * dp02 - duv02.y * dp12) * invdet;
+        *dpdv = -(-duv12.x * dp02 + duv02.x * dp12) * invdet;
+    } else {
+        *dpdu = normalize(computeOrthogonalVector(normal));
+        *dpdv = normalize(cross(normal, *dpdu));
+    }
+}
+
+HD void loadTrianglePositions(const Scene& sc, const RTShape* shape, int primIdx, V3* p0, V3* p1, V3* p2,
+                              uint32_t* i0, uint32_t* i1, uint32_t* i2) {
+    const uint32_t base = shape->startIdx + 3u * (uint32_t)primIdx;
+    *i0 = sc.indices[base];
+    *i1 = sc.indices[base + 1];
+    *i2 = sc.indices[base + 2];
+    *p0 = transformPoint3(shape->toWorld, v3(__ldg(sc.positions + shape->startVertex + *i0)));
+    *p1 = transformPoint3(shape->toWorld, v3(__ldg(sc.positions + shape->startVertex + *i1)));
+    *p2 = transformPoint3(shape->toWorld, v3(__ldg(sc.positions + shape->startVertex + *i2)));
+}
+
+// geometry.cl:177-215 computeSurfaceInteraction (wo / traceErrorOffset are set by the caller)
+HD RTInteraction computeSurfaceInteraction(const Scene& sc, int shapeId, int primIdx, float bu, float bv) {
+    RTInteraction si;
+    const RTShape* shape = sc.shapes + shapeId;
+    uint32_t i0, i1, i2;
+    V3 p0, p1, p2;
+    loadTrianglePositions(sc, shape, primIdx, &p0, &p1, &p2, &i0, &i1, &i2);
+    const uint32_t sv = shape->startVertex;
+    float2 t0 = __ldg(sc.uvs + sv + i0), t1 = __ldg(sc.uvs + sv + i1), t2 = __ldg(sc.uvs + sv + i2);
+    V2 uv0 = v2(t0.x, t0.y), uv1 = v2(t1.x, t1.y), uv2 = v2(t2.x, t2.y);
+    V3 n0 = transformVector3(shape->toWorldInvT, v3(__ldg(sc.normals + sv + i0)));
+    V3 n1 = transformVector3(shape->toWorldInvT, v3(__ldg(sc.normals + sv + i1)));
+    V3 n2 = transformVector3(shape->toWorldInvT, v3(__ldg(sc.normals + sv + i2)));
+    const float w = 1.0f - bu - bv;
+    si.p = p0 * w + p1 * bu + p2 * bv;
+    si.uv = uv0 * w + uv1 * bu + uv2 * bv;
+    si.gn = normalize(cross(p0 - p2, p1 - p2));
+    si.sn = normalize(n0 * w + n1 * bu + n2 * bv);
+    computeTrianglePartialDerivates(uv0, uv1, uv2, p0, p1, p2, si.sn, &si.dpdu, &si.dpdv);
+    si.sdpdu = normalize(si.dpdu - dot(si.sn, si.dpdu) * si.sn);
+    si.sdpdv = normalize(si.dpdv - dot(si.sn, si.dpdv) * si.sn - dot(si.sdpdu, si.dpdv) * si.sdpdu);
+    si.shapeIdx = shapeId;
+    si.wo = v3(0.f);
+    si.traceErrorOffset = 0.f;
+    return si;
+}
+
+// textures.cl:70-125 readTexture2Df_linear (the only filter reached: textures.cl:204-209)
+HD float4 readTexture2Df(const Scene& sc, int texId, V2 uv) {
+    const TextureDesc2D tex = sc.textures2D[texId];
+    const int tw = tex.width, th = tex.height;
+    uv.x -= 1.0f / tw * 0.5f;
+    uv.y -= 1.0f / th * 0.5f;
+    switch (tex.wrap) {
+        case TEX_WRAP_REPEAT:
+            uv.x -= floorf(uv.x);
+            uv.y -= floorf(uv.y);
+            break;
+        case TEX_WRAP_MIRRORED_REPEAT:
+            if (uv.x > 1.0f || uv.x < 0.0f) uv.x = 1.0f - (uv.x - floorf(uv.x));
+            if (uv.y > 1.0f || uv.y < 0.0f) uv.y = 1.0f - (uv.y - floorf(uv.y));
+            break;
+        case TEX_WRAP_CLAMP_TO_EDGE:
+            uv = v2(clampf(uv.x, 0.0f, 1.0f), clampf(uv.y, 0.0f, 1.0f));
+            break;
+        case TEX_WRAP_CLAMP_TO_BORDER:
+            if (uv.x > 1.0f || uv.x < 0.0f || uv.y > 1.0f || uv.y < 0.0f) return make_float4(0.f, 0.f, 0.f, 0.f);
+            break;
+    }
+    const float fx = uv.x * tw, fy = uv.y * th;
+    int x0 = ((int)floorf(fx)) % tw;
+    int y0 = ((int)floorf(fy)) % th;
+    int x1 = (x0 + 1) % tw;
+    int y1 = (y0 + 1) % th;
+    x0 = min(max(x0, 0), tw - 1);
+    y0 = min(max(y0, 0), th - 1);
+    x1 = min(max(x1, 0), tw - 1);
+    y1 = min(max(y1, 0), th - 1);
+    const float tx = fx - floorf(fx), ty = fy - floorf(fy);
+    const uchar4* texD = (const uchar4*)(sc.texData2D + tex.memOffset);
+    const uchar4 c00 = __ldg(texD + x0 + y0 * tw), c10 = __ldg(texD + x1 + y0 * tw);
+    const uchar4 c01 = __ldg(texD + x0 + y1 * tw), c11 = __ldg(texD + x1 + y1 * tw);
+    const float4 v00 = make_float4(c00.x, c00.y, c00.z, c00.w), v10 = make_float4(c10.x, c10.y, c10.z, c10.w);
+    const float4 v01 = make_float4(c01.x, c01.y, c01.z, c01.w), v11 = make_float4(c11.x, c11.y, c11.z, c11.w);
+    const float4 r = mix4(mix4(v00, v10, tx), mix4(v01, v11, tx), ty);
+    const float k = 1.0f / 255.0f;
+    return make_float4(r.x * k, r.y * k, r.z * k, r.w * k);
+}
+
+// materials.cl:14-30
+HD void applyNormalMapping(const Scene& sc, int materialIdx, RTInteraction* si) {
+    if (materialIdx == RT_INVALID_ID) return;
+    const int texId = sc.materials[materialIdx].normalMapId;
+    if (texId == RT_INVALID_ID) return;
+    const float4 t = readTexture2Df(sc, texId, si->uv);
+    const V3 nm = 2.0f * v3(t) - v3(1.0f);
+    si->sn = normalize(si->sdpdu * nm.x + si->sdpdv * nm.y + si->sn * nm.z);
+    si->sdpdu = normalize(cross(si->sn, si->sdpdv));
+    si->sdpdv = normalize(cross(si->sdpdu, si->sn));
+}
+
+}  // namespace mcrt

@@ -99,7 +99,8 @@ def compare_hits(test_hits, oracle_hits, tris, rays, ties=None):
     """Classify a CUDA (or reference-kernel) closest-hit result against the brute-force oracle.
 
     Returns a dict: exact (ids and t bit-equal), tie_ok (t bit-equal, ids differ, test winner is in
-    the tied set -- SURVEY Appendix A, E1), bad (everything else), and the indices of `bad`."""
+    the tied set -- SURVEY Appendix A, E1), b_farther (test found a hit that `oracle_hits` missed or
+    placed farther, E4), bad (everything else), and the indices of each class."""
     a, b = test_hits, oracle_hits
     active = rays["extra"][:, 1] != 0
     same_id = (a["shapeid"] == b["shapeid"]) & (a["primid"] == b["primid"])
@@ -108,12 +109,17 @@ def compare_hits(test_hits, oracle_hits, tris, rays, ties=None):
     uv_equal = (a["uvwt"][:, :3].view(np.uint32) == b["uvwt"][:, :3].view(np.uint32)).all(axis=1)
     exact = active & same_id & (~hit | (t_equal & uv_equal))
     cand = np.nonzero(active & ~exact)[0]
-    tie_ok, bad = [], []
+    tie_ok, bad, b_farther = [], [], []
     for i in cand:
         if hit[i] and a["shapeid"][i] >= 0 and t_equal[i] and hit_in_tied_set(
                 tris, rays[i:i + 1], a["uvwt"][i, 3], a["shapeid"][i], a["primid"][i]):
             tie_ok.append(int(i))
+        elif a["shapeid"][i] >= 0 and (not hit[i] or b["uvwt"][i, 3] > a["uvwt"][i, 3]):
+            # `oracle_hits` missed, or found only a farther hit than `test_hits`: when the second
+            # argument is the reference's BVH kernel this is its slab-test culling a leaf whose
+            # triangle test would have accepted -- never the brute force.
+            b_farther.append(int(i))
         else:
             bad.append(int(i))
     return {"active": int(active.sum()), "exact": int(exact.sum()), "tie_ok": len(tie_ok), "bad": len(bad),
-            "bad_idx": bad, "tie_idx": tie_ok}
+            "b_farther": len(b_farther), "bad_idx": bad, "tie_idx": tie_ok, "b_farther_idx": b_farther}

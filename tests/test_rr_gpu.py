@@ -228,6 +228,8 @@ def test_primary_hits_bit_exact_vs_oracle_and_reference(api, cornell, request):
         ref_hits = o.intersect(o.build_scene_bvh(cornell), rays)
         r2 = port.compare_hits(got, ref_hits, tris, rays)
         assert r2["bad"] == 0, r2
+        # the reference's slab test may cull a leaf its own triangle test accepts (E4): < 1e-5 of rays
+        assert r2["b_farther"] <= max(1, rays.shape[0] // 100000), r2
         # every id difference sits on a pixel where the oracle found more than one triangle at that t
         assert all(ties[i] > 1 for i in r2["tie_idx"])
 
