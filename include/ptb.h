@@ -1,0 +1,117 @@
+/* ptb.h -- C ABI of the B200 path-tracer stages (inside libmcrt_b200.so).
+ *
+ * Drop-in boundary, surface 2: what the engine's render passes call instead of compiling and
+ * launching assets/kernels/*.cl through CLW (source/application/PathTracer/raytracing/renderPasses/
+ * RTPrimaryRaysPass.cpp:32-134, RTPathTracingPass.cpp:40-218, RTBDPTPass.cpp:67-511,
+ * RTReconstructionPass.cpp:71-123) and instead of RTScene::setSceneArgs / upload*
+ * (scene/RTScene.cpp:178-197,680-809).  Pass classes mirroring the reference's are in
+ * monte-carlo-raytracer_b200/host/passes.hpp; the binding a maintainer adds is in INTEGRATION.md.
+ *
+ * A ptb_context lives on the device and stream of the rrb_api it was created from and traces
+ * against that API's committed world (rrb_commit must have run).  All functions return 0 or a
+ * negative rrb_status; the message is ptb_last_error().  No CPU fallback exists.
+ *
+ * Buffer names (ptb_get_buffer) are the reference's blackboard keys and members:
+ *   "RayBuffer"                    RTRay[P] 48 B            RTPrimaryRaysPass.cpp:64
+ *   "PrimaryIntersectionBufferCL"  Intersection[P] 32 B     RTPrimaryRaysPass.cpp:65
+ *   "ShadowRayBuffer"              RTRay[P]                 RTPathTracingPass.cpp:215
+ *   "ShadowRayOcclusionBuffer"     int32[P]                 RTPathTracingPass.cpp:216
+ *   "TempRadianceBuffer"           float4[P]                RTPathTracingPass.cpp:211
+ *   "ThroughputBuffer"             RTThroughput[P] 32 B     RTPathTracingPass.cpp:212
+ *   "RadianceBufferCL"             float4[P]                RTPathTracingPass.cpp:106 / RTBDPTPass.cpp:120
+ *   "NextFrameImageCL"             float4[P] (was a GL-interop image2d_t, RTReconstructionPass.cpp:67)
+ *   "WeightedRadianceBuffer", "FilterWeightsBuffer"  float4[P], float[P]  RTReconstructionPass.cpp:212-213
+ */
+#ifndef PTB_H
+#define PTB_H
+#include <stddef.h>
+#include <stdint.h>
+
+#include "rrb.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ptb_context ptb_context;
+
+/* Host pointers to the RTHostScene arrays (scene/RTScene.h:44-61) in the device layouts of
+ * kernel_data.h:36-152,278-294.  float3 pools have a 16-byte stride.  tangents / binormals /
+ * colors are bound by the reference but never read on this path and are not taken. */
+typedef struct ptb_scene_desc {
+    const void* shapes;          /* RTShape[num_shapes], 160 B */
+    const uint32_t* indices;     /* 3 per triangle, relative to RTShape::startVertex */
+    const float* positions;      /* float4 stride */
+    const float* uvs;            /* float2 */
+    const float* normals;        /* float4 stride */
+    const void* textures;        /* TextureDesc2D[num_textures], 16 B */
+    const unsigned char* texdata;
+    const uint32_t* sobol;       /* 1024 x 52 direction numbers or NULL (random sampler is the default) */
+    const void* lights;          /* RTLight[num_lights], 80 B */
+    const void* materials;       /* RTMaterial[num_materials], 128 B */
+    const void* camera;          /* unused here: see ptb_set_camera */
+    int32_t num_shapes, num_textures, num_lights, num_materials;
+    int64_t num_indices, num_vertices, texdata_bytes;
+} ptb_scene_desc;
+
+/* RTFilterProperties (kernel_data.h:63-80), packed for C. */
+typedef struct ptb_filter_props {
+    int32_t filter_type;         /* RT_BOX_FILTER..RT_LANCZOS_SINC_FILTER = 0..4 */
+    float radius[2];
+    float mitchell_b, mitchell_c;
+    float lanczos_sinc_tau;
+    float gaussian_alpha, gaussian_exp_x, gaussian_exp_y;
+    float pixel_offset[2];
+} ptb_filter_props;
+
+typedef struct ptb_counters {
+    int64_t closest_rays;        /* active rays given to closest-hit traversal */
+    int64_t shadow_rays;         /* active rays given to any-hit traversal */
+    int64_t shaded_vertices;     /* path vertices shaded */
+    int64_t samples;             /* pixel-samples (paths) started */
+    int64_t kernel_launches;     /* CUDA kernels launched by this context */
+} ptb_counters;
+
+const char* ptb_last_error(void);
+
+int ptb_create(rrb_api* api, ptb_context** out);
+int ptb_destroy(ptb_context* ctx);
+
+/* RTScene::uploadShapes/uploadLights/uploadMaterials/uploadTextures + buffer creation. Blocking. */
+int ptb_upload_scene(ptb_context* ctx, const ptb_scene_desc* scene);
+/* PathTracerSettings::GI.imageResolution; (re)allocates every per-pixel buffer, zero-filled. */
+int ptb_resize(ptb_context* ctx, int width, int height);
+/* WriteBuffer(camera) of RTPrimaryRaysPass.cpp:106-107 / RTBDPTPass.cpp:168-169: 176 bytes. */
+int ptb_set_camera(ptb_context* ctx, const void* rt_pinhole_camera);
+/* Multi-GPU image partition: this context renders only pixels whose 64x64 tile index t satisfies
+ * t % num_parts == part (round-robin tiles); buffers stay full-frame so global pixel
+ * indices seed the sampler.  Default (0, 1) = whole image. */
+int ptb_set_partition(ptb_context* ctx, int part, int num_parts);
+
+/* ---- stage-wise entry points in the reference's buffer layouts (one call = one kernel the reference launches) */
+int ptb_generate_primary_rays(ptb_context* ctx);                                 /* GeneratePerspectiveRays */
+int ptb_pt_shade(ptb_context* ctx, int frame, int max_depth, int bounce);       /* PathTracing */
+int ptb_pt_shadow_resolve(ptb_context* ctx, int bounce);                         /* ShadowPass */
+
+/* ---- fused wavefront: RTPrimaryRaysPass::update + RTPathTracingPass::update for one frame (one sample
+ * per pixel, `max_depth` bounces) on SoA queues with stream compaction.  Result: "RadianceBufferCL". */
+int ptb_pt_render_sample(ptb_context* ctx, int frame, int max_depth);
+/* Same for RTBDPTPass::update. */
+int ptb_bdpt_render_sample(ptb_context* ctx, int frame, int max_depth);
+
+/* ReconstructionPass (reconstruction.cl:6-60): clamp, filter weight of the frame's pixel offset,
+ * running weighted mean into "NextFrameImageCL"; frame 0 restarts the mean (reconstruction.cl:47-57). */
+int ptb_accumulate(ptb_context* ctx, int frame, const ptb_filter_props* filter);
+int ptb_reset_accumulation(ptb_context* ctx);
+
+int ptb_get_buffer(ptb_context* ctx, const char* name, void** device_ptr, size_t* bytes);
+/* Blocking device->host read of a named buffer (the step's result for the end-to-end leg). */
+int ptb_read_buffer(ptb_context* ctx, const char* name, void* host_dst, size_t bytes);
+int ptb_synchronize(ptb_context* ctx);
+int ptb_get_counters(ptb_context* ctx, ptb_counters* out);
+int ptb_reset_counters(ptb_context* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB_H */

@@ -124,6 +124,8 @@ int rrb_query_intersection_counted(rrb_api* api, const rrb_buffer* rays, int num
                                    rrb_buffer* counts);
 /* Device pointers of the committed acceleration structure (used by the path-tracer library). */
 int rrb_get_bvh(rrb_api* api, const void** nodes, const void** triangles, int64_t* num_nodes, int64_t* num_tris);
+/* The CUDA device index and cudaStream_t every query of this API is enqueued on. */
+int rrb_get_stream(rrb_api* api, int* cuda_device, void** cuda_stream);
 
 
 /* ---- host-only builder access (no CUDA call; used by the CPU test-suite to validate the tree):

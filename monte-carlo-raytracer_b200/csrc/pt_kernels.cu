@@ -1,0 +1,282 @@
+// pt_kernels.cu -- the regular path tracer's kernels for sm_100a.
+//
+// Wavefront design (replaces the reference's "every stage over all W*H work-items, dead paths
+// early-out", RTPathTracingPass.cpp:70-86): per-pixel SoA path state in HBM, queues of live pixel
+// indices compacted with a warp ballot + one atomic per warp, persistent warp-cooperative
+// traversal kernels that pull work from the queues, the shadow-ray resolve (the reference's
+// ShadowPass, PathTracing.cl:186-217) fused into the any-hit traversal, the primary-ray
+// generation fused with the zeroing of the radiance buffer.  Per bounce: closest-hit trace ->
+// shade -> any-hit trace + resolve.  No host synchronisation inside a frame: queue sizes stay on
+// the device.
+#include "pt_kernels.h"
+
+#include "pt_shade.cuh"
+#include "traverse.cuh"
+
+namespace mcrt {
+
+__device__ __forceinline__ Scene make_scene(const PtState& s) {
+    Scene sc;
+    sc.shapes = (const RTShape*)s.shapes;
+    sc.indices = s.indices;
+    sc.positions = s.positions;
+    sc.uvs = s.uvs;
+    sc.normals = s.normals;
+    sc.textures2D = (const TextureDesc2D*)s.textures2D;
+    sc.texData2D = s.texData2D;
+    sc.lights = (const RTLight*)s.lights;
+    sc.materials = (const RTMaterial*)s.materials;
+    sc.camera = (const RTPinholeCamera*)s.camera;
+    sc.numLights = s.numLights;
+    return sc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// queue control: one thread, between stages (keeps all counts on the device)
+// ---------------------------------------------------------------------------------------------
+__global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int cur, int first, int n_first) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (first) {
+        cnt[cur] = (unsigned)n_first;
+        stats[3] += (unsigned long long)n_first;
+    } else {
+        stats[1] += cnt[2];   // shadow rays of the bounce that just finished
+    }
+    stats[0] += cnt[cur];     // closest-hit rays of the bounce about to start
+    stats[2] += cnt[cur];     // = path vertices handed to the shade stage
+    cnt[1 - cur] = 0;
+    cnt[2] = 0;
+    cnt[3] = 0;
+    cnt[4] = 0;
+}
+__global__ void k_sample_end(unsigned int* cnt, unsigned long long* stats) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    stats[1] += cnt[2];
+}
+
+// ---------------------------------------------------------------------------------------------
+// primary rays (GeneratePerspectiveRays, PathTracing.cl:13-35) + radiance clear + queue fill
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_raygen(PtState s, const uint32_t* __restrict__ pixels, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t px = pixels ? pixels[i] : (uint32_t)i;
+    const RTPinholeCamera* cam = (const RTPinholeCamera*)s.camera;
+    const int x = (int)(px % (uint32_t)s.width), y = (int)(px / (uint32_t)s.width);
+    const V3 d = primary_ray_dir(cam, x, y);
+    s.ray_o[px] = make_float4(cam->pos.x, cam->pos.y, cam->pos.z, 1000.0f);
+    s.ray_d[px] = make_float4(d.x, d.y, d.z, 0.0f);
+    s.radiance[px] = make_float4(0.f, 0.f, 0.f, 0.f);
+    s.queue[0][i] = px;
+}
+
+// ---------------------------------------------------------------------------------------------
+// persistent traversal over a queue
+// ---------------------------------------------------------------------------------------------
+template <bool ANY_HIT, typename Fetch, typename Store>
+__device__ __forceinline__ void persistent_trace(const uint4* nodes, const float4* tris, unsigned count,
+                                                 unsigned int* work_counter, Fetch fetch, Store store) {
+    const unsigned lane = threadIdx.x & 31u;
+    Traverser<ANY_HIT, false> trav{nodes, tris};
+    uint2 stack[MCRT_STACK_SIZE];
+    TravState st;
+    Ray ray;
+    int item = -1;
+    bool exhausted = false;
+    while (true) {
+        const unsigned idle = __ballot_sync(0xffffffffu, item < 0 && !exhausted);
+        if (idle) {
+            const int n_idle = __popc(idle);
+            const int my_rank = __popc(idle & ((1u << lane) - 1u));
+            unsigned base = 0;
+            const int leader = __ffs(idle) - 1;
+            if ((int)lane == leader) base = atomicAdd(work_counter, (unsigned)n_idle);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (item < 0 && !exhausted) {
+                const unsigned idx = base + (unsigned)my_rank;
+                if (idx >= count) {
+                    exhausted = true;
+                } else {
+                    fetch(idx, ray);
+                    trav.init(st, ray);
+                    item = (int)idx;
+                }
+            }
+        }
+        if (__all_sync(0xffffffffu, item < 0 && exhausted)) break;
+        if (item >= 0) {
+            if (trav.run(st, ray, stack, nullptr)) {
+                store((unsigned)item, ray, st);
+                item = -1;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128, 8)
+k_trace_closest(PtState s, int cur) {
+    const unsigned count = s.cnt[cur];
+    const uint32_t* __restrict__ queue = s.queue[cur];
+    const float4* __restrict__ tris = s.tris;
+    persistent_trace<false>(
+        s.nodes, s.tris, count, s.cnt + 3,
+        [&](unsigned idx, Ray& r) {
+            const uint32_t px = queue[idx];
+            const float4 o = s.ray_o[px], d = s.ray_d[px];
+            r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmax = o.w;
+            r.dx = d.x; r.dy = d.y; r.dz = d.z;
+            r.mask = -1;   // setRay(): extra = 0xFFFFFFFF (kernel_data.h:434-440)
+        },
+        [&](unsigned idx, const Ray& r, const TravState& st) {
+            const uint32_t px = queue[idx];
+            int4 h = make_int4(-1, -1, 0, 0);
+            if (st.best_tri >= 0) {
+                const float4 v0 = __ldg(tris + 3 * (size_t)st.best_tri + 0);
+                const float4 v1 = __ldg(tris + 3 * (size_t)st.best_tri + 1);
+                const float4 v2 = __ldg(tris + 3 * (size_t)st.best_tri + 2);
+                const float hx = add_(r.ox, mul_(st.closest, r.dx));
+                const float hy = add_(r.oy, mul_(st.closest, r.dy));
+                const float hz = add_(r.oz, mul_(st.closest, r.dz));
+                const float2 uv = barycentrics_ref(hx, hy, hz, v0, v1, v2);
+                h = make_int4(__float_as_int(v0.w), __float_as_int(v1.w), __float_as_int(uv.x), __float_as_int(uv.y));
+            }
+            s.hit[px] = h;
+        });
+}
+
+// any-hit traversal fused with the reference's ShadowPass: radiance += (throughput * L) * V
+__global__ void __launch_bounds__(128, 8)
+k_trace_shadow(PtState s) {
+    const unsigned count = s.cnt[2];
+    persistent_trace<true>(
+        s.nodes, s.tris, count, s.cnt + 4,
+        [&](unsigned idx, Ray& r) {
+            const float4 o = s.sh_o[idx], d = s.sh_d[idx];
+            r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmax = o.w;
+            r.dx = d.x; r.dy = d.y; r.dz = d.z;
+            r.mask = -1;
+        },
+        [&](unsigned idx, const Ray&, const TravState& st) {
+            const uint32_t px = (uint32_t)__float_as_int(s.sh_d[idx].w);
+            const float V = st.best_tri >= 0 ? 0.0f : 1.0f;
+            const float4 L = s.sh_L[idx];
+            float4 r = s.radiance[px];
+            r.x += L.x * V;
+            r.y += L.y * V;
+            r.z += L.z * V;
+            s.radiance[px] = r;
+        });
+}
+
+// ---------------------------------------------------------------------------------------------
+// shade (PathTracing kernel body) over the live queue, with compaction of both outputs
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned warp_push(bool pred, unsigned int* counter) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0) return 0;
+    unsigned base = 0;
+    const int leader = __ffs(m) - 1;
+    if ((int)lane == leader) base = atomicAdd(counter, (unsigned)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(128)
+k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
+    const unsigned count = s.cnt[cur];
+    // grid-stride over whole warps so that the ballots below always see full warps
+    for (unsigned base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < count;
+         base += gridDim.x * blockDim.x) {
+        const unsigned i = base + (threadIdx.x & 31u);
+        bool pushNext = false, pushShadow = false;
+        ShadeOut out;
+        uint32_t px = 0;
+        if (i < count) {
+            px = s.queue[cur][i];
+            const int4 h = s.hit[px];
+            if (h.x != -1 && h.y != -1) {
+                const Scene sc = make_scene(s);
+                ShadeIn in;
+                in.pixel = (int)px;
+                in.shapeId = h.x;
+                in.primId = h.y;
+                in.bu = __int_as_float(h.z);
+                in.bv = __int_as_float(h.w);
+                const float4 d = s.ray_d[px];
+                in.rayDir = v3(d.x, d.y, d.z);
+                const float4 tp = s.throughput[px];
+                in.throughput = v3(tp.x, tp.y, tp.z);
+                in.prevBsdfFlags = __float_as_int(tp.w);
+                shade_vertex(sc, in, frame, s.width, s.height, bounce, maxDepth, &out);
+                if (out.hasEmission) {
+                    float4 r = s.radiance[px];
+                    r.x += out.emitted.x;
+                    r.y += out.emitted.y;
+                    r.z += out.emitted.z;
+                    s.radiance[px] = r;
+                } else {
+                    // a zero contribution adds nothing whatever the visibility: no shadow ray needed
+                    pushShadow = out.shadow.written &&
+                                 !(out.direct.x == 0.0f && out.direct.y == 0.0f && out.direct.z == 0.0f);
+                    pushNext = out.continues;
+                }
+            }
+        }
+        const unsigned si = warp_push(pushShadow, s.cnt + 2);
+        if (pushShadow) {
+            s.sh_o[si] = make_float4(out.shadow.o.x, out.shadow.o.y, out.shadow.o.z, out.shadow.tmax);
+            s.sh_d[si] = make_float4(out.shadow.d.x, out.shadow.d.y, out.shadow.d.z, __int_as_float((int)px));
+            s.sh_L[si] = make_float4(out.direct.x, out.direct.y, out.direct.z, 0.0f);
+        }
+        const unsigned ni = warp_push(pushNext, s.cnt + (1 - cur));
+        if (pushNext) {
+            s.ray_o[px] = make_float4(out.nextO.x, out.nextO.y, out.nextO.z, RT_MAX_TRACE_DISTANCE);
+            s.ray_d[px] = make_float4(out.nextD.x, out.nextD.y, out.nextD.z, 0.0f);
+            s.throughput[px] = make_float4(out.throughput.x, out.throughput.y, out.throughput.z,
+                                           __int_as_float(out.bsdfFlags));
+            s.queue[1 - cur][ni] = px;
+        }
+    }
+}
+
+static int sm_count() {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
+int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int frame, int max_depth,
+                     cudaStream_t stream, cudaError_t* err) {
+    int launches = 0;
+    *err = cudaSuccess;
+    if (n_pixels <= 0) return 0;
+    const int sms = sm_count();
+    const int trace_blocks = min(sms * 8, (n_pixels + 127) / 128);
+    const int shade_blocks = min(sms * 16, (n_pixels + 127) / 128);
+    k_raygen<<<(n_pixels + 255) / 256, 256, 0, stream>>>(s, pixels, n_pixels);
+    ++launches;
+    if (s.numLights > 0) {   // RTPathTracingPass::update returns early without lights (:42-43); PathTracing.cl:72
+        int cur = 0;
+        for (int b = 0; b < max_depth; ++b) {
+            k_bounce_ctl<<<1, 32, 0, stream>>>(s.cnt, s.stats, cur, b == 0, n_pixels);
+            k_trace_closest<<<trace_blocks, 128, 0, stream>>>(s, cur);
+            k_shade<<<shade_blocks, 128, 0, stream>>>(s, cur, frame, b, max_depth);
+            k_trace_shadow<<<trace_blocks, 128, 0, stream>>>(s);
+            launches += 4;
+            cur = 1 - cur;
+        }
+        k_sample_end<<<1, 32, 0, stream>>>(s.cnt, s.stats);
+        ++launches;
+    }
+    *err = cudaGetLastError();
+    return launches;
+}
+
+}  // namespace mcrt

@@ -1,0 +1,73 @@
+// pt_kernels.h -- device state and host-callable launchers of the path-tracer kernels (pt_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mcrt {
+
+struct SceneDev;  // opaque here; defined in pt_kernels.cu as mcrt::Scene
+
+// Everything a kernel needs, passed by value.  Per-pixel arrays are full-frame (P = width*height)
+// and indexed by the GLOBAL pixel index; queues hold pixel indices of live paths.
+struct PtState {
+    // scene (device pointers, reference layouts)
+    const void* shapes;
+    const uint32_t* indices;
+    const float4* positions;
+    const float2* uvs;
+    const float4* normals;
+    const void* textures2D;
+    const unsigned char* texData2D;
+    const void* lights;
+    const void* materials;
+    const void* camera;
+    int numLights;
+    int width, height;
+    // acceleration structure
+    const uint4* nodes;
+    const float4* tris;
+    // SoA wavefront state
+    float4* ray_o;        // xyz origin, w tmax
+    float4* ray_d;        // xyz direction
+    int4* hit;            // shape id, prim id, u bits, v bits
+    float4* throughput;   // rgb, w = previous BSDF flags (int bits)
+    float4* radiance;     // "RadianceBufferCL": this frame's per-pixel radiance
+    uint32_t* queue[2];   // ping-pong live-path queues (pixel indices)
+    float4* sh_o;         // shadow queue: xyz origin, w tmax
+    float4* sh_d;         // xyz direction, w = pixel index (int bits)
+    float4* sh_L;         // rgb = throughput * L (unshadowed direct light)
+    unsigned int* cnt;    // [0],[1] queue counts, [2] shadow count, [3] closest work ctr, [4] shadow work ctr
+    unsigned long long* stats;  // [0] closest rays, [1] shadow rays, [2] shaded vertices, [3] samples
+    // reference-layout (AoS) stage buffers
+    void* aos_rays;        // RTRay[P]
+    void* aos_isect;       // Intersection[P]
+    void* aos_shadow_rays; // RTRay[P]
+    int* aos_occlusion;    // int[P]
+    float4* aos_temp_radiance;
+    void* aos_throughput;  // RTThroughput[P]
+    // accumulation
+    float4* weighted_radiance;
+    float* filter_weights;
+    float4* image;         // "NextFrameImageCL"
+};
+
+// One frame of the fused wavefront path tracer.  `pixels` (device, may be NULL = identity) lists the
+// n_pixels global pixel indices this context owns.  Returns the number of kernels launched.
+int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int frame, int max_depth,
+                     cudaStream_t stream, cudaError_t* err);
+
+// Stage-wise, reference layouts.
+cudaError_t launch_generate_primary_rays(const PtState& s, cudaStream_t stream);
+cudaError_t launch_pt_shade_aos(const PtState& s, int frame, int max_depth, int bounce, cudaStream_t stream);
+cudaError_t launch_pt_shadow_resolve_aos(const PtState& s, int bounce, cudaStream_t stream);
+
+struct FilterProps {
+    int filter_type;
+    float radius[2];
+    float mitchell_b, mitchell_c, lanczos_sinc_tau, gaussian_alpha, gaussian_exp_x, gaussian_exp_y;
+    float pixel_offset[2];
+};
+cudaError_t launch_accumulate(const PtState& s, const FilterProps& f, int frame, const uint32_t* pixels, int n_pixels,
+                              cudaStream_t stream);
+
+}  // namespace mcrt

@@ -1,0 +1,118 @@
+// pt_shade.cuh -- one path vertex of the regular path tracer: surface interaction, emission,
+// next-event estimation and BSDF sampling.  Restates the body of the reference's `PathTracing`
+// kernel (assets/kernels/PathTracing.cl:52-184) as a device function on registers, so that both the
+// queue-based wavefront kernel and the reference-layout stage kernel share it.
+//
+// Reference semantics kept: emission only on the first hit or after
+// a specular bounce, and it terminates the path; one light sample per vertex; sampler re-seeded
+// per bounce with draws in the fixed order 1D light pick, 2D light sample, 2D BSDF sample; no
+// Russian roulette, no MIS, no environment term.
+#pragma once
+#include "pt_material.cuh"
+
+namespace mcrt {
+
+struct ShadeIn {
+    int pixel;            // GLOBAL buffer index (seeds the sampler)
+    int shapeId, primId;
+    float bu, bv;         // hit barycentrics
+    V3 rayDir;
+    V3 throughput;        // ignored on bounce 0 (set to 1)
+    int prevBsdfFlags;
+};
+
+struct ShadeOut {
+    V3 emitted;           // throughput * Le, added unconditionally (ignoreOcclusion = 1)
+    bool hasEmission;
+    V3 direct;            // throughput * L, to be multiplied by the shadow ray's visibility
+    ShadowRay shadow;     // .written = the reference's setRay() on the shadow ray ran
+    bool continues;       // a next ray was spawned
+    V3 nextO, nextD;
+    V3 throughput;
+    int bsdfFlags;
+};
+
+HD void shade_vertex(const Scene& sc, const ShadeIn& in, int frame, int width, int height, int bounce, int maxDepth,
+                     ShadeOut* out) {
+    out->hasEmission = false;
+    out->emitted = v3(0.0f);
+    out->direct = v3(0.0f);
+    out->shadow.written = false;
+    out->continues = false;
+    out->bsdfFlags = in.prevBsdfFlags;
+    V3 throughput = bounce == 0 ? v3(1.0f) : in.throughput;
+    out->throughput = throughput;
+
+    RTInteraction si = computeSurfaceInteraction(sc, in.shapeId, in.primId, in.bu, in.bv);
+    si.wo = -in.rayDir;
+    const bool isBackfacing = dot(si.gn, si.wo) < 0.0f;
+    si.traceErrorOffset = isBackfacing ? -RT_TRACE_OFFSET : RT_TRACE_OFFSET;
+    const RTShape* shape = sc.shapes + in.shapeId;
+    const int materialId = shape->materialId;
+    applyNormalMapping(sc, materialId, &si);
+
+    const int lightID = shape->lightID;
+    const bool isEmitter = lightID != RT_INVALID_ID;
+    const bool sampledSpecular = (BSDF_SPECULAR & in.prevBsdfFlags) == BSDF_SPECULAR;
+    if (isEmitter && (bounce == 0 || sampledSpecular)) {
+        V3 Le = evalLightLe(sc.lights + lightID, si.gn, si.wo);
+        out->emitted = throughput * Le;
+        out->hasEmission = true;
+        return;
+    }
+
+    Sampler sampler = makeSampler(in.pixel, frame, width, height, bounce);
+    UberProps um;
+    const bool hasMaterial = materialId != RT_INVALID_ID;
+    if (hasMaterial) getUberMaterialProperties(sc, materialId, &si, &um);
+
+    {   // direct lighting: one light, one sample (PathTracing.cl:106-134)
+        float lightPdf = 0.0f;
+        uint32_t lightIdx = ((uint32_t)floorf(getSample1D(&sampler) * sc.numLights));
+        lightIdx %= (uint32_t)sc.numLights;
+        V3 wi = v3(0.0f);
+        V2 u = getSample2D(&sampler);
+        V3 unusedN, unusedP;
+        V3 Li = sampleLightLi((int)lightIdx, sc, &si, u, &unusedP, &unusedN, &wi, &lightPdf, &out->shadow);
+        lightPdf *= sc.lights[lightIdx].choicePdf;
+        V3 L = v3(0.0f);
+        if (hasMaterial) {
+            V3 bsdf = evaluateUberBSDF(um, &si, si.wo, wi, TRANSPORT_MODE_RADIANCE);
+            bsdf *= absDot(wi, si.sn);
+            if (!isNearZero(lightPdf)) L = Li * bsdf / lightPdf;
+        }
+        out->direct = throughput * L;
+    }
+
+    if (bounce + 1 < maxDepth) {   // extend the path (PathTracing.cl:137-172)
+        V2 bsdfSample = getSample2D(&sampler);
+        if (hasMaterial) {
+            float pdf = 0.0f;
+            int sampledType, unused;
+            V3 wi = v3(0.0f);
+            V3 f = sampleUberBSDF(um, &si, bsdfSample, TRANSPORT_MODE_RADIANCE, BSDF_ALL, si.wo, &wi, &pdf, &unused,
+                                  &sampledType);
+            out->bsdfFlags = sampledType;
+            if (!(isNearZero(pdf) || isBlack(f))) {
+                f /= pdf;
+                V3 tp = f * absDot(wi, si.sn);
+                out->throughput = throughput * tp;
+                float traceErrorOffset = si.traceErrorOffset;
+                if ((sampledType & BSDF_TRANSMISSION) != 0 && dot(si.gn, wi) * signf(traceErrorOffset) < 0.0f)
+                    traceErrorOffset *= -1.0f;
+                out->nextO = si.p + si.gn * traceErrorOffset;
+                out->nextD = wi;
+                out->continues = true;
+            }
+        }
+    }
+}
+
+// PathTracing.cl:13-35 GeneratePerspectiveRays: pixel CORNER uv, no +0.5 (E15)
+HD V3 primary_ray_dir(const RTPinholeCamera* cam, int x, int y) {
+    const float rx = 1.0f / cam->width, ry = 1.0f / cam->height;
+    const float u = x * rx, v = y * ry;
+    return lerpDirection(v3(cam->r00), v3(cam->r10), v3(cam->r11), v3(cam->r01), u, v);
+}
+
+}  // namespace mcrt

@@ -1,0 +1,226 @@
+// pt_stage_kernels.cu -- the reference's own stage granularity in the reference's own buffer layouts
+// (for pass code that keeps the reference's per-stage dispatch), and the accumulation stage.
+//
+//   k_generate_rays_aos   GeneratePerspectiveRays  assets/kernels/PathTracing.cl:13-35
+//   k_pt_shade_aos        PathTracing              assets/kernels/PathTracing.cl:52-184
+//   k_shadow_pass_aos     ShadowPass               assets/kernels/PathTracing.cl:186-217
+//   k_accumulate          ReconstructionPass       assets/kernels/reconstruction.cl:6-60, filters.cl:12-69
+// They share shade_vertex() with the wavefront kernels; buffers they do not write keep their
+// previous contents exactly like the reference's (stale shadow rays of paths that did no NEE).
+#include "pt_kernels.h"
+
+#include "pt_shade.cuh"
+
+namespace mcrt {
+
+struct AosRay {           // RTRay, kernel_data.h:407-417
+    float4 o, d;
+    int2 extra;
+    int doBackfaceCulling, padding;
+};
+struct AosIsect {         // RTIntersection, kernel_data.h:394-405
+    int shapeid, primid, pad0, pad1;
+    float4 uvwt;
+};
+struct AosThroughput {    // RTThroughput, kernel_data.h:154-160
+    float4 throughput;
+    int prevBsdfFlags, ignoreOcclusion, pad0, pad1;
+};
+static_assert(sizeof(AosRay) == 48 && sizeof(AosIsect) == 32 && sizeof(AosThroughput) == 32, "layout");
+
+__device__ __forceinline__ Scene make_scene2(const PtState& s) {
+    Scene sc;
+    sc.shapes = (const RTShape*)s.shapes;
+    sc.indices = s.indices;
+    sc.positions = s.positions;
+    sc.uvs = s.uvs;
+    sc.normals = s.normals;
+    sc.textures2D = (const TextureDesc2D*)s.textures2D;
+    sc.texData2D = s.texData2D;
+    sc.lights = (const RTLight*)s.lights;
+    sc.materials = (const RTMaterial*)s.materials;
+    sc.camera = (const RTPinholeCamera*)s.camera;
+    sc.numLights = s.numLights;
+    return sc;
+}
+
+// setRay (kernel_data.h:434-440): o.xyz, o.w, d.xyz and extra are written; d.w and the tail are not
+__device__ __forceinline__ void set_ray(AosRay* r, V3 p, float maxRange, V3 d) {
+    r->o = make_float4(p.x, p.y, p.z, maxRange);
+    r->d.x = d.x;
+    r->d.y = d.y;
+    r->d.z = d.z;
+    r->extra = make_int2(-1, -1);
+}
+
+__global__ void __launch_bounds__(256) k_generate_rays_aos(PtState s) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s.width * s.height) return;
+    const RTPinholeCamera* cam = (const RTPinholeCamera*)s.camera;
+    const V3 d = primary_ray_dir(cam, i % s.width, i / s.width);
+    set_ray((AosRay*)s.aos_rays + i, v3(cam->pos), 1000.0f, d);
+}
+
+__global__ void __launch_bounds__(128) k_pt_shade_aos(PtState s, int frame, int maxDepth, int bounce) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s.width * s.height) return;
+    AosRay* ray = (AosRay*)s.aos_rays + i;
+    AosRay* shadow = (AosRay*)s.aos_shadow_rays + i;
+    AosThroughput* tp = (AosThroughput*)s.aos_throughput + i;
+    const AosIsect isect = ((const AosIsect*)s.aos_isect)[i];
+    float4 radiance = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ray->extra.y != 0 && isect.shapeid != -1 && isect.primid != -1 && s.numLights > 0) {
+        const Scene sc = make_scene2(s);
+        ShadeIn in;
+        in.pixel = i;
+        in.shapeId = isect.shapeid;
+        in.primId = isect.primid;
+        in.bu = isect.uvwt.x;
+        in.bv = isect.uvwt.y;
+        in.rayDir = v3(ray->d);
+        in.throughput = v3(tp->throughput);
+        in.prevBsdfFlags = tp->prevBsdfFlags;
+        ShadeOut out;
+        shade_vertex(sc, in, frame, s.width, s.height, bounce, maxDepth, &out);
+        if (bounce == 0) tp->throughput = make_float4(1.f, 1.f, 1.f, tp->throughput.w);
+        if (out.hasEmission) {
+            radiance = make_float4(out.emitted.x, out.emitted.y, out.emitted.z, 0.f);
+            shadow->extra.y = 0;
+            ray->extra.y = 0;
+            tp->ignoreOcclusion = 1;
+        } else {
+            tp->ignoreOcclusion = 0;
+            if (out.shadow.written) set_ray(shadow, out.shadow.o, out.shadow.tmax, out.shadow.d);
+            radiance = make_float4(out.direct.x, out.direct.y, out.direct.z, 0.f);
+            if (bounce + 1 < maxDepth) {
+                const int materialId = sc.shapes[isect.shapeid].materialId;
+                if (materialId != RT_INVALID_ID) {
+                    tp->prevBsdfFlags = out.bsdfFlags;
+                    if (out.continues) {
+                        tp->throughput = make_float4(out.throughput.x, out.throughput.y, out.throughput.z, tp->throughput.w);
+                        set_ray(ray, out.nextO, RT_MAX_TRACE_DISTANCE, out.nextD);
+                    } else {
+                        ray->extra.y = 0;
+                    }
+                } else {
+                    ray->extra.y = 0;
+                }
+            }
+        }
+    } else {
+        ray->extra.y = 0;
+    }
+    s.aos_temp_radiance[i] = radiance;
+}
+
+__global__ void __launch_bounds__(256) k_shadow_pass_aos(PtState s, int bounce) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s.width * s.height) return;   // the reference's `&&` border test (E11) is not reproduced
+    float4 radiance = s.aos_temp_radiance[i];
+    const AosThroughput* tp = (const AosThroughput*)s.aos_throughput + i;
+    if (tp->ignoreOcclusion == 0) {
+        const AosRay* sr = (const AosRay*)s.aos_shadow_rays + i;
+        const float V = (sr->extra.y == 0 || s.aos_occlusion[i] != -1) ? 0.0f : 1.0f;
+        radiance.x *= V;
+        radiance.y *= V;
+        radiance.z *= V;
+        radiance.w *= V;
+    }
+    if (bounce == 0) {
+        s.radiance[i] = radiance;
+    } else {
+        float4 r = s.radiance[i];
+        r.x += radiance.x;
+        r.y += radiance.y;
+        r.z += radiance.z;
+        r.w += radiance.w;
+        s.radiance[i] = r;
+    }
+}
+
+// ------------------------------------------------------------------ filters.cl:12-69
+__device__ __forceinline__ float gaussian1(float d, float alpha, float expv) { return fmaxf(0.0f, expf(-alpha * d * d) - expv); }
+__device__ __forceinline__ float mitchell1D(float x, float B, float C) {
+    x = fabsf(2.0f * x);
+    if (x > 1.0f)
+        return ((-B - 6 * C) * x * x * x + (6 * B + 30 * C) * x * x + (-12 * B - 48 * C) * x + (8 * B + 24 * C)) * (1.f / 6.f);
+    else
+        return ((12 - 9 * B - 6 * C) * x * x * x + (-18 + 12 * B + 6 * C) * x * x + (6 - 2 * B)) * (1.f / 6.f);
+}
+__device__ __forceinline__ float sinc1(float x) {
+    x = fabsf(x);
+    if (x < 1e-5) return 1.0f;
+    return sinf(PT_PI * x) / (PT_PI * x);
+}
+__device__ __forceinline__ float windowedSinc(float x, float radius, float tau) {
+    x = fabsf(x);
+    if (x > radius) return 0.0f;
+    float lanczos = sinc1(x / tau);
+    return sinc1(x) * lanczos;
+}
+__device__ __forceinline__ float filter_weight(const FilterProps& f) {
+    const float px = f.pixel_offset[0], py = f.pixel_offset[1];
+    switch (f.filter_type) {
+        case 0: return 1.0f;
+        case 1: return fmaxf(0.0f, f.radius[0] - fabsf(px)) * fmaxf(0.0f, f.radius[1] - fabsf(py));
+        case 2: return gaussian1(px, f.gaussian_alpha, f.gaussian_exp_x) * gaussian1(py, f.gaussian_alpha, f.gaussian_exp_y);
+        case 3: return mitchell1D(px / f.radius[0], f.mitchell_b, f.mitchell_c) * mitchell1D(py / f.radius[1], f.mitchell_b, f.mitchell_c);
+        case 4: return windowedSinc(px, f.radius[0], f.lanczos_sinc_tau) * windowedSinc(py, f.radius[1], f.lanczos_sinc_tau);
+        default: return 1.0f;
+    }
+}
+
+#define RT_MAX_ALLOWED_RADIANCE 1000.0f   // kernel_data.h:13
+
+__global__ void __launch_bounds__(256)
+k_accumulate(PtState s, FilterProps f, int frame, const uint32_t* __restrict__ pixels, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t px = pixels ? pixels[i] : (uint32_t)i;
+    float4 r = s.radiance[px];
+    r.x = clampf(r.x, 0.0f, RT_MAX_ALLOWED_RADIANCE);
+    r.y = clampf(r.y, 0.0f, RT_MAX_ALLOWED_RADIANCE);
+    r.z = clampf(r.z, 0.0f, RT_MAX_ALLOWED_RADIANCE);
+    r.w = clampf(r.w, 0.0f, RT_MAX_ALLOWED_RADIANCE);
+    const float w = filter_weight(f);
+    float4 acc;
+    float wsum;
+    if (frame == 0) {
+        acc = make_float4(r.x * w, r.y * w, r.z * w, r.w * w);
+        wsum = w;
+    } else {
+        acc = s.weighted_radiance[px];
+        acc.x += r.x * w;
+        acc.y += r.y * w;
+        acc.z += r.z * w;
+        acc.w += r.w * w;
+        wsum = s.filter_weights[px] + w;
+    }
+    s.weighted_radiance[px] = acc;
+    s.filter_weights[px] = wsum;
+    s.image[px] = make_float4(acc.x / wsum, acc.y / wsum, acc.z / wsum, acc.w / wsum);
+}
+
+cudaError_t launch_generate_primary_rays(const PtState& s, cudaStream_t stream) {
+    const int n = s.width * s.height;
+    k_generate_rays_aos<<<(n + 255) / 256, 256, 0, stream>>>(s);
+    return cudaGetLastError();
+}
+cudaError_t launch_pt_shade_aos(const PtState& s, int frame, int max_depth, int bounce, cudaStream_t stream) {
+    const int n = s.width * s.height;
+    k_pt_shade_aos<<<(n + 127) / 128, 128, 0, stream>>>(s, frame, max_depth, bounce);
+    return cudaGetLastError();
+}
+cudaError_t launch_pt_shadow_resolve_aos(const PtState& s, int bounce, cudaStream_t stream) {
+    const int n = s.width * s.height;
+    k_shadow_pass_aos<<<(n + 255) / 256, 256, 0, stream>>>(s, bounce);
+    return cudaGetLastError();
+}
+cudaError_t launch_accumulate(const PtState& s, const FilterProps& f, int frame, const uint32_t* pixels, int n_pixels,
+                              cudaStream_t stream) {
+    if (n_pixels <= 0) return cudaSuccess;
+    k_accumulate<<<(n_pixels + 255) / 256, 256, 0, stream>>>(s, f, frame, pixels, n_pixels);
+    return cudaGetLastError();
+}
+
+}  // namespace mcrt

@@ -1,0 +1,463 @@
+// ptb_api.cu -- implementation of include/ptb.h: device-side scene, per-pixel buffers and the
+// stage / frame entry points of the path tracer.
+//
+// Takes the role of RTScene's upload half (scene/RTScene.cpp:178-197,680-809), of
+// RTBufferManager (system/RTBufferManager.h:59-71) and of the kernel-launch halves of
+// RTPrimaryRaysPass / RTPathTracingPass / RTReconstructionPass.  No CPU fallback.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/ptb.h"
+#include "bdpt_kernels.h"
+#include "pt_kernels.h"
+
+namespace {
+thread_local std::string g_ptb_error;
+
+int pfail(int code, const std::string& msg) {
+    g_ptb_error = msg;
+    return code;
+}
+#define PTB_CUDA(call)                                                                                 \
+    do {                                                                                               \
+        cudaError_t e__ = (call);                                                                      \
+        if (e__ != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+};
+}  // namespace
+
+struct ptb_context {
+    rrb_api* api = nullptr;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int width = 0, height = 0;
+    int part = 0, num_parts = 1;
+    bool scene_loaded = false;
+    mcrt::PtState st;
+    mcrt::BdptState bd;
+    std::map<std::string, DevBuf> scene_bufs;     // freed on re-upload
+    std::map<std::string, DevBuf> pixel_bufs;     // freed on resize
+    std::map<std::string, DevBuf> named;          // ptb_get_buffer view (non-owning)
+    uint32_t* d_pixels = nullptr;                 // partition pixel list (NULL = identity)
+    int n_pixels = 0;
+    int bdpt_depth = -1;
+    int64_t launches = 0;
+    ptb_context() {
+        std::memset(&st, 0, sizeof(st));
+        std::memset(&bd, 0, sizeof(bd));
+    }
+};
+
+namespace {
+
+int set_dev(ptb_context* c) {
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+void free_map(std::map<std::string, DevBuf>& m) {
+    for (auto& kv : m)
+        if (kv.second.p) cudaFree(kv.second.p);
+    m.clear();
+}
+
+int alloc_into(std::map<std::string, DevBuf>& m, const std::string& name, size_t bytes, bool zero, cudaStream_t s,
+               void** out) {
+    DevBuf b;
+    b.bytes = bytes;
+    if (bytes) {
+        cudaError_t e = cudaMalloc(&b.p, bytes);
+        if (e != cudaSuccess)
+            return pfail(RRB_ERROR_OUT_OF_MEMORY, "cudaMalloc(" + name + ", " + std::to_string(bytes) + "): " + cudaGetErrorString(e));
+        if (zero) {
+            e = cudaMemsetAsync(b.p, 0, bytes, s);
+            if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("cudaMemsetAsync: ") + cudaGetErrorString(e));
+        }
+    }
+    m[name] = b;
+    *out = b.p;
+    return 0;
+}
+
+int upload(ptb_context* c, const std::string& name, const void* src, size_t bytes, const void** out) {
+    void* p = nullptr;
+    // keep a small non-null allocation for empty arrays so kernels never see NULL tables
+    int rc = alloc_into(c->scene_bufs, name, bytes ? bytes : 16, bytes == 0, c->stream, &p);
+    if (rc) return rc;
+    if (bytes) {
+        if (!src) return pfail(RRB_ERROR_INVALID_ARGUMENT, "scene array '" + name + "' is null");
+        cudaError_t e = cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, c->stream);
+        if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("cudaMemcpyAsync: ") + cudaGetErrorString(e));
+    }
+    *out = p;
+    return 0;
+}
+
+int refresh_bvh(ptb_context* c) {
+    const void *nodes = nullptr, *tris = nullptr;
+    int rc = rrb_get_bvh(c->api, &nodes, &tris, nullptr, nullptr);
+    if (rc) return pfail(rc, rrb_last_error());
+    c->st.nodes = (const uint4*)nodes;
+    c->st.tris = (const float4*)tris;
+    return 0;
+}
+
+int ready(ptb_context* c) {
+    if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
+    if (!c->scene_loaded) return pfail(RRB_ERROR_INVALID_ARGUMENT, "ptb_upload_scene has not been called");
+    if (c->width <= 0) return pfail(RRB_ERROR_INVALID_ARGUMENT, "ptb_resize has not been called");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    return refresh_bvh(c);
+}
+
+int build_partition(ptb_context* c) {
+    if (c->d_pixels) {
+        cudaFree(c->d_pixels);
+        c->d_pixels = nullptr;
+    }
+    const int P = c->width * c->height;
+    if (c->num_parts <= 1) {
+        c->n_pixels = P;
+        return 0;
+    }
+    // 64x64 tiles dealt round-robin in row-major tile order (partition A)
+    std::vector<uint32_t> px;
+    const int tw = (c->width + 63) / 64, th = (c->height + 63) / 64;
+    for (int ty = 0; ty < th; ++ty)
+        for (int tx = 0; tx < tw; ++tx) {
+            if ((ty * tw + tx) % c->num_parts != c->part) continue;
+            for (int y = ty * 64; y < std::min(c->height, ty * 64 + 64); ++y)
+                for (int x = tx * 64; x < std::min(c->width, tx * 64 + 64); ++x) px.push_back((uint32_t)(y * c->width + x));
+        }
+    c->n_pixels = (int)px.size();
+    if (!px.empty()) {
+        PTB_CUDA(cudaMalloc((void**)&c->d_pixels, px.size() * 4));
+        PTB_CUDA(cudaMemcpyAsync(c->d_pixels, px.data(), px.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        PTB_CUDA(cudaStreamSynchronize(c->stream));
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* ptb_last_error(void) { return g_ptb_error.c_str(); }
+
+int ptb_create(rrb_api* api, ptb_context** out) {
+    if (!api || !out) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    std::unique_ptr<ptb_context> c(new ptb_context());
+    c->api = api;
+    void* stream = nullptr;
+    int rc = rrb_get_stream(api, &c->device, &stream);
+    if (rc) return pfail(rc, rrb_last_error());
+    c->stream = (cudaStream_t)stream;
+    rc = set_dev(c.get());
+    if (rc) return rc;
+    void* p = nullptr;
+    rc = alloc_into(c->named, "__cnt", 64, true, c->stream, &p);
+    if (rc) return rc;
+    c->st.cnt = (unsigned int*)p;
+    rc = alloc_into(c->named, "__stats", 64, true, c->stream, &p);
+    if (rc) return rc;
+    c->st.stats = (unsigned long long*)p;
+    rc = alloc_into(c->named, "__camera", 176, true, c->stream, &p);
+    if (rc) return rc;
+    c->st.camera = p;
+    *out = c.release();
+    return 0;
+}
+
+int ptb_destroy(ptb_context* c) {
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_map(c->scene_bufs);
+    free_map(c->pixel_bufs);
+    for (const char* k : {"__cnt", "__stats", "__camera"}) {
+        auto it = c->named.find(k);
+        if (it != c->named.end() && it->second.p) cudaFree(it->second.p);
+    }
+    if (c->d_pixels) cudaFree(c->d_pixels);
+    delete c;
+    return 0;
+}
+
+int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
+    if (!c || !d) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    free_map(c->scene_bufs);
+    c->scene_loaded = false;
+    const void* p = nullptr;
+    if ((rc = upload(c, "shapes", d->shapes, (size_t)d->num_shapes * 160, &p))) return rc;
+    c->st.shapes = p;
+    if ((rc = upload(c, "indices", d->indices, (size_t)d->num_indices * 4, &p))) return rc;
+    c->st.indices = (const uint32_t*)p;
+    if ((rc = upload(c, "positions", d->positions, (size_t)d->num_vertices * 16, &p))) return rc;
+    c->st.positions = (const float4*)p;
+    if ((rc = upload(c, "uvs", d->uvs, (size_t)d->num_vertices * 8, &p))) return rc;
+    c->st.uvs = (const float2*)p;
+    if ((rc = upload(c, "normals", d->normals, (size_t)d->num_vertices * 16, &p))) return rc;
+    c->st.normals = (const float4*)p;
+    if ((rc = upload(c, "textures", d->textures, (size_t)d->num_textures * 16, &p))) return rc;
+    c->st.textures2D = p;
+    if ((rc = upload(c, "texdata", d->texdata, (size_t)d->texdata_bytes, &p))) return rc;
+    c->st.texData2D = (const unsigned char*)p;
+    if ((rc = upload(c, "lights", d->lights, (size_t)d->num_lights * 80, &p))) return rc;
+    c->st.lights = p;
+    if ((rc = upload(c, "materials", d->materials, (size_t)d->num_materials * 128, &p))) return rc;
+    c->st.materials = p;
+    c->st.numLights = d->num_lights;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    c->scene_loaded = true;
+    return 0;
+}
+
+int ptb_resize(ptb_context* c, int width, int height) {
+    if (!c || width <= 0 || height <= 0) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad size");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    free_map(c->pixel_bufs);
+    c->bdpt_depth = -1;
+    std::memset(&c->bd, 0, sizeof(c->bd));
+    c->width = width;
+    c->height = height;
+    c->st.width = width;
+    c->st.height = height;
+    const size_t P = (size_t)width * height;
+    struct Spec {
+        const char* name;
+        size_t elem;
+        void** dst;
+        const char* public_name;
+    };
+    mcrt::PtState& s = c->st;
+    const Spec specs[] = {
+        {"ray_o", 16, (void**)&s.ray_o, nullptr},
+        {"ray_d", 16, (void**)&s.ray_d, nullptr},
+        {"hit", 16, (void**)&s.hit, nullptr},
+        {"throughput", 16, (void**)&s.throughput, nullptr},
+        {"radiance", 16, (void**)&s.radiance, "RadianceBufferCL"},
+        {"queue0", 4, (void**)&s.queue[0], nullptr},
+        {"queue1", 4, (void**)&s.queue[1], nullptr},
+        {"sh_o", 16, (void**)&s.sh_o, nullptr},
+        {"sh_d", 16, (void**)&s.sh_d, nullptr},
+        {"sh_L", 16, (void**)&s.sh_L, nullptr},
+        {"aos_rays", 48, &s.aos_rays, "RayBuffer"},
+        {"aos_isect", 32, &s.aos_isect, "PrimaryIntersectionBufferCL"},
+        {"aos_shadow_rays", 48, &s.aos_shadow_rays, "ShadowRayBuffer"},
+        {"aos_occlusion", 4, (void**)&s.aos_occlusion, "ShadowRayOcclusionBuffer"},
+        {"aos_temp_radiance", 16, (void**)&s.aos_temp_radiance, "TempRadianceBuffer"},
+        {"aos_throughput", 32, &s.aos_throughput, "ThroughputBuffer"},
+        {"weighted_radiance", 16, (void**)&s.weighted_radiance, "WeightedRadianceBuffer"},
+        {"filter_weights", 4, (void**)&s.filter_weights, "FilterWeightsBuffer"},
+        {"image", 16, (void**)&s.image, "NextFrameImageCL"},
+    };
+    for (const Spec& sp : specs) {
+        void* p = nullptr;
+        // zero-filled at creation: defines what the reference leaves uninitialised
+        if ((rc = alloc_into(c->pixel_bufs, sp.name, P * sp.elem, true, c->stream, &p))) return rc;
+        *sp.dst = p;
+        if (sp.public_name) {
+            DevBuf v;
+            v.p = p;
+            v.bytes = P * sp.elem;
+            c->named[sp.public_name] = v;
+        }
+    }
+    rc = build_partition(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int ptb_set_camera(ptb_context* c, const void* cam) {
+    if (!c || !cam) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    // pageable source: the copy is staged before the call returns, so the caller may reuse `cam`
+    PTB_CUDA(cudaMemcpyAsync((void*)c->st.camera, cam, 176, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+
+int ptb_set_partition(ptb_context* c, int part, int num_parts) {
+    if (!c || num_parts < 1 || part < 0 || part >= num_parts) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad partition");
+    c->part = part;
+    c->num_parts = num_parts;
+    if (c->width > 0) {
+        int rc = set_dev(c);
+        if (rc) return rc;
+        PTB_CUDA(cudaStreamSynchronize(c->stream));
+        return build_partition(c);
+    }
+    return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// stage / frame entry points
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+int ptb_generate_primary_rays(ptb_context* c) {
+    int rc = ready(c);
+    if (rc) return rc;
+    PTB_CUDA(mcrt::launch_generate_primary_rays(c->st, c->stream));
+    c->launches += 1;
+    return 0;
+}
+
+int ptb_pt_shade(ptb_context* c, int frame, int max_depth, int bounce) {
+    int rc = ready(c);
+    if (rc) return rc;
+    PTB_CUDA(mcrt::launch_pt_shade_aos(c->st, frame, max_depth, bounce, c->stream));
+    c->launches += 1;
+    return 0;
+}
+
+int ptb_pt_shadow_resolve(ptb_context* c, int bounce) {
+    int rc = ready(c);
+    if (rc) return rc;
+    PTB_CUDA(mcrt::launch_pt_shadow_resolve_aos(c->st, bounce, c->stream));
+    c->launches += 1;
+    return 0;
+}
+
+int ptb_pt_render_sample(ptb_context* c, int frame, int max_depth) {
+    int rc = ready(c);
+    if (rc) return rc;
+    if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
+    cudaError_t e = cudaSuccess;
+    c->launches += mcrt::launch_pt_sample(c->st, c->d_pixels, c->n_pixels, frame, max_depth, c->stream, &e);
+    if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("path tracer launch: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+int ptb_bdpt_render_sample(ptb_context* c, int frame, int max_depth) {
+    int rc = ready(c);
+    if (rc) return rc;
+    if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
+    if (c->bdpt_depth != max_depth) {
+        // RTBDPTPass::createBuffers (RTBDPTPass.cpp:451-478): sized by maxDepth, zero-filled (E12)
+        PTB_CUDA(cudaStreamSynchronize(c->stream));
+        for (const char* k : mcrt::bdpt_buffer_names()) {
+            auto it = c->pixel_bufs.find(k);
+            if (it != c->pixel_bufs.end()) {
+                if (it->second.p) cudaFree(it->second.p);
+                c->pixel_bufs.erase(it);
+            }
+        }
+        const size_t P = (size_t)c->width * c->height;
+        for (const mcrt::BdptBufferSpec& sp : mcrt::bdpt_buffer_specs(c->bd, max_depth)) {
+            void* p = nullptr;
+            if ((rc = alloc_into(c->pixel_bufs, sp.name, P * sp.bytes_per_pixel, true, c->stream, &p))) return rc;
+            *sp.dst = p;
+        }
+        c->bdpt_depth = max_depth;
+    }
+    cudaError_t e = cudaSuccess;
+    c->launches += mcrt::launch_bdpt_sample(c->st, c->bd, frame, max_depth, c->stream, &e);
+    if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("bdpt launch: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+int ptb_accumulate(ptb_context* c, int frame, const ptb_filter_props* f) {
+    int rc = ready(c);
+    if (rc) return rc;
+    if (!f) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null filter properties");
+    mcrt::FilterProps fp;
+    fp.filter_type = f->filter_type;
+    fp.radius[0] = f->radius[0];
+    fp.radius[1] = f->radius[1];
+    fp.mitchell_b = f->mitchell_b;
+    fp.mitchell_c = f->mitchell_c;
+    fp.lanczos_sinc_tau = f->lanczos_sinc_tau;
+    fp.gaussian_alpha = f->gaussian_alpha;
+    fp.gaussian_exp_x = f->gaussian_exp_x;
+    fp.gaussian_exp_y = f->gaussian_exp_y;
+    fp.pixel_offset[0] = f->pixel_offset[0];
+    fp.pixel_offset[1] = f->pixel_offset[1];
+    PTB_CUDA(mcrt::launch_accumulate(c->st, fp, frame, c->d_pixels, c->n_pixels, c->stream));
+    c->launches += 1;
+    return 0;
+}
+
+int ptb_reset_accumulation(ptb_context* c) {
+    int rc = ready(c);
+    if (rc) return rc;
+    const size_t P = (size_t)c->width * c->height;
+    PTB_CUDA(cudaMemsetAsync(c->st.weighted_radiance, 0, P * 16, c->stream));
+    PTB_CUDA(cudaMemsetAsync(c->st.filter_weights, 0, P * 4, c->stream));
+    PTB_CUDA(cudaMemsetAsync(c->st.image, 0, P * 16, c->stream));
+    return 0;
+}
+
+int ptb_get_buffer(ptb_context* c, const char* name, void** device_ptr, size_t* bytes) {
+    if (!c || !name) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    auto it = c->named.find(name);
+    if (it == c->named.end() || name[0] == '_') return pfail(RRB_ERROR_INVALID_ARGUMENT, std::string("unknown buffer '") + name + "'");
+    if (device_ptr) *device_ptr = it->second.p;
+    if (bytes) *bytes = it->second.bytes;
+    return 0;
+}
+
+int ptb_read_buffer(ptb_context* c, const char* name, void* host_dst, size_t bytes) {
+    void* p = nullptr;
+    size_t n = 0;
+    int rc = ptb_get_buffer(c, name, &p, &n);
+    if (rc) return rc;
+    if (!host_dst || bytes > n) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad destination or size");
+    if ((rc = set_dev(c))) return rc;
+    PTB_CUDA(cudaMemcpyAsync(host_dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int ptb_synchronize(ptb_context* c) {
+    if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int ptb_get_counters(ptb_context* c, ptb_counters* out) {
+    if (!c || !out) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    unsigned long long h[8];
+    PTB_CUDA(cudaMemcpyAsync(h, c->st.stats, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    out->closest_rays = (int64_t)h[0];
+    out->shadow_rays = (int64_t)h[1];
+    out->shaded_vertices = (int64_t)h[2];
+    out->samples = (int64_t)h[3];
+    out->kernel_launches = c->launches;
+    return 0;
+}
+
+int ptb_reset_counters(ptb_context* c) {
+    if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaMemsetAsync(c->st.stats, 0, 64, c->stream));
+    c->launches = 0;
+    return 0;
+}
+
+}  // extern "C"

@@ -636,6 +636,13 @@ int rrb_get_bvh(rrb_api* api, const void** nodes, const void** triangles, int64_
     return RRB_OK;
 }
 
+int rrb_get_stream(rrb_api* api, int* cuda_device, void** cuda_stream) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    if (cuda_device) *cuda_device = api->device;
+    if (cuda_stream) *cuda_stream = (void*)api->stream;
+    return RRB_OK;
+}
+
 struct rrb_host_bvh {
     mcrt::Bvh8 bvh;
 };

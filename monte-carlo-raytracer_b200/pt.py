@@ -1,0 +1,332 @@
+"""Host-side mirror of the engine's path-tracer pass interface over the C ABI (include/ptb.h).
+
+The reference dispatches the hot path through `RenderPass::update()` objects registered with a
+`RenderPipeline` that doubles as a string-keyed blackboard
+(source/engine/rendering/architecture/RenderPass.h:6-32, RenderPipeline.h:49-71,
+RenderPipeline.cpp:36-67).  The classes here keep those names, the blackboard keys and the
+`update()` call shape; their bodies call the CUDA library instead of CLW:
+
+    RTPrimaryRaysPass   renderPasses/RTPrimaryRaysPass.cpp:32-134
+    RTPathTracingPass   renderPasses/RTPathTracingPass.cpp:40-218
+    RTBDPTPass          renderPasses/RTBDPTPass.cpp:67-511
+    RTReconstructionPass renderPasses/RTReconstructionPass.cpp:41-123
+
+ctypes is plumbing only; there is no CPU fallback.
+"""
+import ctypes
+
+import numpy as np
+
+from . import camera as camera_mod
+from . import layouts as L
+from . import rr
+
+
+class PtbSceneDesc(ctypes.Structure):
+    _fields_ = [("shapes", ctypes.c_void_p), ("indices", ctypes.c_void_p), ("positions", ctypes.c_void_p),
+                ("uvs", ctypes.c_void_p), ("normals", ctypes.c_void_p), ("textures", ctypes.c_void_p),
+                ("texdata", ctypes.c_void_p), ("sobol", ctypes.c_void_p), ("lights", ctypes.c_void_p),
+                ("materials", ctypes.c_void_p), ("camera", ctypes.c_void_p),
+                ("num_shapes", ctypes.c_int32), ("num_textures", ctypes.c_int32), ("num_lights", ctypes.c_int32),
+                ("num_materials", ctypes.c_int32), ("num_indices", ctypes.c_int64), ("num_vertices", ctypes.c_int64),
+                ("texdata_bytes", ctypes.c_int64)]
+
+
+class PtbFilterProps(ctypes.Structure):
+    _fields_ = [("filter_type", ctypes.c_int32), ("radius", ctypes.c_float * 2), ("mitchell_b", ctypes.c_float),
+                ("mitchell_c", ctypes.c_float), ("lanczos_sinc_tau", ctypes.c_float),
+                ("gaussian_alpha", ctypes.c_float), ("gaussian_exp_x", ctypes.c_float),
+                ("gaussian_exp_y", ctypes.c_float), ("pixel_offset", ctypes.c_float * 2)]
+
+
+class PtbCounters(ctypes.Structure):
+    _fields_ = [("closest_rays", ctypes.c_int64), ("shadow_rays", ctypes.c_int64), ("shaded_vertices", ctypes.c_int64),
+                ("samples", ctypes.c_int64), ("kernel_launches", ctypes.c_int64)]
+
+
+_bound = False
+
+
+def _lib():
+    global _bound
+    lib = rr.load_library()
+    if not _bound:
+        vp, i, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+        pp = ctypes.POINTER(ctypes.c_void_p)
+        sig = {
+            "ptb_create": [vp, pp], "ptb_destroy": [vp], "ptb_upload_scene": [vp, ctypes.POINTER(PtbSceneDesc)],
+            "ptb_resize": [vp, i, i], "ptb_set_camera": [vp, vp], "ptb_set_partition": [vp, i, i],
+            "ptb_generate_primary_rays": [vp], "ptb_pt_shade": [vp, i, i, i], "ptb_pt_shadow_resolve": [vp, i],
+            "ptb_pt_render_sample": [vp, i, i], "ptb_bdpt_render_sample": [vp, i, i],
+            "ptb_accumulate": [vp, i, ctypes.POINTER(PtbFilterProps)], "ptb_reset_accumulation": [vp],
+            "ptb_get_buffer": [vp, ctypes.c_char_p, pp, ctypes.POINTER(sz)],
+            "ptb_read_buffer": [vp, ctypes.c_char_p, vp, sz], "ptb_synchronize": [vp],
+            "ptb_get_counters": [vp, ctypes.POINTER(PtbCounters)], "ptb_reset_counters": [vp],
+        }
+        for name, args in sig.items():
+            fn = getattr(lib, name)
+            fn.argtypes = args
+            fn.restype = ctypes.c_int
+        lib.ptb_last_error.restype = ctypes.c_char_p
+        _bound = True
+    return lib
+
+
+class PathTracerError(RuntimeError):
+    pass
+
+
+def _check(rc):
+    if rc != 0:
+        raise PathTracerError(_lib().ptb_last_error().decode())
+
+
+def _ptr(a):
+    return None if a is None or a.size == 0 else a.ctypes.data_as(ctypes.c_void_p)
+
+
+# PathTracerSettings::GI defaults (GUI/PathTracingSettings.h:52-81)
+class GISettings:
+    def __init__(self):
+        self.maxDepth = 2
+        self.imageResolution = (1280, 720)
+        self.useTAA = True
+        self.filterType = L.RT_TRIANGLE_FILTER
+        self.filterRadius = (2.0, 2.0)
+        self.mitchellB = 1.0 / 3.0
+        self.mitchellC = 1.0 / 3.0
+        self.lanczosSincTau = 3.0
+        self.gaussianAlpha = 1.0
+        self.curPixelOffset = (0.0, 0.0)
+
+    def filter_props(self) -> PtbFilterProps:
+        f = PtbFilterProps()
+        f.filter_type = self.filterType
+        f.radius[0], f.radius[1] = self.filterRadius
+        f.mitchell_b, f.mitchell_c = self.mitchellB, self.mitchellC
+        f.lanczos_sinc_tau = self.lanczosSincTau
+        f.gaussian_alpha = self.gaussianAlpha
+        # gaussianExpX/Y = exp(-alpha * r^2) (pbrt GaussianFilter; RTReconstructionPass.cpp:95-97)
+        f.gaussian_exp_x = float(np.exp(np.float32(-self.gaussianAlpha * self.filterRadius[0] ** 2)))
+        f.gaussian_exp_y = float(np.exp(np.float32(-self.gaussianAlpha * self.filterRadius[1] ** 2)))
+        f.pixel_offset[0], f.pixel_offset[1] = self.curPixelOffset
+        return f
+
+
+class RTScene:
+    """Device scene + Radeon Rays world: RTScene's constructor, attachMesh and commit
+    (scene/RTScene.cpp:28-56,199-267,564-678) for a headless host scene."""
+
+    def __init__(self, api: rr.IntersectionApi, scene):
+        self.api = api
+        self.host = scene
+        self.shapes = rr.attach_scene(api, scene)
+        # RTScene::commit: acc.type / bvh.builder from the GUI defaults (PathTracingSettings.h:241-249)
+        api.SetOption("acc.type", "fatbvh")
+        api.SetOption("bvh.builder", "sah")
+        api.SetOption("bvh.sah.traversal_cost", 10.0)
+        api.SetOption("bvh.sah.num_bins", 64.0)
+        api.Commit()
+        h = ctypes.c_void_p()
+        _check(_lib().ptb_create(api._h, ctypes.byref(h)))
+        self._h = h
+        self.upload()
+
+    def upload(self):
+        s = self.host
+        d = PtbSceneDesc()
+        d.shapes, d.indices, d.positions = _ptr(s.shapes), _ptr(s.indices), _ptr(s.positions)
+        d.uvs, d.normals = _ptr(s.uvs), _ptr(s.normals)
+        d.textures, d.texdata, d.sobol = _ptr(s.textures), _ptr(s.texdata), None
+        d.lights, d.materials, d.camera = _ptr(s.lights), _ptr(s.materials), None
+        d.num_shapes, d.num_textures = len(s.shapes), len(s.textures)
+        d.num_lights, d.num_materials = len(s.lights), len(s.materials)
+        d.num_indices, d.num_vertices = s.indices.size, s.positions.shape[0]
+        d.texdata_bytes = s.texdata.size
+        _check(_lib().ptb_upload_scene(self._h, ctypes.byref(d)))
+
+    def destroy(self):
+        if self._h:
+            _lib().ptb_destroy(self._h)
+            self._h = None
+
+
+class RenderPipeline:
+    """engine/rendering/architecture/RenderPipeline: ordered passes + string-keyed blackboard."""
+
+    def __init__(self, rt_scene: RTScene, settings: GISettings = None):
+        self.scene = rt_scene
+        self.GI = settings or GISettings()
+        self.passes = []
+        self.board = {}
+        self.frameIndex = 0
+        self._size = None
+
+    def addRenderPasses(self, *passes):
+        for p in passes:
+            p.m_renderPipeline = self
+            self.passes.append(p)
+
+    def put(self, key, value):
+        self.board[key] = value
+
+    def fetch(self, key):
+        return self.board.get(key)
+
+    putPtr, fetchPtr = put, fetch
+
+    def ensure_size(self):
+        if self._size != tuple(self.GI.imageResolution):
+            w, h = self.GI.imageResolution
+            _check(_lib().ptb_resize(self.scene._h, int(w), int(h)))
+            self._size = (int(w), int(h))
+
+    def set_camera_for_frame(self):
+        """PathTracingApp::update TAA jitter (:208-215) + camera upload (RTPrimaryRaysPass.cpp:96-107)."""
+        self.ensure_size()
+        w, h = self._size
+        if self.GI.useTAA:
+            self.GI.curPixelOffset = camera_mod.taa_pixel_offset(self.frameIndex, self.GI.filterRadius, True)
+        cam = camera_mod.make_camera(self.scene.host.camera, w, h, self.GI.curPixelOffset)
+        _check(_lib().ptb_set_camera(self.scene._h, _ptr(cam)))
+        return cam
+
+    def update(self):
+        for p in self.passes:
+            p.update()
+
+    # ---- buffer helpers
+    def device_buffer(self, name):
+        p, n = ctypes.c_void_p(), ctypes.c_size_t()
+        _check(_lib().ptb_get_buffer(self.scene._h, name.encode(), ctypes.byref(p), ctypes.byref(n)))
+        return p.value, n.value
+
+    def read_buffer(self, name, dtype=np.float32, out=None):
+        _, n = self.device_buffer(name)
+        if out is None:
+            out = np.empty(n // np.dtype(dtype).itemsize, dtype=dtype)
+        _check(_lib().ptb_read_buffer(self.scene._h, name.encode(), _ptr(out), out.nbytes))
+        return out
+
+    def counters(self):
+        c = PtbCounters()
+        _check(_lib().ptb_get_counters(self.scene._h, ctypes.byref(c)))
+        return {k: getattr(c, k) for k, _ in PtbCounters._fields_}
+
+    def reset_counters(self):
+        _check(_lib().ptb_reset_counters(self.scene._h))
+
+    def synchronize(self):
+        _check(_lib().ptb_synchronize(self.scene._h))
+
+    def set_partition(self, part, num_parts):
+        _check(_lib().ptb_set_partition(self.scene._h, int(part), int(num_parts)))
+
+
+class RenderPass:
+    m_renderPipeline: RenderPipeline = None
+
+    def update(self):
+        raise NotImplementedError
+
+
+class RTPrimaryRaysPass(RenderPass):
+    """Stage-wise primary rays + primary hits in the reference's layouts (RTPrimaryRaysPass.cpp:32-66)."""
+
+    def update(self):
+        pl = self.m_renderPipeline
+        pl.set_camera_for_frame()
+        h, api = pl.scene._h, pl.scene.api
+        _check(_lib().ptb_generate_primary_rays(h))
+        w, hgt = pl._size
+        rp, rn = pl.device_buffer("RayBuffer")
+        ip, inb = pl.device_buffer("PrimaryIntersectionBufferCL")
+        rays = api.CreateFromDevicePtr(rp, rn)      # the engine wraps on every call (:133)
+        isect = api.CreateFromDevicePtr(ip, inb)
+        api.QueryIntersection(rays, w * hgt, isect).Wait()
+        pl.putPtr("RayBuffer", rays)
+        pl.putPtr("PrimaryIntersectionBufferCL", isect)
+
+
+class RTPathTracingPass(RenderPass):
+    """RTPathTracingPass::update (RTPathTracingPass.cpp:40-114).
+
+    fused=True (default) runs the whole frame -- primary rays included -- as the queue-based
+    wavefront (ptb_pt_render_sample); fused=False keeps the reference's stage-by-stage dispatch over
+    the reference-layout buffers and needs an RTPrimaryRaysPass before it."""
+
+    def __init__(self, fused=True):
+        self.fused = fused
+        self.m_frameIndex = 0
+
+    def update(self):
+        pl = self.m_renderPipeline
+        h, api = pl.scene._h, pl.scene.api
+        depth = int(pl.GI.maxDepth)
+        if len(pl.scene.host.lights) == 0:
+            return                                   # :42-43
+        pl.frameIndex = self.m_frameIndex
+        if self.fused:
+            pl.set_camera_for_frame()
+            _check(_lib().ptb_pt_render_sample(h, self.m_frameIndex, depth))
+        else:
+            w, hgt = pl._size
+            rays, isect = pl.fetchPtr("RayBuffer"), pl.fetchPtr("PrimaryIntersectionBufferCL")
+            sp, sn = pl.device_buffer("ShadowRayBuffer")
+            op, on = pl.device_buffer("ShadowRayOcclusionBuffer")
+            shadow, occl = api.CreateFromDevicePtr(sp, sn), api.CreateFromDevicePtr(op, on)
+            for i in range(depth):
+                _check(_lib().ptb_pt_shade(h, self.m_frameIndex, depth, i))            # applyShading
+                api.QueryOcclusion(shadow, w * hgt, occl).Wait()                       # applyVisibilityTest
+                _check(_lib().ptb_pt_shadow_resolve(h, i))
+                if i + 1 < depth:
+                    api.QueryIntersection(rays, w * hgt, isect).Wait()
+        pl.put("RadianceBufferCL", pl.device_buffer("RadianceBufferCL")[0])
+        self.m_frameIndex += 1
+        pl.frameIndex = self.m_frameIndex
+
+
+class RTBDPTPass(RenderPass):
+    """RTBDPTPass::update (RTBDPTPass.cpp:67-128)."""
+
+    def __init__(self):
+        self.m_frameIndex = 0
+
+    def update(self):
+        pl = self.m_renderPipeline
+        if len(pl.scene.host.lights) == 0:
+            return
+        pl.frameIndex = self.m_frameIndex
+        pl.set_camera_for_frame()
+        _check(_lib().ptb_bdpt_render_sample(pl.scene._h, self.m_frameIndex, int(pl.GI.maxDepth)))
+        pl.put("RadianceBufferCL", pl.device_buffer("RadianceBufferCL")[0])
+        self.m_frameIndex += 1
+        pl.frameIndex = self.m_frameIndex
+
+
+class RTReconstructionPass(RenderPass):
+    """RTReconstructionPass::updateReconstruction (RTReconstructionPass.cpp:71-123): the frame that was
+    just rendered is frameIndex - 1 (the integrator pass has already incremented it)."""
+
+    def update(self):
+        pl = self.m_renderPipeline
+        if pl.fetch("RadianceBufferCL") is None:
+            return
+        f = pl.GI.filter_props()
+        _check(_lib().ptb_accumulate(pl.scene._h, pl.frameIndex - 1, ctypes.byref(f)))
+        pl.put("NextFrameImageCL", pl.device_buffer("NextFrameImageCL")[0])
+
+
+def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=True):
+    """PathTracingApp::startPathTracing's PT pipeline (:248-255) without denoise / tonemap / display."""
+    rts = RTScene(api, scene)
+    gi = GISettings()
+    gi.imageResolution = (width, height)
+    gi.maxDepth = max_depth
+    gi.useTAA = use_taa
+    pl = RenderPipeline(rts, gi)
+    if fused:
+        pl.addRenderPasses(RTPathTracingPass(True), RTReconstructionPass())
+    else:
+        pl.addRenderPasses(RTPrimaryRaysPass(), RTPathTracingPass(False), RTReconstructionPass())
+    return pl

@@ -65,6 +65,7 @@ def load_library():
         "rrb_query_intersection_host": [vp, vp, i, vp], "rrb_query_occlusion_host": [vp, vp, i, vp],
         "rrb_get_stats": [vp, ctypes.POINTER(RrbStats)], "rrb_query_intersection_counted": [vp, vp, i, vp, vp],
         "rrb_get_bvh": [vp, pp, pp, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)],
+        "rrb_get_stream": [vp, ctypes.POINTER(i), pp],
         "rrb_host_bvh_build": [vp, i, vp, i, vp, i, pp],
         "rrb_host_bvh_get": [vp, pp, ctypes.POINTER(ctypes.c_int64), pp, ctypes.POINTER(ctypes.c_int64)],
         "rrb_host_bvh_free": [vp],

@@ -252,3 +252,18 @@ def test_large_soup_bit_exact(api):
     assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
     st = api.GetStats()
     assert st["num_triangles"] == n and st["num_nodes"] > 0
+
+
+def test_golden_intersections(api, cornell):
+    """Committed vectors from the reference's own kernel (tests/golden/cornell_isect_4096.npz)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cornell_isect_4096.npz"))
+    rays = np.ascontiguousarray(g["rays"]).view(L.RAY)
+    rr.attach_scene(api, cornell)
+    api.Commit()
+    ref_hits = np.zeros(rays.shape[0], dtype=L.INTERSECTION)
+    ref_hits["shapeid"], ref_hits["primid"], ref_hits["uvwt"] = g["shapeid"], g["primid"], g["uvwt"]
+    tris = port.scene_triangles(cornell)
+    res = port.compare_hits(api.QueryIntersectionHost(rays), ref_hits, tris, rays)
+    assert res["bad"] == 0 and res["b_farther"] <= 1, res
+    assert np.array_equal(api.QueryOcclusionHost(rays), g["occluded"])
