@@ -5,8 +5,11 @@ Reads the reference's OpenCL-C sources where they lie under /root/reference and 
 C++-compilable copies to oracle/_ref/gen/ (git-ignored; never committed).  The rewrite is
 purely mechanical -- no arithmetic, control flow or constant is touched:
 
-  1. OpenCL vector literals   `(float3)(a,b,c)` -> `make_float3(a,b,c)`   (not valid C++)
-     for float2/3/4, int2/3, uint2.
+  1. OpenCL vector literals   `(float3)(a,b,c)` -> `float3{a,b,c}`   (not valid C++)
+     for float2/3/4, int2/3, uint2.  Braced initialisation is used because it evaluates the
+     components left to right, as OpenCL compilers (clang) do; a function call would let g++
+     evaluate them right to left, which swaps the two draws of `(float2)(randFloat(..),
+     randFloat(..))` in samplers.cl:getSample2D.
   2. `#ifdef __cplusplus` in kernel_data.h -> `#ifdef MCRT_REF_HOST_BRANCH` so that the
      OpenCL branch of that shared header (the device-side struct layouts) is the one compiled.
   3. `#include <../RadeonRays/src/kernels/CL/common.cl>` -> `#include "common.cl"`.
@@ -26,8 +29,21 @@ RR_KERNELS = ["common.cl", "intersect_bvh2_lds.cl"]
 VEC_LITERAL = re.compile(r"\((float[234]|int[23]|uint2)\)\s*\(")
 
 
+def rewrite_literals(text: str) -> str:
+    while True:
+        m = VEC_LITERAL.search(text)
+        if not m:
+            return text
+        depth, j = 1, m.end()
+        while depth:
+            c = text[j]
+            depth += (c == "(") - (c == ")")
+            j += 1
+        text = text[:m.start()] + m.group(1) + "{" + text[m.end():j - 1] + "}" + text[j:]
+
+
 def rewrite(text: str) -> str:
-    text = VEC_LITERAL.sub(lambda m: "make_%s(" % m.group(1), text)
+    text = rewrite_literals(text)
     text = text.replace("#ifdef __cplusplus", "#ifdef MCRT_REF_HOST_BRANCH")
     text = text.replace("#include <../RadeonRays/src/kernels/CL/common.cl>", '#include "common.cl"')
     return text

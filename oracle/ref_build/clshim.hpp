@@ -6,7 +6,7 @@
 // work-item per function call.  Nothing of the reference is copied here: the
 // sources are read from /root/reference at build time, pushed through the
 // mechanical rewrite in cl2cpp.py (vector literals `(float3)(..)` ->
-// `make_float3(..)`, the `__cplusplus` branch of kernel_data.h switched off) and
+// `float3{..}`, evaluated left to right, the `__cplusplus` branch of kernel_data.h switched off) and
 // only ever written to oracle/_ref/ (git-ignored).
 //
 // Floating-point contract of this build: strict IEEE fp32, no
@@ -71,7 +71,8 @@ struct alignas(8) float2 {
         Swz2<float2, 0, 1, 2> xy;
     };
     float2() : x(0.f), y(0.f) {}
-    float2(float a, float b) : x(a), y(b) {}
+    template <typename A> explicit float2(A a) : x((float)a), y((float)a) {}
+    template <typename A, typename B> float2(A a, B b) : x((float)a), y((float)b) {}
     float2(const float2& o) : x(o.x), y(o.y) {}
     float2& operator=(const float2& o) { x = o.x; y = o.y; return *this; }
     float2& operator=(float a) { x = a; y = a; return *this; } /* OpenCL scalar widening (matrix.cl:35) */
@@ -87,7 +88,10 @@ struct alignas(16) float3 {
         Swz3<float3, 0, 1, 2> xyz;
     };
     float3() : x(0.f), y(0.f), z(0.f), _w(0.f) {}
-    float3(float a, float b, float c) : x(a), y(b), z(c), _w(0.f) {}
+    explicit float3(float a) : x(a), y(a), z(a), _w(0.f) {}
+    explicit float3(double a) : x((float)a), y((float)a), z((float)a), _w(0.f) {}
+    explicit float3(int a) : x((float)a), y((float)a), z((float)a), _w(0.f) {}
+    template <typename A, typename B, typename C> float3(A a, B b, C c) : x((float)a), y((float)b), z((float)c), _w(0.f) {}
     float3(const float3& o) : x(o.x), y(o.y), z(o.z), _w(0.f) {}
     float3& operator=(const float3& o) { x = o.x; y = o.y; z = o.z; return *this; }
 };
@@ -100,7 +104,9 @@ struct alignas(16) float4 {
         Swz3<float3, 0, 1, 2> xyz;
     };
     float4() : x(0.f), y(0.f), z(0.f), w(0.f) {}
-    float4(float a, float b, float c, float d) : x(a), y(b), z(c), w(d) {}
+    explicit float4(float a) : x(a), y(a), z(a), w(a) {}
+    template <typename A, typename B, typename C, typename D> float4(A a, B b, C c, D d) : x((float)a), y((float)b), z((float)c), w((float)d) {}
+    float4(const float3& v, float d);
     float4(const float4& o) : x(o.x), y(o.y), z(o.z), w(o.w) {}
     float4& operator=(const float4& o) { x = o.x; y = o.y; z = o.z; w = o.w; return *this; }
 };
@@ -108,21 +114,24 @@ struct alignas(16) float4 {
 struct alignas(8) int2 {
     int x, y;
     int2() : x(0), y(0) {}
-    int2(int a, int b) : x(a), y(b) {}
+    template <typename A> explicit int2(A a) : x((int)a), y((int)a) {}
+    template <typename A, typename B> int2(A a, B b) : x((int)a), y((int)b) {}
 };
 struct alignas(8) uint2 {
     uint x, y;
     uint2() : x(0), y(0) {}
-    uint2(uint a, uint b) : x(a), y(b) {}
+    template <typename A, typename B> uint2(A a, B b) : x((uint)a), y((uint)b) {}
 };
 struct alignas(16) int3 {
     int x, y, z, _w;
     int3() : x(0), y(0), z(0), _w(0) {}
-    int3(int a, int b, int c) : x(a), y(b), z(c), _w(0) {}
+    template <typename A, typename B, typename C> int3(A a, B b, C c) : x((int)a), y((int)b), z((int)c), _w(0) {}
 };
 struct alignas(4) uchar4 {
     uchar x, y, z, w;
 };
+
+inline float4::float4(const float3& v, float d) : x(v.x), y(v.y), z(v.z), w(d) {}
 
 static_assert(sizeof(float2) == 8 && sizeof(float3) == 16 && sizeof(float4) == 16, "OpenCL vector sizes");
 static_assert(sizeof(int2) == 8 && sizeof(uchar4) == 4, "OpenCL vector sizes");
