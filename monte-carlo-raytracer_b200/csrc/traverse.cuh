@@ -120,7 +120,9 @@ struct Traverser {
         s.idx = safe_inv(r.dx);
         s.idy = safe_inv(r.dy);
         s.idz = safe_inv(r.dz);
-        const uint32_t oct = (r.dx < 0.f ? 1u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 4u : 0u);
+        // signs are taken from the inverse direction so that d = -0.0f (idir = -1e20) is handled as
+        // "negative" consistently by the octant order and by the near/far plane selection below
+        const uint32_t oct = (s.idx < 0.f ? 1u : 0u) | (s.idy < 0.f ? 2u : 0u) | (s.idz < 0.f ? 4u : 0u);
         s.octinv4 = (7u - oct) * 0x01010101u;
         s.closest = r.tmax;
         s.best_tri = -1;
@@ -173,9 +175,9 @@ struct Traverser {
                     const uint32_t qlx = half == 0 ? n2.x : n2.y, qhx = half == 0 ? n3.z : n3.w;
                     const uint32_t qly = half == 0 ? n2.z : n2.w, qhy = half == 0 ? n4.x : n4.y;
                     const uint32_t qlz = half == 0 ? n3.x : n3.y, qhz = half == 0 ? n4.z : n4.w;
-                    const uint32_t xmin = r.dx < 0.f ? qhx : qlx, xmax = r.dx < 0.f ? qlx : qhx;
-                    const uint32_t ymin = r.dy < 0.f ? qhy : qly, ymax = r.dy < 0.f ? qly : qhy;
-                    const uint32_t zmin = r.dz < 0.f ? qhz : qlz, zmax = r.dz < 0.f ? qlz : qhz;
+                    const uint32_t xmin = s.idx < 0.f ? qhx : qlx, xmax = s.idx < 0.f ? qlx : qhx;
+                    const uint32_t ymin = s.idy < 0.f ? qhy : qly, ymax = s.idy < 0.f ? qly : qhy;
+                    const uint32_t zmin = s.idz < 0.f ? qhz : qlz, zmax = s.idz < 0.f ? qlz : qhz;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const float tminx = __fmaf_rn((float)extract_byte(xmin, j), aix, orx);

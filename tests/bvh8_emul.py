@@ -82,7 +82,7 @@ def closest_hit(nodes, tris, ray_o, ray_d, tmax, tri_test):
     o = np.asarray(ray_o, f32)
     d = np.asarray(ray_d, f32)
     inv = [_safe_inv(d[a]) for a in range(3)]
-    octant = (1 if d[0] < 0 else 0) | (2 if d[1] < 0 else 0) | (4 if d[2] < 0 else 0)
+    octant = (1 if inv[0] < 0 else 0) | (2 if inv[1] < 0 else 0) | (4 if inv[2] < 0 else 0)
     octinv = 7 - octant
     closest, best, best_key = f32(tmax), -1, None
     visited = 0
@@ -116,7 +116,7 @@ def closest_hit(nodes, tris, ray_o, ray_d, tmax, tri_test):
                     sc = np.array([e[a] << 23], np.uint32).view(np.float32)[0]
                     ai = f32(sc * inv[a])
                     org = f32(f32(p[a] - o[a]) * inv[a])
-                    qa, qb = (q[3 + a][s], q[a][s]) if d[a] < 0 else (q[a][s], q[3 + a][s])
+                    qa, qb = (q[3 + a][s], q[a][s]) if inv[a] < 0 else (q[a][s], q[3 + a][s])
                     ta = f32(np.float64(f32(qa)) * np.float64(ai) + np.float64(org))   # fma
                     tb = f32(np.float64(f32(qb)) * np.float64(ai) + np.float64(org))
                     tmin, tmx = max(tmin, ta), min(tmx, tb)

@@ -267,3 +267,27 @@ def test_golden_intersections(api, cornell):
     res = port.compare_hits(api.QueryIntersectionHost(rays), ref_hits, tris, rays)
     assert res["bad"] == 0 and res["b_farther"] <= 1, res
     assert np.array_equal(api.QueryOcclusionHost(rays), g["occluded"])
+
+
+def test_axis_aligned_and_negative_zero_directions(api, cornell):
+    """Directions with exact +0.0 / -0.0 components (directional-light shadow rays are like this):
+    the sign used for the slab order must be the one used for the inverse direction."""
+    rr.attach_scene(api, cornell)
+    api.Commit()
+    tris = port.scene_triangles(cornell)
+    rng = np.random.RandomState(3)
+    n = 6000
+    lo, hi = cornell.world_bounds()
+    rays = random_rays(n, lo + 0.1, hi - 0.1, 17)
+    d = rays["d"][:, :3].copy()
+    axis = rng.randint(0, 3, n)
+    zero = np.where(rng.rand(n) < 0.5, np.float32(0.0), np.float32(-0.0))
+    d[np.arange(n), axis] = zero
+    second = (axis + 1 + rng.randint(0, 2, n)) % 3
+    twice = rng.rand(n) < 0.3
+    d[np.arange(n)[twice], second[twice]] = np.float32(-0.0)
+    d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-6)
+    rays["d"][:, :3] = d
+    res = port.compare_hits(api.QueryIntersectionHost(rays), port.intersect(tris, rays), tris, rays)
+    assert res["bad"] == 0 and res["tie_ok"] == 0, res
+    assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
