@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""bench.py -- paths/s and Mrays/s of the wavefront path tracer on the Sponza-class 1080p workload
+(BASELINE.json configs[2]: 262,144 triangles, textured + normal-mapped uber material, point +
+directional + area light, regular PT 1920x1080, depth 5), one step = one sample per pixel.
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one rank per GPU)
+  python bench.py --impl reference --gpus N --steps K ...   # the reference's kernels on the host cores
+
+Own arm, per rank: the scene is resident in HBM; a step is raygen -> (closest-hit trace -> shade/NEE
+-> shadow trace + radiance add) x depth -> accumulation, launched through the C ABI (include/ptb.h).
+N > 1 partitions by SAMPLE INDEX (rank r renders sample step*N + r of every pixel; weak scaling) and
+merges with one NCCL all-reduce of the float4 accumulation buffers per step.
+`value` is timed with CUDA events on the launching stream (max over ranks); `e2e` drives the same
+frame through the RenderPipeline mirror (camera built and uploaded on the host every step) and reads
+the merged image back into pinned host memory every step.
+
+The reference arm (and the `cpu_baseline` leg of the own arm) executes oracle/_ref -- the
+reference's own OpenCL-C kernels and Radeon Rays BVH2 builder compiled for the host -- and is the
+only place this file touches oracle/.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOAD = "sponza_class_262144tri_1920x1080_pt_depth5"
+METRIC, UNIT = "paths_per_sec", "paths/s"
+# SURVEY 8(d) algorithmic bytes at the reference's buffer layouts
+BYTES_CLOSEST_PER_RAY = 80       # 48 B RTRay read + 32 B RTIntersection write
+BYTES_SHADOW_PER_RAY = 52        # 48 B RTRay read + 4 B occlusion write
+BYTES_SHADE_PER_VERTEX = 948     # PathTracing + ShadowPass stage traffic per active pixel-bounce
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--depth", type=int, default=5)
+    ap.add_argument("--tex", type=int, default=1024, help="texture edge length (1024 = the named workload)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def config_of(args, n_gpus):
+    return {"workload": WORKLOAD, "triangles": 262144, "width": args.width, "height": args.height,
+            "max_depth": args.depth, "spp_per_step": 1, "textures": "74 x %d^2 RGBA8" % args.tex,
+            "lights": "point+directional+area", "partition": "sample-index x%d, 1 all-reduce/step" % n_gpus if n_gpus > 1 else "none",
+            "l2": "no flush: per-step working set (pixel state + textures) exceeds the 126 MB L2"}
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        fd, self.path = tempfile.mkstemp(suffix=".csv")
+        os.close(fd)
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        with open(self.path) as f:
+            for line in f:
+                p = [x.strip() for x in line.split(",")]
+                if len(p) < 7:
+                    continue
+                try:
+                    sm.append(float(p[0]))
+                    mx.append(float(p[1]))
+                except ValueError:
+                    continue
+                for name, v in zip(self.NAMES, p[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ----------------------------------------------------------------------------- reference on the host
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_sample_size(args):
+    """Bounded sample: every third pixel of the 1080p frame in x and y (same camera, scene, depth)."""
+    return max(16, args.width // 3), max(9, args.height // 3)
+
+
+class HostReference:
+    """The reference's kernels (oracle/_ref) on the host cores: BVH2 build + the pass loops."""
+
+    def __init__(self, scene, args):
+        from oracle import ref
+        self.fast = ref.available(True)
+        if not ref.available(self.fast):
+            raise RuntimeError("oracle/_ref is not built (make -C oracle ref needs /root/reference)")
+        from mcrt_b200 import camera
+        self.camera_mod = camera
+        self.scene, self.depth = scene, args.depth
+        self.w, self.h = cpu_sample_size(args)
+        self.oracle = ref.RefOracle(self.fast)
+        t = time.perf_counter()
+        self.nodes = self.oracle.build_scene_bvh(scene)
+        self.build_s = time.perf_counter() - t
+        self.tracer = ref.RefPathTracer(self.oracle, scene, self.nodes, self.w, self.h)
+        self.frame = 0
+
+    def step(self):
+        cam = self.camera_mod.make_camera(self.scene.camera, self.w, self.h, self.camera_mod.taa_pixel_offset(self.frame))
+        self.tracer.render_sample(cam, self.frame, self.depth)
+        self.frame += 1
+
+    def rays(self):
+        return self.tracer.rays_traced + self.tracer.shadow_rays_traced
+
+    def describe(self):
+        return ("%dx%d sub-sampling of the 1080p frame (1/9 of the pixels, same camera/scene/depth), 1 spp per step, "
+                "reference .cl kernels + RR BVH2 compiled %s, OpenMP" % (self.w, self.h, "-O3 AVX2" if self.fast else "-O2 strict fp32"))
+
+
+def run_cpu_baseline(scene, args, seconds):
+    hr = HostReference(scene, args)
+    hr.step()                                   # warm caches / page in
+    r0, frames, t0 = hr.rays(), 0, time.perf_counter()
+    while frames < 2 or time.perf_counter() - t0 < seconds:
+        hr.step()
+        frames += 1
+        if frames >= 64:
+            break
+    dt = time.perf_counter() - t0
+    paths = frames * hr.w * hr.h
+    return {"value": paths / dt, "unit": UNIT, "cores": host_threads(), "kind": "reference",
+            "sample": hr.describe() + ", %d steps in %.1f s" % (frames, dt),
+            "mrays_per_s": (hr.rays() - r0) / dt / 1e6, "bvh_build_s": hr.build_s}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0                                # the host cores are one pool: rank 0 alone measures
+    import mcrt_b200  # noqa: F401
+    from mcrt_b200 import scene_library
+    scene = scene_library.sponza_class(args.tex)
+    hr = HostReference(scene, args)
+    for _ in range(max(args.warmup, 1)):
+        hr.step()
+    r0, t0 = hr.rays(), time.perf_counter()
+    for _ in range(args.steps):
+        hr.step()
+    dt = time.perf_counter() - t0
+    value = args.steps * hr.w * hr.h / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_of(args, args.gpus), "mrays_per_s": (hr.rays() - r0) / dt / 1e6,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": host_threads(), "kind": "reference",
+                             "sample": hr.describe(), "bvh_build_s": hr.build_s},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------- this repo's CUDA path
+class DevView:
+    """__cuda_array_interface__ over a raw device pointer, so torch can address a ptb buffer."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+def own_arm(args):
+    import torch
+    import torch.distributed as dist
+    import mcrt_b200  # noqa: F401
+    from mcrt_b200 import rr, pt, camera, scene_library
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    scene = scene_library.sponza_class(args.tex)
+    W, H, depth, P = args.width, args.height, args.depth, args.width * args.height
+    stream = torch.cuda.Stream(device=dev)
+    api = rr.IntersectionApi.Create(local, cuda_stream=stream.cuda_stream)
+    t0 = time.perf_counter()
+    pl = pt.make_pt_pipeline(api, scene, W, H, depth)          # attaches shapes, Commit() builds the BVH, uploads
+    setup_s = time.perf_counter() - t0
+    stats = api.GetStats()
+    pl.ensure_size()
+    pt_pass = pl.passes[0]
+    lib, h = pt._lib(), pl.scene._h
+    fprops = pl.GI.filter_props()
+
+    # merged-image plumbing for N > 1: [weighted radiance (4P) | filter weights (P)] staged and all-reduced
+    wr_ptr, wr_bytes = pl.device_buffer("WeightedRadianceBuffer")
+    fw_ptr, fw_bytes = pl.device_buffer("FilterWeightsBuffer")
+    img_ptr, img_bytes = pl.device_buffer("NextFrameImageCL")
+    t_wr = torch.as_tensor(DevView(wr_ptr, wr_bytes), device=dev)
+    t_fw = torch.as_tensor(DevView(fw_ptr, fw_bytes), device=dev)
+    t_img = torch.as_tensor(DevView(img_ptr, img_bytes), device=dev)
+    stage = torch.empty(5 * P, dtype=torch.float32, device=dev) if world > 1 else None
+    host_img = torch.empty(4 * P, dtype=torch.float32, pin_memory=True)
+    host_np = host_img.numpy()
+
+    def cam_for(frame):
+        off = camera.taa_pixel_offset(frame, pl.GI.filterRadius, True)
+        return camera.make_camera(scene.camera, W, H, off), off
+
+    def merge():
+        """One NCCL all-reduce of the accumulation buffers; every rank ends with the merged image."""
+        stage[:4 * P].copy_(t_wr)
+        stage[4 * P:].copy_(t_fw)
+        dist.all_reduce(stage)
+        torch.div(stage[:4 * P].view(P, 4), stage[4 * P:].view(P, 1), out=t_img.view(P, 4))
+
+    def device_step(frame, cam, off):
+        """C-ABI calls only; the camera struct was built before the timed region."""
+        fprops.pixel_offset[0], fprops.pixel_offset[1] = off
+        pt._check(lib.ptb_set_camera(h, cam.ctypes.data_as(ctypes.c_void_p)))
+        pt._check(lib.ptb_pt_render_sample(h, frame, depth))
+        pt._check(lib.ptb_accumulate(h, frame, ctypes.byref(fprops)))
+        if world > 1:
+            merge()
+
+    def e2e_step(frame):
+        """The call a user makes: pipeline.update() (host camera build + upload) and the image on the host."""
+        pt_pass.m_frameIndex = frame
+        pl.update()
+        if world > 1:
+            merge()
+        pt._check(lib.ptb_read_buffer(h, b"NextFrameImageCL", host_np.ctypes.data_as(ctypes.c_void_p), host_np.nbytes))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    K, Wm = args.steps, max(args.warmup, 3)
+    frames = [(s * world + rank) for s in range(Wm + K)]
+    cams = [cam_for(f) for f in frames]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    with torch.cuda.stream(stream):
+        # ---------------- device-resident timing
+        for s in range(Wm):
+            device_step(frames[s], *cams[s])
+        barrier()
+        pl.reset_counters()
+        pl.profile_enable(True)
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        barrier()
+        ev0.record(stream)
+        for s in range(Wm, Wm + K):
+            device_step(frames[s], *cams[s])
+        ev1.record(stream)
+        barrier()
+        ms = max_over_ranks(ev0.elapsed_time(ev1))
+        clocks = sampler.stop() if rank == 0 else None
+        cnt = pl.counters()
+        prof = pl.profile_collect()
+        pl.profile_enable(False)
+
+        # ---------------- end to end through the pipeline mirror, image read back every step
+        pt._check(lib.ptb_reset_accumulation(h))
+        for s in range(Wm):
+            e2e_step(frames[s])
+        barrier()
+        ev0.record(stream)
+        for s in range(Wm, Wm + K):
+            e2e_step(frames[s])
+        ev1.record(stream)
+        barrier()
+        ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
+        img_mean = float(host_np.reshape(-1, 4)[:, :3].mean())
+
+    paths_total = sum_over_ranks(float(cnt["samples"]))
+    closest_total = sum_over_ranks(float(cnt["closest_rays"]))
+    shadow_total = sum_over_ranks(float(cnt["shadow_rays"]))
+    launches_total = int(sum_over_ranks(float(cnt["kernel_launches"])))
+    value = paths_total / (ms * 1e-3)
+    e2e_value = paths_total / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        peaks, peak_src = {}, "fallback (B200_PROFILING.md)"
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+            peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        nb = max(prof["bounces"], 1)
+        stages = {
+            "k_trace_closest": (prof["closest_ms"], cnt["closest_rays"] * BYTES_CLOSEST_PER_RAY),
+            "k_shade": (prof["shade_ms"], cnt["shaded_vertices"] * BYTES_SHADE_PER_VERTEX),
+            "k_trace_shadow": (prof["shadow_ms"], cnt["shadow_rays"] * BYTES_SHADOW_PER_RAY),
+        }
+        top = max(stages, key=lambda k: stages[k][0])
+        top_ms, top_bytes = stages[top]
+        achieved = top_bytes / max(top_ms * 1e-3, 1e-12) / 1e9
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                traffic = json.load(f).get(top)
+        except OSError:
+            pass
+        roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                    "launches": nb, "avg_launch_ms": top_ms / nb, "algorithmic_bytes_per_launch": top_bytes / nb,
+                    "stage_ms_per_step": {k: v[0] / K for k, v in stages.items()},
+                    "stage_share_of_step": {k: v[0] / max(ms, 1e-9) for k, v in stages.items()},
+                    "rays_per_s": {"closest": cnt["closest_rays"] / max(prof["closest_ms"] * 1e-3, 1e-12),
+                                   "shadow": cnt["shadow_rays"] / max(prof["shadow_ms"] * 1e-3, 1e-12)}}
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            cpu = run_cpu_baseline(scene, args, args.cpu_seconds)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "config": config_of(args, world),
+                "mrays_per_s": (closest_total + shadow_total) / (ms * 1e-3) / 1e6,
+                "rays_per_path": (closest_total + shadow_total) / max(paths_total, 1.0),
+                "roofline": roofline, "cpu_baseline": cpu,
+                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / K, "h2d_bytes_per_step": 176,
+                        "d2h_bytes_per_step": int(host_np.nbytes), "image_mean": img_mean},
+                "gpu_launches": launches_total, "clocks": clocks,
+                "bvh": {"build_and_upload_s": setup_s, "nodes": int(stats.get("num_nodes", 0)) if isinstance(stats, dict) else None}}
+        print(json.dumps(line), flush=True)
+    pl.scene.destroy()
+    rr.IntersectionApi.Delete(api)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    return own_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

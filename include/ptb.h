@@ -99,6 +99,14 @@ int ptb_pt_render_sample(ptb_context* ctx, int frame, int max_depth);
 /* Same for RTBDPTPass::update. */
 int ptb_bdpt_render_sample(ptb_context* ctx, int frame, int max_depth);
 
+/* Per-stage device timing of the fused wavefront (no reference counterpart; measurement only).
+ * While enabled every bounce records CUDA events on the context's stream around the closest-hit
+ * trace, the shade stage and the shadow trace; collect() synchronises, returns the summed
+ * milliseconds of each stage and the number of bounces measured, and rearms the recorder. */
+int ptb_profile_enable(ptb_context* ctx, int on);
+int ptb_profile_collect(ptb_context* ctx, double* ms_closest, double* ms_shade, double* ms_shadow,
+                        int64_t* launches_each);
+
 /* ReconstructionPass (reconstruction.cl:6-60): clamp, filter weight of the frame's pixel offset,
  * running weighted mean into "NextFrameImageCL"; frame 0 restarts the mean (reconstruction.cl:47-57). */
 int ptb_accumulate(ptb_context* ctx, int frame, const ptb_filter_props* filter);

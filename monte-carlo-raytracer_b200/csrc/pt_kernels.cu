@@ -253,7 +253,7 @@ static int sm_count() {
 }
 
 int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int frame, int max_depth,
-                     cudaStream_t stream, cudaError_t* err) {
+                     cudaStream_t stream, cudaError_t* err, StageTimer* timer) {
     int launches = 0;
     *err = cudaSuccess;
     if (n_pixels <= 0) return 0;
@@ -266,9 +266,13 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         int cur = 0;
         for (int b = 0; b < max_depth; ++b) {
             k_bounce_ctl<<<1, 32, 0, stream>>>(s.cnt, s.stats, cur, b == 0, n_pixels);
+            if (timer) timer->mark(stream);
             k_trace_closest<<<trace_blocks, 128, 0, stream>>>(s, cur);
+            if (timer) timer->mark(stream);
             k_shade<<<shade_blocks, 128, 0, stream>>>(s, cur, frame, b, max_depth);
+            if (timer) timer->mark(stream);
             k_trace_shadow<<<trace_blocks, 128, 0, stream>>>(s);
+            if (timer) timer->mark(stream);
             launches += 4;
             cur = 1 - cur;
         }

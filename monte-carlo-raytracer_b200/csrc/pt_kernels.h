@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <vector>
+
 namespace mcrt {
 
 struct SceneDev;  // opaque here; defined in pt_kernels.cu as mcrt::Scene
@@ -51,10 +53,32 @@ struct PtState {
     float4* image;         // "NextFrameImageCL"
 };
 
+// Optional per-stage timing: every mark() records a pooled CUDA event on the launching stream; the
+// caller reads the gaps after a synchronise (ptb_profile_collect).  Marks per bounce: before the
+// closest-hit trace, before shade, before the shadow trace, after the shadow trace.
+struct StageTimer {
+    std::vector<cudaEvent_t> events;   // pool, grown on demand
+    size_t used = 0;
+    void mark(cudaStream_t stream) {
+        if (used == events.size()) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            events.push_back(e);
+        }
+        cudaEventRecord(events[used++], stream);
+    }
+    void reset() { used = 0; }
+    void destroy() {
+        for (cudaEvent_t e : events) cudaEventDestroy(e);
+        events.clear();
+        used = 0;
+    }
+};
+
 // One frame of the fused wavefront path tracer.  `pixels` (device, may be NULL = identity) lists the
 // n_pixels global pixel indices this context owns.  Returns the number of kernels launched.
 int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int frame, int max_depth,
-                     cudaStream_t stream, cudaError_t* err);
+                     cudaStream_t stream, cudaError_t* err, StageTimer* timer = nullptr);
 
 // Stage-wise, reference layouts.
 cudaError_t launch_generate_primary_rays(const PtState& s, cudaStream_t stream);

@@ -51,6 +51,8 @@ struct ptb_context {
     int n_pixels = 0;
     int bdpt_depth = -1;
     int64_t launches = 0;
+    bool profiling = false;
+    mcrt::StageTimer timer;
     ptb_context() {
         std::memset(&st, 0, sizeof(st));
         std::memset(&bd, 0, sizeof(bd));
@@ -190,6 +192,7 @@ int ptb_destroy(ptb_context* c) {
         if (it != c->named.end() && it->second.p) cudaFree(it->second.p);
     }
     if (c->d_pixels) cudaFree(c->d_pixels);
+    c->timer.destroy();
     delete c;
     return 0;
 }
@@ -343,8 +346,42 @@ int ptb_pt_render_sample(ptb_context* c, int frame, int max_depth) {
     if (rc) return rc;
     if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
     cudaError_t e = cudaSuccess;
-    c->launches += mcrt::launch_pt_sample(c->st, c->d_pixels, c->n_pixels, frame, max_depth, c->stream, &e);
+    c->launches += mcrt::launch_pt_sample(c->st, c->d_pixels, c->n_pixels, frame, max_depth, c->stream, &e,
+                                          c->profiling ? &c->timer : nullptr);
     if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("path tracer launch: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+int ptb_profile_enable(ptb_context* c, int on) {
+    if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    c->profiling = on != 0;
+    c->timer.reset();
+    return 0;
+}
+
+int ptb_profile_collect(ptb_context* c, double* ms_closest, double* ms_shade, double* ms_shadow, int64_t* launches_each) {
+    if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    double acc[3] = {0.0, 0.0, 0.0};
+    int64_t n = 0;
+    for (size_t i = 0; i + 3 < c->timer.used; i += 4) {       // 4 marks per bounce (pt_kernels.h)
+        for (int k = 0; k < 3; ++k) {
+            float ms = 0.0f;
+            PTB_CUDA(cudaEventElapsedTime(&ms, c->timer.events[i + k], c->timer.events[i + k + 1]));
+            acc[k] += ms;
+        }
+        ++n;
+    }
+    if (ms_closest) *ms_closest = acc[0];
+    if (ms_shade) *ms_shade = acc[1];
+    if (ms_shadow) *ms_shadow = acc[2];
+    if (launches_each) *launches_each = n;
+    c->timer.reset();
     return 0;
 }
 

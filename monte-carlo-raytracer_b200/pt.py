@@ -62,6 +62,9 @@ def _lib():
             "ptb_get_buffer": [vp, ctypes.c_char_p, pp, ctypes.POINTER(sz)],
             "ptb_read_buffer": [vp, ctypes.c_char_p, vp, sz], "ptb_synchronize": [vp],
             "ptb_get_counters": [vp, ctypes.POINTER(PtbCounters)], "ptb_reset_counters": [vp],
+            "ptb_profile_enable": [vp, ctypes.c_int],
+            "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
+                                    ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
         }
         for name, args in sig.items():
             fn = getattr(lib, name)
@@ -219,6 +222,15 @@ class RenderPipeline:
     def synchronize(self):
         _check(_lib().ptb_synchronize(self.scene._h))
 
+    def profile_enable(self, on=True):
+        _check(_lib().ptb_profile_enable(self.scene._h, int(bool(on))))
+
+    def profile_collect(self):
+        """Summed device milliseconds of the three wavefront stages since the last collect."""
+        a, b, c, n = ctypes.c_double(), ctypes.c_double(), ctypes.c_double(), ctypes.c_int64()
+        _check(_lib().ptb_profile_collect(self.scene._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c), ctypes.byref(n)))
+        return {"closest_ms": a.value, "shade_ms": b.value, "shadow_ms": c.value, "bounces": n.value}
+
     def set_partition(self, part, num_parts):
         _check(_lib().ptb_set_partition(self.scene._h, int(part), int(num_parts)))
 
@@ -330,3 +342,20 @@ def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=T
     else:
         pl.addRenderPasses(RTPrimaryRaysPass(), RTPathTracingPass(False), RTReconstructionPass())
     return pl
+
+
+def smoke_check(api, scene, width=64, height=64, depth=3):
+    """One small frame of the fused wavefront on the current device; finite, non-black, and the
+    stage-wise dispatch over the reference layouts reproduces it bit for bit."""
+    out = []
+    for fused in (True, False):
+        a = api if fused else rr.IntersectionApi.Create(0)
+        pl = make_pt_pipeline(a, scene, width, height, depth, fused=fused)
+        pl.update()
+        out.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+        pl.scene.destroy()
+        if not fused:
+            rr.IntersectionApi.Delete(a)
+    assert np.isfinite(out[0]).all() and out[0][:, :3].sum() > 0.0
+    assert np.array_equal(out[0].view(np.uint32)[:, :3], out[1].view(np.uint32)[:, :3])
+    return out[0]

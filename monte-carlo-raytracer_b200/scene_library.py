@@ -189,3 +189,156 @@ def traversal_bench_scene(nq=707) -> Scene:
     sc = dragon_class(nq, nq)
     sc.name = "traversal_1M"
     return sc
+
+
+# ----------------------------------------------------------------------------- C3: Sponza-class atrium
+def lattice_noise(size, seed, octaves=4, base=8):
+    """Tileable value noise in [0,1] on a size x size image: per octave a (base*2^o)^2 lattice of
+    wang-hashed values, bilinearly interpolated with wrap-around (so REPEAT wrapping is seamless)."""
+    out = np.zeros((size, size), np.float64)
+    amp, tot = 1.0, 0.0
+    ys, xs = np.meshgrid(np.arange(size), np.arange(size), indexing="ij")
+    for o in range(octaves):
+        n = base << o
+        gy, gx = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+        lat = hash01(gx, gy, seed * 131 + o)
+        fx, fy = xs * (n / size), ys * (n / size)
+        ix, iy = np.floor(fx).astype(np.int64), np.floor(fy).astype(np.int64)
+        tx, ty = fx - ix, fy - iy
+        tx, ty = tx * tx * (3 - 2 * tx), ty * ty * (3 - 2 * ty)
+        ix1, iy1 = (ix + 1) % n, (iy + 1) % n
+        out += amp * ((lat[iy, ix] * (1 - tx) + lat[iy, ix1] * tx) * (1 - ty) +
+                      (lat[iy1, ix] * (1 - tx) + lat[iy1, ix1] * tx) * ty)
+        tot += amp
+        amp *= 0.5
+    return out / tot
+
+
+def make_texture_set(tex_id_base, size, tint, with_opacity=False):
+    """Diffuse (RGBA8, alpha 255), specular and normal-map textures of one material, plus an optional
+    alpha-mask texture; returns a list of (size,size,4) uint8 arrays (level 0 only: the kernels never
+    sample another level, textures.cl:204-209)."""
+    h = lattice_noise(size, 3000 + tex_id_base, 5, 4)
+    g = lattice_noise(size, 3001 + tex_id_base, 3, 16)
+    tint = np.asarray(tint, np.float64)
+    diff = np.empty((size, size, 4), np.uint8)
+    diff[..., :3] = np.clip((0.35 + 0.65 * h[..., None]) * tint * (0.85 + 0.15 * g[..., None]) * 255.0, 0, 255)
+    diff[..., 3] = 255
+    spec = np.empty((size, size, 4), np.uint8)
+    spec[..., :3] = np.clip((0.2 + 0.8 * g[..., None]) * 255.0, 0, 255)
+    spec[..., 3] = 255
+    # normal map from the height field by central differences (wrap), encoded 0.5 * n + 0.5
+    dx = (np.roll(h, -1, 1) - np.roll(h, 1, 1)) * (size / 64.0)
+    dy = (np.roll(h, -1, 0) - np.roll(h, 1, 0)) * (size / 64.0)
+    n = np.stack([-dx, -dy, np.ones_like(h)], -1)
+    n /= np.linalg.norm(n, axis=-1, keepdims=True)
+    nm = np.empty((size, size, 4), np.uint8)
+    nm[..., :3] = np.clip((0.5 * n + 0.5) * 255.0 + 0.5, 0, 255)
+    nm[..., 3] = 255
+    out = [diff, spec, nm]
+    if with_opacity:
+        m = lattice_noise(size, 3002 + tex_id_base, 2, 8)
+        op = np.empty((size, size, 4), np.uint8)
+        op[..., :3] = np.where(m[..., None] > 0.35, 255, 0)
+        op[..., 3] = 255
+        out.append(op)
+    return out
+
+
+def cylinder_mesh(name, cx, cz, radius, y0, y1, nseg, nring, material, flutes=12) -> Mesh:
+    th = np.linspace(0.0, 2 * np.pi, nseg + 1)
+    ys = np.linspace(y0, y1, nring + 1)
+    T, Y = np.meshgrid(th, ys, indexing="ij")
+    r = radius * (1.0 + 0.04 * np.cos(flutes * T)) * (1.0 + 0.08 * np.exp(-((Y - y0) / 0.4) ** 2) +
+                                                      0.08 * np.exp(-((y1 - Y) / 0.4) ** 2))
+    P = np.stack([cx + r * np.cos(T), Y, cz + r * np.sin(T)], -1)
+    N = np.stack([np.cos(T), np.zeros_like(T), np.sin(T)], -1)
+    UV = np.stack([T / (2 * np.pi) * 2.0, (Y - y0) / (y1 - y0) * 4.0], -1)
+    m = grid_mesh(name, P, N, UV, material)
+    m.indices = m.indices[:, [0, 2, 1]].copy()     # geometric normal outward, like the shading normal
+    return m
+
+
+def plane_grid(name, origin, eu, ev, nu, nv, material, uv_scale, normal, height_seed=None, amp=0.0) -> Mesh:
+    """Planar nu x nv-quad grid spanned by eu, ev from origin; optional noise displacement along normal."""
+    a = np.linspace(0.0, 1.0, nu + 1)
+    b = np.linspace(0.0, 1.0, nv + 1)
+    A, B = np.meshgrid(a, b, indexing="ij")
+    origin, eu, ev, normal = (np.asarray(v, np.float64) for v in (origin, eu, ev, normal))
+    P = origin + A[..., None] * eu + B[..., None] * ev
+    if height_seed is not None:
+        hgt = value_noise(A * 12.0, B * 8.0, height_seed, 4) * amp
+        P = P + hgt[..., None] * normal
+    N = np.broadcast_to(normal, P.shape).copy()
+    UV = np.stack([A * uv_scale[0], B * uv_scale[1]], -1)
+    m = grid_mesh(name, P, N, UV, material)
+    p, i = m.positions, m.indices
+    gn = np.cross(p[i[0, 0]] - p[i[0, 2]], p[i[0, 1]] - p[i[0, 2]])
+    if np.dot(gn, normal) < 0:
+        m.indices = m.indices[:, [0, 2, 1]].copy()
+    return m
+
+
+def merge_meshes(name, meshes, material) -> Mesh:
+    pos, nrm, uvs, idx, base = [], [], [], [], 0
+    for m in meshes:
+        pos.append(m.positions); nrm.append(m.normals); uvs.append(m.uvs); idx.append(m.indices + base)
+        base += m.positions.shape[0]
+    return Mesh(name, np.concatenate(pos), np.concatenate(nrm), np.concatenate(uvs), np.concatenate(idx), material)
+
+
+def sponza_class(tex_size=1024) -> Scene:
+    """C3: 262,144 triangles (2^18) in 24 shapes / 24 materials, every material with 1024^2 RGBA8
+    diffuse + specular + normal-map textures (2 also alpha-masked), point + directional + triangle-mesh
+    area light.  Hall 24 x 8 x 12 with an open central nave, two rows of 8 fluted columns."""
+    X0, X1, Z0, Z1, H = -12.0, 12.0, -6.0, 6.0, 8.0
+    tints = [(0.80, 0.72, 0.60), (0.70, 0.70, 0.72), (0.75, 0.62, 0.50), (0.62, 0.68, 0.60)]
+    meshes = []
+    # 0 floor, 1 aisle ceilings (two strips, nave open to the sky), 2-3 long walls, 4-5 end walls, 6 relief
+    meshes.append(plane_grid("floor", (X0, 0, Z0), (X1 - X0, 0, 0), (0, 0, Z1 - Z0), 128, 128, 0, (12, 6), (0, 1, 0)))
+    c0 = plane_grid("c0", (X0, H, Z0), (X1 - X0, 0, 0), (0, 0, 2.5), 128, 64, 1, (12, 2), (0, -1, 0))
+    c1 = plane_grid("c1", (X0, H, Z1 - 2.5), (X1 - X0, 0, 0), (0, 0, 2.5), 128, 64, 1, (12, 2), (0, -1, 0))
+    meshes.append(merge_meshes("ceiling", [c0, c1], 1))
+    meshes.append(plane_grid("wallN", (X0, 0, Z1), (X1 - X0, 0, 0), (0, H, 0), 128, 64, 2, (12, 4), (0, 0, -1)))
+    meshes.append(plane_grid("wallS", (X0, 0, Z0), (X1 - X0, 0, 0), (0, H, 0), 128, 64, 3, (12, 4), (0, 0, 1)))
+    meshes.append(plane_grid("wallW", (X0, 0, Z0), (0, 0, Z1 - Z0), (0, H, 0), 128, 64, 4, (6, 4), (1, 0, 0)))
+    meshes.append(plane_grid("wallE", (X1, 0, Z0), (0, 0, Z1 - Z0), (0, H, 0), 128, 64, 5, (6, 4), (-1, 0, 0)))
+    meshes.append(plane_grid("relief", (X0 + 2, 0.5, Z1 - 0.35), (X1 - X0 - 4, 0, 0), (0, 5.0, 0), 217, 151, 6, (8, 3),
+                             (0, 0, -1), height_seed=33, amp=0.3))
+    k = 7
+    for row, cz in enumerate((-3.5, 3.5)):
+        for j in range(8):
+            cx = X0 + 1.5 + j * 3.0
+            meshes.append(cylinder_mesh("column%d_%d" % (row, j), cx, cz, 0.42, 0.0, H, 64, 32, k))
+            k += 1
+    # 23: emissive ceiling panel under the north aisle ceiling (2 triangles), facing down
+    meshes.append(plane_grid("panel", (-2.0, H - 0.05, Z1 - 2.2), (4.0, 0, 0), (0, 0, 1.6), 1, 1, 23, (1, 1), (0, -1, 0)))
+    assert len(meshes) == 24
+
+    mats, tex_images = [], []
+    for m in range(24):
+        mat = make_material(kd=(1, 1, 1), ks=(0.25, 0.25, 0.25), roughness=(np.sqrt(2.0 / 22.0),) * 2)
+        masked = m in (6, 9)
+        imgs = make_texture_set(10 * m, tex_size, tints[m % 4], with_opacity=masked)
+        base = len(tex_images)
+        tex_images += imgs
+        mat["uber_diffuseTexId"], mat["uber_glossyTexId"], mat["uber_normalMapId"] = base, base + 1, base + 2
+        if masked:
+            mat["uber_opacityTexId"] = base + 3
+        mats.append(mat)
+    textures = np.zeros(len(tex_images), dtype=L.TEXDESC)
+    off = 0
+    for i, im in enumerate(tex_images):
+        textures[i]["width"], textures[i]["height"] = im.shape[1], im.shape[0]
+        textures[i]["numMipLevels"], textures[i]["format"], textures[i]["wrap"] = 1, L.TEX_FORMAT_RGBA8, L.TEX_WRAP_REPEAT
+        textures[i]["memOffset"] = off
+        off += im.size
+    texdata = np.concatenate([im.reshape(-1) for im in tex_images])
+
+    sc = Scene("sponza_class", meshes, np.concatenate(mats), np.zeros(0, dtype=L.LIGHT),
+               CameraSpec(position=(-10.6, 2.6, 0.4), euler_deg=(-4.0, 84.0, 0.0)), textures=textures, texdata=texdata)
+    lo, hi = sc.world_bounds()
+    sc.lights = np.concatenate([point_light((0.0, 5.0, 0.0), (30.0, 30.0, 30.0)),
+                                directional_light((72.0, 0.0, 0.0), (40.0, 40.0, 40.0), lo, hi),
+                                tri_mesh_light(23, (15.0, 15.0, 15.0), mesh_area(meshes[23]))])
+    return sc.finalize()

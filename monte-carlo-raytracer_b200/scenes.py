@@ -51,7 +51,7 @@ def rand_float(state):
 def hash01(ix, iy, seed):
     """Uniform [0,1) from two integer lattice coordinates and a seed."""
     h = wang_hash(np.asarray(ix, np.uint32) * np.uint32(73856093) ^ np.asarray(iy, np.uint32) * np.uint32(19349663)
-                  ^ np.uint32(seed) * np.uint32(83492791))
+                  ^ np.uint32((int(seed) * 83492791) & 0xFFFFFFFF))
     return (h >> np.uint32(8)).astype(np.float64) / float(1 << 24)
 
 

@@ -160,3 +160,17 @@ def test_tile_partition_union_is_bit_identical(api, cornell):
             rr.IntersectionApi.Delete(a2)
     merged = parts[0] + parts[1]
     assert np.array_equal(merged.view(np.uint32)[:, :3], full[0].view(np.uint32)[:, :3])
+
+
+def test_textured_normal_mapped_scene_vs_reference(api):
+    """C3 geometry (262,144 triangles, 24 textured + normal-mapped materials, two alpha-masked; point +
+    directional + triangle-mesh area light) with 64^2 textures: texture fetch, normal mapping, opacity
+    lobe and the three light types against the compiled reference."""
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    scene = scene_library.sponza_class(64)
+    w, h = 240, 136
+    got, _, _ = render_frames(api, scene, w, h, 5, 2)
+    want, _ = ref_frames(scene, w, h, 5, 2)
+    for f in range(2):
+        check_against(got[f], want[f], 0.97)
