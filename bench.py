@@ -44,7 +44,7 @@ BYTES_SHADE_PER_VERTEX = 948     # PathTracing + ShadowPass stage traffic per ac
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--width", type=int, default=1920)
@@ -78,7 +78,7 @@ class ClockSampler:
         os.close(fd)
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "25"],
                                          stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except OSError:
             self.proc = None
@@ -92,23 +92,25 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        rows, reasons = [], set()
         with open(self.path) as f:
             for line in f:
                 p = [x.strip() for x in line.split(",")]
                 if len(p) < 7:
                     continue
                 try:
-                    sm.append(float(p[0]))
-                    mx.append(float(p[1]))
+                    rows.append((float(p[0]), float(p[1]), float(p[2])))
                 except ValueError:
                     continue
                 for name, v in zip(self.NAMES, p[3:7]):
                     if v.lower().startswith("active"):
                         reasons.add(name)
         os.unlink(self.path)
-        if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        if rows:
+            pmax = max(r[2] for r in rows)
+            load = [r for r in rows if r[2] >= 0.6 * pmax] or rows      # samples taken while kernels ran
+            out.update(sm_mhz=float(np.median([r[0] for r in load])), sm_max_mhz=float(max(r[1] for r in rows)),
+                       reasons=sorted(reasons), samples=len(rows), samples_under_load=len(load), power_w_max=pmax)
         return out
 
 
@@ -303,14 +305,14 @@ def own_arm(args):
 
     with torch.cuda.stream(stream):
         # ---------------- device-resident timing
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()                     # runs through warm-up, both timed loops; idle samples are dropped
         for s in range(Wm):
             device_step(frames[s], *cams[s])
         barrier()
         pl.reset_counters()
         pl.profile_enable(True)
-        sampler = ClockSampler(local)
-        if rank == 0:
-            sampler.start()
         barrier()
         ev0.record(stream)
         for s in range(Wm, Wm + K):
@@ -318,7 +320,6 @@ def own_arm(args):
         ev1.record(stream)
         barrier()
         ms = max_over_ranks(ev0.elapsed_time(ev1))
-        clocks = sampler.stop() if rank == 0 else None
         cnt = pl.counters()
         prof = pl.profile_collect()
         pl.profile_enable(False)
@@ -334,6 +335,7 @@ def own_arm(args):
         ev1.record(stream)
         barrier()
         ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
+        clocks = sampler.stop() if rank == 0 else None
         img_mean = float(host_np.reshape(-1, 4)[:, :3].mean())
 
     paths_total = sum_over_ranks(float(cnt["samples"]))
