@@ -134,3 +134,20 @@ def test_emulated_walk_matches_bruteforce_on_soup_and_is_ordered():
     assert np.array_equal(got["primid"], want["primid"])
     # front-to-back slot order + SAH keep the walk short: far fewer node visits than nodes
     assert visited < 0.25 * nodes.shape[0], visited
+
+
+def test_cpp_adaptor_compiles_against_reference_header_and_fails_loudly_without_gpu():
+    """include/radeon_rays_b200.hpp (the IntersectionApi adaptor a maintainer adds to the engine) against
+    the reference's own radeon_rays.h; without a CUDA device Create() must throw, not fall back."""
+    import subprocess
+    import __graft_entry__ as g
+    if not os.path.isdir("/root/reference/third_party/RadeonRays/RadeonRays/include"):
+        pytest.skip("reference headers not present")
+    exe = g.build_adaptor_check()
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    import torch
+    if not torch.cuda.is_available():
+        assert out.stdout.startswith("NO_DEVICE") and "no CPU fallback" in out.stdout
+    else:
+        assert "OK" in out.stdout

@@ -2,6 +2,8 @@
 against the brute-force oracle and -- where it was built -- the compiled reference kernel.
 The cases restate the reference's own API tests (UnitTest/radeon_rays_apitest_cl.h,
 radeon_rays_conformance_test_cl.h, radeon_rays_test_cl.h)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -291,3 +293,14 @@ def test_axis_aligned_and_negative_zero_directions(api, cornell):
     res = port.compare_hits(api.QueryIntersectionHost(rays), port.intersect(tris, rays), tris, rays)
     assert res["bad"] == 0 and res["tie_ok"] == 0, res
     assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
+
+
+def test_cpp_adaptor_binary_on_device():
+    """The engine-side C++ calling sequence through include/radeon_rays_b200.hpp (binary prebuilt
+    against the reference's radeon_rays.h by __graft_entry__.build(), tests/cpp/adaptor_check.cpp)."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "adaptor_check")
+    if not os.path.exists(exe):
+        pytest.skip("adaptor_check not prebuilt (needs the reference headers)")
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "OK" in out.stdout, out.stdout + out.stderr
