@@ -11,25 +11,9 @@
 #include "pt_kernels.h"
 
 #include "pt_shade.cuh"
-#include "traverse.cuh"
+#include "pt_wavefront.cuh"
 
 namespace mcrt {
-
-__device__ __forceinline__ Scene make_scene(const PtState& s) {
-    Scene sc;
-    sc.shapes = (const RTShape*)s.shapes;
-    sc.indices = s.indices;
-    sc.positions = s.positions;
-    sc.uvs = s.uvs;
-    sc.normals = s.normals;
-    sc.textures2D = (const TextureDesc2D*)s.textures2D;
-    sc.texData2D = s.texData2D;
-    sc.lights = (const RTLight*)s.lights;
-    sc.materials = (const RTMaterial*)s.materials;
-    sc.camera = (const RTPinholeCamera*)s.camera;
-    sc.numLights = s.numLights;
-    return sc;
-}
 
 // ---------------------------------------------------------------------------------------------
 // queue control: one thread, between stages (keeps all counts on the device)
@@ -69,49 +53,6 @@ k_raygen(PtState s, const uint32_t* __restrict__ pixels, int n) {
     s.ray_d[px] = make_float4(d.x, d.y, d.z, 0.0f);
     s.radiance[px] = make_float4(0.f, 0.f, 0.f, 0.f);
     s.queue[0][i] = px;
-}
-
-// ---------------------------------------------------------------------------------------------
-// persistent traversal over a queue
-// ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, typename Fetch, typename Store>
-__device__ __forceinline__ void persistent_trace(const uint4* nodes, const float4* tris, unsigned count,
-                                                 unsigned int* work_counter, Fetch fetch, Store store) {
-    const unsigned lane = threadIdx.x & 31u;
-    Traverser<ANY_HIT, false> trav{nodes, tris};
-    uint2 stack[MCRT_STACK_SIZE];
-    TravState st;
-    Ray ray;
-    int item = -1;
-    bool exhausted = false;
-    while (true) {
-        const unsigned idle = __ballot_sync(0xffffffffu, item < 0 && !exhausted);
-        if (idle) {
-            const int n_idle = __popc(idle);
-            const int my_rank = __popc(idle & ((1u << lane) - 1u));
-            unsigned base = 0;
-            const int leader = __ffs(idle) - 1;
-            if ((int)lane == leader) base = atomicAdd(work_counter, (unsigned)n_idle);
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (item < 0 && !exhausted) {
-                const unsigned idx = base + (unsigned)my_rank;
-                if (idx >= count) {
-                    exhausted = true;
-                } else {
-                    fetch(idx, ray);
-                    trav.init(st, ray);
-                    item = (int)idx;
-                }
-            }
-        }
-        if (__all_sync(0xffffffffu, item < 0 && exhausted)) break;
-        if (item >= 0) {
-            if (trav.run(st, ray, stack, nullptr)) {
-                store((unsigned)item, ray, st);
-                item = -1;
-            }
-        }
-    }
 }
 
 __global__ void __launch_bounds__(128, 8)
@@ -172,17 +113,6 @@ k_trace_shadow(PtState s) {
 // ---------------------------------------------------------------------------------------------
 // shade (PathTracing kernel body) over the live queue, with compaction of both outputs
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned warp_push(bool pred, unsigned int* counter) {
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned m = __ballot_sync(0xffffffffu, pred);
-    if (m == 0) return 0;
-    unsigned base = 0;
-    const int leader = __ffs(m) - 1;
-    if ((int)lane == leader) base = atomicAdd(counter, (unsigned)__popc(m));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    return base + __popc(m & ((1u << lane) - 1u));
-}
-
 __global__ void __launch_bounds__(128)
 k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
     const unsigned count = s.cnt[cur];
@@ -239,17 +169,6 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
             s.queue[1 - cur][ni] = px;
         }
     }
-}
-
-static int sm_count() {
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (sms <= 0) sms = 148;
-    }
-    return sms;
 }
 
 int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int frame, int max_depth,

@@ -402,13 +402,14 @@ int ptb_bdpt_render_sample(ptb_context* c, int frame, int max_depth) {
         const size_t P = (size_t)c->width * c->height;
         for (const mcrt::BdptBufferSpec& sp : mcrt::bdpt_buffer_specs(c->bd, max_depth)) {
             void* p = nullptr;
-            if ((rc = alloc_into(c->pixel_bufs, sp.name, P * sp.bytes_per_pixel, true, c->stream, &p))) return rc;
+            const size_t bytes = sp.bytes_per_pixel ? P * sp.bytes_per_pixel : 64;
+            if ((rc = alloc_into(c->pixel_bufs, sp.name, bytes, true, c->stream, &p))) return rc;
             *sp.dst = p;
         }
         c->bdpt_depth = max_depth;
     }
     cudaError_t e = cudaSuccess;
-    c->launches += mcrt::launch_bdpt_sample(c->st, c->bd, frame, max_depth, c->stream, &e);
+    c->launches += mcrt::launch_bdpt_sample(c->st, c->bd, c->d_pixels, c->n_pixels, frame, max_depth, c->stream, &e);
     if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("bdpt launch: ") + cudaGetErrorString(e));
     return 0;
 }

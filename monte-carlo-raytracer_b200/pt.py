@@ -359,3 +359,15 @@ def smoke_check(api, scene, width=64, height=64, depth=3):
     assert np.isfinite(out[0]).all() and out[0][:, :3].sum() > 0.0
     assert np.array_equal(out[0].view(np.uint32)[:, :3], out[1].view(np.uint32)[:, :3])
     return out[0]
+
+
+def make_bdpt_pipeline(api, scene, width, height, max_depth, use_taa=True):
+    """PathTracingApp::startPathTracing's BDPT pipeline (:256-263): RTBDPTPass + RTReconstructionPass."""
+    rts = RTScene(api, scene)
+    gi = GISettings()
+    gi.imageResolution = (width, height)
+    gi.maxDepth = max_depth
+    gi.useTAA = use_taa
+    pl = RenderPipeline(rts, gi)
+    pl.addRenderPasses(RTBDPTPass(), RTReconstructionPass())
+    return pl

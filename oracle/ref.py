@@ -175,3 +175,88 @@ class RefPathTracer:
                 o.intersect(self.nodes, self.rays, self.isect)
                 self.rays_traced += int((self.rays["extra"][:, 1] != 0).sum())
         return self.radiance
+
+
+class RefBDPT:
+    """RTBDPTPass state and host loop (renderPasses/RTBDPTPass.cpp:67-128,130-448,451-478): buffers are
+    zero-filled at creation and live across frames (the kernels read some of them before writing,
+    SURVEY App. A E12), so frames must be rendered in order from frame 0."""
+
+    def __init__(self, oracle: RefOracle, scene, nodes, width, height, max_depth):
+        self.o, self.scene, self.nodes, self.w, self.h, self.D = oracle, scene, nodes, width, height, max_depth
+        lib = oracle.lib
+        lib.ref_bdpt_vertex_size.restype = ctypes.c_int
+        vp, i, fp, ip = ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p
+        lib.ref_bdpt_generate_start_vertices.argtypes = [vp, i, i, i, i] + [vp] * 11
+        lib.ref_bdpt_generate_secondary_vertices.argtypes = [vp, i, i, i, i, i, vp, vp, vp, vp, fp, ip, i]
+        lib.ref_bdpt_prepare_connections.argtypes = [vp, i, i, i, i] + [vp] * 8
+        lib.ref_bdpt_connect_vertices.argtypes = [vp, i, i, i, i] + [vp] * 10
+        lib.ref_bdpt_copy_buffer.argtypes = [i, i, vp, vp]
+        self.vsize = lib.ref_bdpt_vertex_size()
+        n, D = width * height, max_depth
+        self.max_conn = (D + 2) * (D + 3) // 2 - 2              # getMaxPossibleConnectionsCount (:397-401)
+        z = lambda count, dt: np.zeros(count, dtype=dt)
+        self.radiance = np.zeros((n, 4), np.float32)
+        self.final = z(n * 3, np.float32)
+        self.cam_vertices = z(n * (D + 2) * self.vsize, np.uint8)
+        self.light_vertices = z(n * (D + 1) * self.vsize, np.uint8)
+        self.cam_rays, self.light_rays = z(n, L.RAY), z(n, L.RAY)
+        self.cam_isect, self.light_isect = z(n, L.INTERSECTION), z(n, L.INTERSECTION)
+        self.cam_beta, self.light_beta = np.zeros((n, 4), np.float32), np.zeros((n, 4), np.float32)
+        self.cam_pdf, self.light_pdf = z(n, np.float32), z(n, np.float32)
+        self.cam_counts, self.light_counts = z(n, np.int32), z(n, np.int32)
+        self.conn_rays = z(n * self.max_conn, L.RAY)
+        self.conn_vis = z(n * self.max_conn, np.int32)
+        self.sampled_cam = z(n * D * self.vsize, np.uint8)
+        self.sampled_light = z(n * D * self.vsize, np.uint8)
+        self.temp_radiance = np.zeros((n * self.max_conn, 4), np.float32)
+        self.rays_traced = 0
+        self.connection_rays_traced = 0
+
+    def _trace(self, rays, isect):
+        self.o.intersect(self.nodes, rays, isect)
+        self.rays_traced += int((rays["extra"][:, 1] != 0).sum())
+
+    def render_sample(self, camera, frame, trace=None):
+        lib, o, D, w, h = self.o.lib, self.o, self.D, self.w, self.h
+        desc = o.scene_desc(self.scene, camera)
+        d = ctypes.byref(desc)
+        # generateStartVertices (:130-221)
+        lib.ref_bdpt_generate_start_vertices(d, w, h, frame, D, _ptr(self.cam_vertices), _ptr(self.cam_rays),
+                                             _ptr(self.cam_beta), _ptr(self.cam_pdf), _ptr(self.cam_counts),
+                                             _ptr(self.light_vertices), _ptr(self.light_rays), _ptr(self.light_beta),
+                                             _ptr(self.light_pdf), _ptr(self.light_counts), _ptr(self.final))
+        self._trace(self.cam_rays, self.cam_isect)
+        self._trace(self.light_rays, self.light_isect)
+        # generateSecondaryVertices (:223-307)
+        for depth in range(1, D + 2):
+            lib.ref_bdpt_generate_secondary_vertices(d, w, h, frame, D, 1, _ptr(self.cam_vertices), _ptr(self.cam_rays),
+                                                     _ptr(self.cam_isect), _ptr(self.cam_beta), _ptr(self.cam_pdf),
+                                                     _ptr(self.cam_counts), depth)
+            if depth <= D:
+                lib.ref_bdpt_generate_secondary_vertices(d, w, h, frame, D, 0, _ptr(self.light_vertices),
+                                                         _ptr(self.light_rays), _ptr(self.light_isect),
+                                                         _ptr(self.light_beta), _ptr(self.light_pdf),
+                                                         _ptr(self.light_counts), depth)
+            self._trace(self.cam_rays, self.cam_isect)
+            if depth <= D:
+                self._trace(self.light_rays, self.light_isect)
+        # prepareVertexConnections (:309-360)
+        lib.ref_bdpt_prepare_connections(d, w, h, frame, D, _ptr(self.cam_vertices), _ptr(self.light_vertices),
+                                         _ptr(self.sampled_cam), _ptr(self.sampled_light), _ptr(self.conn_rays),
+                                         _ptr(self.cam_counts), _ptr(self.light_counts), _ptr(self.temp_radiance))
+        o.occluded(self.nodes, self.conn_rays, self.conn_vis)
+        self.connection_rays_traced += int((self.conn_rays["extra"][:, 1] != 0).sum())
+        if trace is not None:
+            trace["cam_counts"] = self.cam_counts.copy()
+            trace["light_counts"] = self.light_counts.copy()
+            trace["unweighted"] = self.temp_radiance.copy()
+            trace["conn_active"] = (self.conn_rays["extra"][:, 1] != 0).copy()
+            trace["conn_vis"] = self.conn_vis.copy()
+        # makeConnections (:362-395), copyRadianceBuffer (:403-430)
+        lib.ref_bdpt_connect_vertices(d, w, h, frame, D, _ptr(self.cam_vertices), _ptr(self.light_vertices),
+                                      _ptr(self.sampled_cam), _ptr(self.sampled_light), _ptr(self.conn_rays),
+                                      _ptr(self.conn_vis), _ptr(self.cam_counts), _ptr(self.light_counts),
+                                      _ptr(self.temp_radiance), _ptr(self.final))
+        lib.ref_bdpt_copy_buffer(w, h, _ptr(self.final), _ptr(self.radiance))
+        return self.radiance
