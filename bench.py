@@ -214,7 +214,7 @@ def own_arm(args):
     import torch
     import torch.distributed as dist
     import mcrt_b200  # noqa: F401
-    from mcrt_b200 import rr, pt, camera, scene_library
+    from mcrt_b200 import rr, pt, camera, scene_library, multi_gpu
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -257,10 +257,7 @@ def own_arm(args):
 
     def merge():
         """One NCCL all-reduce of the accumulation buffers; every rank ends with the merged image."""
-        stage[:4 * P].copy_(t_wr)
-        stage[4 * P:].copy_(t_fw)
-        dist.all_reduce(stage)
-        torch.div(stage[:4 * P].view(P, 4), stage[4 * P:].view(P, 1), out=t_img.view(P, 4))
+        multi_gpu.merge_accumulation(t_wr, t_fw, stage=stage, image=t_img)
 
     def device_step(frame, cam, off):
         """C-ABI calls only; the camera struct was built before the timed region."""
@@ -299,7 +296,7 @@ def own_arm(args):
         return float(t.item())
 
     K, Wm = args.steps, max(args.warmup, 3)
-    frames = [(s * world + rank) for s in range(Wm + K)]
+    frames = multi_gpu.frames_of_rank(rank, world, Wm + K)
     cams = [cam_for(f) for f in frames]
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 

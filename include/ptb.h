@@ -87,6 +87,10 @@ int ptb_set_camera(ptb_context* ctx, const void* rt_pinhole_camera);
  * t % num_parts == part (round-robin tiles); buffers stay full-frame so global pixel
  * indices seed the sampler.  Default (0, 1) = whole image. */
 int ptb_set_partition(ptb_context* ctx, int part, int num_parts);
+/* Host-only: the global pixel indices part `part` of `num_parts` owns (64x64 tiles, round-robin in
+ * row-major tile order).  `out` may be NULL to query the count.  Needs no device. */
+int ptb_partition_pixels(int width, int height, int part, int num_parts, uint32_t* out, int64_t capacity,
+                         int64_t* count);
 
 /* ---- stage-wise entry points in the reference's buffer layouts (one call = one kernel the reference launches) */
 int ptb_generate_primary_rays(ptb_context* ctx);                                 /* GeneratePerspectiveRays */

@@ -123,6 +123,17 @@ int ready(ptb_context* c) {
     return refresh_bvh(c);
 }
 
+// 64x64 tiles dealt round-robin in row-major tile order (partition A)
+void partition_pixels(int width, int height, int part, int num_parts, std::vector<uint32_t>& px) {
+    const int tw = (width + 63) / 64, th = (height + 63) / 64;
+    for (int ty = 0; ty < th; ++ty)
+        for (int tx = 0; tx < tw; ++tx) {
+            if ((ty * tw + tx) % num_parts != part) continue;
+            for (int y = ty * 64; y < std::min(height, ty * 64 + 64); ++y)
+                for (int x = tx * 64; x < std::min(width, tx * 64 + 64); ++x) px.push_back((uint32_t)(y * width + x));
+        }
+}
+
 int build_partition(ptb_context* c) {
     if (c->d_pixels) {
         cudaFree(c->d_pixels);
@@ -133,15 +144,8 @@ int build_partition(ptb_context* c) {
         c->n_pixels = P;
         return 0;
     }
-    // 64x64 tiles dealt round-robin in row-major tile order (partition A)
     std::vector<uint32_t> px;
-    const int tw = (c->width + 63) / 64, th = (c->height + 63) / 64;
-    for (int ty = 0; ty < th; ++ty)
-        for (int tx = 0; tx < tw; ++tx) {
-            if ((ty * tw + tx) % c->num_parts != c->part) continue;
-            for (int y = ty * 64; y < std::min(c->height, ty * 64 + 64); ++y)
-                for (int x = tx * 64; x < std::min(c->width, tx * 64 + 64); ++x) px.push_back((uint32_t)(y * c->width + x));
-        }
+    partition_pixels(c->width, c->height, c->part, c->num_parts, px);
     c->n_pixels = (int)px.size();
     if (!px.empty()) {
         PTB_CUDA(cudaMalloc((void**)&c->d_pixels, px.size() * 4));
@@ -294,6 +298,19 @@ int ptb_set_camera(ptb_context* c, const void* cam) {
     if (rc) return rc;
     // pageable source: the copy is staged before the call returns, so the caller may reuse `cam`
     PTB_CUDA(cudaMemcpyAsync((void*)c->st.camera, cam, 176, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+
+int ptb_partition_pixels(int width, int height, int part, int num_parts, uint32_t* out, int64_t capacity, int64_t* count) {
+    if (width <= 0 || height <= 0 || num_parts < 1 || part < 0 || part >= num_parts || !count)
+        return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad partition");
+    std::vector<uint32_t> px;
+    partition_pixels(width, height, part, num_parts, px);
+    *count = (int64_t)px.size();
+    if (out) {
+        if (capacity < (int64_t)px.size()) return pfail(RRB_ERROR_INVALID_ARGUMENT, "pixel list capacity too small");
+        std::memcpy(out, px.data(), px.size() * sizeof(uint32_t));
+    }
     return 0;
 }
 

@@ -1,0 +1,48 @@
+"""Multi-GPU plumbing of the path tracer: one process per GPU, scene and BVH replicated,
+work split by image tiles (A) or by sample index (B), and ONE collective -- an all-reduce (sum) of the
+accumulation buffers  sum(w*L) (float4[P])  and  sum(w) (float[P]) -- followed by the division
+ReconstructionPass does (reconstruction.cl:50-58).  The reference has no multi-device path; this is
+the whole exchange step.
+
+Works on CUDA tensors over NCCL (bench.py) and on CPU tensors over gloo (tests)."""
+import ctypes
+
+import numpy as np
+
+
+def partition_pixels(width, height, part, num_parts):
+    """Global pixel indices of partition A (host-side mirror of ptb_set_partition, needs no GPU)."""
+    from . import pt
+    lib = pt._lib()
+    lib.ptb_partition_pixels.argtypes = [ctypes.c_int] * 4 + [ctypes.c_void_p, ctypes.c_int64, ctypes.POINTER(ctypes.c_int64)]
+    n = ctypes.c_int64()
+    pt._check(lib.ptb_partition_pixels(width, height, part, num_parts, None, 0, ctypes.byref(n)))
+    out = np.empty(n.value, np.uint32)
+    pt._check(lib.ptb_partition_pixels(width, height, part, num_parts, out.ctypes.data_as(ctypes.c_void_p), out.size, ctypes.byref(n)))
+    return out
+
+
+def frames_of_rank(rank, world, steps, first=0):
+    """Partition B: the sample (frame) indices rank `rank` renders in `steps` steps."""
+    return [first + s * world + rank for s in range(steps)]
+
+
+def merge_accumulation(weighted, weights, stage=None, image=None, group=None):
+    """All-reduce (sum) the two accumulation buffers and divide.
+
+    weighted: float32 tensor (P, 4) -- this rank's  sum(w * clamp(L));  weights: float32 (P,).
+    stage: optional preallocated float32 (5P,) scratch; image: optional (P, 4) output.
+    The rank-local buffers are left untouched (they keep accumulating); returns the merged image."""
+    import torch
+    import torch.distributed as dist
+    P = weights.numel()
+    if stage is None:
+        stage = torch.empty(5 * P, dtype=torch.float32, device=weighted.device)
+    stage[:4 * P].copy_(weighted.reshape(-1))
+    stage[4 * P:].copy_(weights.reshape(-1))
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(stage, op=dist.ReduceOp.SUM, group=group)
+    if image is None:
+        image = torch.empty(P, 4, dtype=torch.float32, device=weighted.device)
+    torch.div(stage[:4 * P].view(P, 4), stage[4 * P:].view(P, 1), out=image.view(P, 4))
+    return image

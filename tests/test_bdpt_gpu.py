@@ -115,3 +115,21 @@ def test_bdpt_agrees_with_path_tracer_in_the_mean(cornell):
     m_b = np.mean([g[:, :3].mean(0) for g in got], axis=0)
     m_p = acc[:, :3].mean(0) / 16
     assert np.allclose(m_b, m_p, rtol=0.1), (m_b, m_p)
+
+
+def test_golden_cornell_spheres_bdpt():
+    """Committed vectors of the compiled reference (tools/make_golden.py), frames 0 and 1."""
+    g = np.load(os.path.join(GOLDEN, "cornell_spheres_bdpt_64x64_d5.npz"))
+    got, _ = gpu_frames(scene_library.cornell_box(True), 64, 64, 5, 2)
+    for f in range(2):
+        check(got[f], g["radiance_f%d" % f], 0.97)
+
+
+def test_bdpt_tile_partition_sums_to_full_frame(cornell):
+    """Tile partition: each rank traces its tiles' subpaths but splats anywhere; the sum of
+    the ranks' full-frame buffers equals the single-context image up to float-add reassociation."""
+    w, h = 128, 128
+    full, _ = gpu_frames(cornell, w, h, 4, 1)
+    parts = [gpu_frames(cornell, w, h, 4, 1, partition=(p, 2))[0][0] for p in range(2)]
+    merged = parts[0] + parts[1]
+    assert np.allclose(merged[:, :3], full[0][:, :3], rtol=1e-5, atol=1e-6)

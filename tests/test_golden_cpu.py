@@ -31,6 +31,18 @@ def test_golden_is_reproducible_from_compiled_reference(ref_oracle, cornell):
         assert np.array_equal(fresh[k], g[k]), k
 
 
+def test_bdpt_golden_is_reproducible_from_compiled_reference(ref_oracle):
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(GOLDEN), "..", "tools"))
+    import make_golden
+    fresh = make_golden.cornell_spheres_bdpt()
+    g = np.load(os.path.join(GOLDEN, "cornell_spheres_bdpt_64x64_d5.npz"))
+    for k in g.files:      # float atomics: summation order is not fixed (BDPT.cl:654-669)
+        assert np.allclose(fresh[k], g[k], rtol=1e-5, atol=1e-7), k
+    # BDPT and PT estimate the same image
+    assert 0.05 < g["radiance_f0"][:, 0].mean() < 2.0
+
+
 def test_golden_image_is_plausible():
     g = np.load(os.path.join(GOLDEN, "cornell_pt_64x64_d5.npz"))
     r = g["radiance_f0"]

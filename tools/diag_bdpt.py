@@ -1,7 +1,9 @@
 """Per-depth / per-frame agreement of the CUDA BDPT with the compiled reference (run on a GPU box)."""
 import sys
 import numpy as np
-sys.path.insert(0, "tests")
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 import mcrt_b200  # noqa
 from mcrt_b200 import scene_library
 import test_bdpt_gpu as T

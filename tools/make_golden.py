@@ -35,6 +35,20 @@ def cornell_pt(w=64, h=64, depth=5, frames=2):
     return out
 
 
+def cornell_spheres_bdpt(w=64, h=64, depth=5, frames=2):
+    """C4 (Cornell + glass + mirror sphere), BDPT.  The reference sums strategies with float atomics in
+    an unspecified order, so these vectors are reproducible to rounding only (compared with rtol 1e-5)."""
+    scene = scene_library.cornell_box(True)
+    o = ref.RefOracle()
+    nodes = o.build_scene_bvh(scene)
+    rb = ref.RefBDPT(o, scene, nodes, w, h, depth)
+    out = {}
+    for f in range(frames):
+        cam = camera.make_camera(scene.camera, w, h, camera.taa_pixel_offset(f))
+        out["radiance_f%d" % f] = rb.render_sample(cam, f).copy()
+    return out
+
+
 def cornell_isect(n=4096):
     scene = scene_library.cornell_box()
     o = ref.RefOracle()
@@ -51,6 +65,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     np.savez_compressed(os.path.join(OUT, "cornell_pt_64x64_d5.npz"), **cornell_pt())
     np.savez_compressed(os.path.join(OUT, "cornell_isect_4096.npz"), **cornell_isect())
+    np.savez_compressed(os.path.join(OUT, "cornell_spheres_bdpt_64x64_d5.npz"), **cornell_spheres_bdpt())
     print("wrote", os.listdir(OUT))
 
 
