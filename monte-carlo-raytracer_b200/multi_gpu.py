@@ -46,3 +46,41 @@ def merge_accumulation(weighted, weights, stage=None, image=None, group=None):
         image = torch.empty(P, 4, dtype=torch.float32, device=weighted.device)
     torch.div(stage[:4 * P].view(P, 4), stage[4 * P:].view(P, 1), out=image.view(P, 4))
     return image
+
+
+class PipelinedMerger:
+    """merge_accumulation split in two so the all-reduce of step k overlaps the rendering of step k+1:
+    begin() snapshots the rank's buffers and starts the collective asynchronously (NCCL runs it on its
+    own stream once the snapshot is complete); finish() makes the current stream wait for it and writes
+    the merged image.  The displayed image therefore lags the samples by one step; call finish() once
+    more after the last step."""
+
+    def __init__(self, num_pixels, device, group=None):
+        import torch
+        self.P, self.group = num_pixels, group
+        self.stage = torch.empty(5 * num_pixels, dtype=torch.float32, device=device)
+        self.work = None
+        self.pending = False
+
+    def begin(self, weighted, weights):
+        import torch.distributed as dist
+        if self.pending:
+            raise RuntimeError("PipelinedMerger.begin() before finish() of the previous step")
+        P = self.P
+        self.stage[:4 * P].copy_(weighted.reshape(-1))
+        self.stage[4 * P:].copy_(weights.reshape(-1))
+        if dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            self.work = dist.all_reduce(self.stage, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        self.pending = True
+
+    def finish(self, image):
+        import torch
+        if not self.pending:
+            return image
+        if self.work is not None:
+            self.work.wait()
+            self.work = None
+        P = self.P
+        torch.div(self.stage[:4 * P].view(P, 4), self.stage[4 * P:].view(P, 1), out=image.view(P, 4))
+        self.pending = False
+        return image

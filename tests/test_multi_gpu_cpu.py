@@ -56,7 +56,14 @@ def _worker(rank, world, port, mode, queue):
             mask = np.zeros(W * H, np.float32)
             mask[multi_gpu.partition_pixels(W, H, rank, world)] = 1.0
             wr, fw = accumulate(range(FRAMES), mask)
-        img = multi_gpu.merge_accumulation(torch.from_numpy(wr), torch.from_numpy(fw))
+        if mode == "sample":      # the pipelined form bench.py uses: begin / finish around the collective
+            m = multi_gpu.PipelinedMerger(W * H, torch.device("cpu"))
+            img = torch.zeros(W * H, 4)
+            m.begin(torch.from_numpy(wr), torch.from_numpy(fw))
+            m.finish(img)
+            assert m.finish(img) is img      # idempotent when nothing is pending
+        else:
+            img = multi_gpu.merge_accumulation(torch.from_numpy(wr), torch.from_numpy(fw))
         if rank == 0:
             queue.put(img.numpy().copy())
     finally:
