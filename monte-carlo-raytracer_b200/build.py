@@ -17,13 +17,23 @@ STAMP_PATH = os.path.join(_HERE, ".libmcrt_b200.stamp")
 CUDA_SOURCES = ["rrb_api.cu", "rrb_kernels.cu", "ptb_api.cu", "pt_kernels.cu", "pt_stage_kernels.cu", "bdpt_kernels.cu"]
 CXX_SOURCES = ["bvh8_build.cpp"]
 
+# fp32 modes of the SHADING arithmetic.  The traversal, the triangle test and the hit
+# barycentrics are written with explicit __fmul_rn/__fadd_rn/__fdiv_rn and are identical in every mode.
+#   strict  no FMA contraction, IEEE division and sqrt: operation-for-operation the oracle's arithmetic
+#   fma     contraction allowed, IEEE division and sqrt
+#   fast    contraction allowed, approximate division / sqrt (2 ulp)
+FP_MODES = {
+    "strict": ["--fmad=false", "--prec-div=true", "--prec-sqrt=true", "--ftz=false"],
+    "fma": ["--fmad=true", "--prec-div=true", "--prec-sqrt=true", "--ftz=false"],
+    "fast": ["--fmad=true", "--prec-div=false", "--prec-sqrt=false", "--ftz=false"],
+}
+FP_MODE = os.environ.get("MCRT_FP_MODE", "strict")
+
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    # fp32 parity contract: no implicit FMA contraction, IEEE division and sqrt.  Hot
-    # loops that want FMAs ask for them explicitly (__fmaf_rn in the slab test).
-    "--fmad=false", "--prec-div=true", "--prec-sqrt=true", "--ftz=false",
+] + FP_MODES[FP_MODE] + [
     "-Xcompiler", "-fPIC,-O3,-ffp-contract=off,-fno-fast-math", "-Xptxas", "-v",
-]
+] + os.environ.get("MCRT_NVCC_DEFS", "").split()
 
 
 def _nvcc():

@@ -64,7 +64,7 @@ HD bool isReflection(V3 woWorld, V3 wiWorld, const RTInteraction* si) {
 HD bool BxDFMatchesFlags(int bxdfType, int flags) { return (bxdfType & flags) == bxdfType; }
 
 // bxdfs.cl:159-190
-HD float evaluateFresnelDielectric(float cosThetaI, float etaI, float etaT) {
+HD_BXDF float evaluateFresnelDielectric(float cosThetaI, float etaI, float etaT) {
     cosThetaI = clampf(cosThetaI, -1.0f, 1.0f);
     if (cosThetaI <= 0.0f) {
         float h = etaI;
@@ -135,7 +135,7 @@ HD float roughnessToAlpha(float roughness) {
 }
 
 // bxdfs.cl:406-415
-HD float computeTrowbridgeReitzDistribution(V3 wh, V2 alpha) {
+HD_BXDF float computeTrowbridgeReitzDistribution(V3 wh, V2 alpha) {
     float tan2Theta = evalTanSqTheta(wh);
     if (isinf(tan2Theta)) return 0.0f;
     const float cos4Theta = evalCosSqTheta(wh) * evalCosSqTheta(wh);
@@ -143,7 +143,7 @@ HD float computeTrowbridgeReitzDistribution(V3 wh, V2 alpha) {
     return 1.0f / (PT_PI * alpha.x * alpha.y * cos4Theta * (1.0f + e) * (1.0f + e));
 }
 // bxdfs.cl:435-445
-HD float computeTrowbridgeReitzDistributionLambda(V3 w, V2 alpha) {
+HD_BXDF float computeTrowbridgeReitzDistributionLambda(V3 w, V2 alpha) {
     float absTanTheta = fabsf(evalTanTheta(w));
     if (isinf(absTanTheta)) return 0.0f;
     float alphaW = sqrtf(evalCosSqPhi(w) * alpha.x * alpha.x + evalSinSqPhi(w) * alpha.y * alpha.y);
@@ -156,7 +156,7 @@ HD float computeTrowbridgeReitzDistributionG(V3 wo, V3 wi, V2 alpha) {
 }
 
 // bxdfs.cl:481-500
-HD V3 evaluateMicrofacetReflection_TR(V3 R, V2 alpha, float etaI, float etaT, V3 wo, V3 wi) {
+HD_BXDF V3 evaluateMicrofacetReflection_TR(V3 R, V2 alpha, float etaI, float etaT, V3 wo, V3 wi) {
     float cosThetaO = evalAbsCosTheta(wo);
     float cosThetaI = evalAbsCosTheta(wi);
     V3 wh = wi + wo;
@@ -169,7 +169,7 @@ HD V3 evaluateMicrofacetReflection_TR(V3 R, V2 alpha, float etaI, float etaT, V3
 }
 
 // bxdfs.cl:563-588
-HD V3 evaluateMicrofacetTransmission_TR(V3 T, int mode, V2 alpha, float etaI, float etaT, V3 wo, V3 wi) {
+HD_BXDF V3 evaluateMicrofacetTransmission_TR(V3 T, int mode, V2 alpha, float etaI, float etaT, V3 wo, V3 wi) {
     if (isSameHemisphere(wo, wi)) return v3(0.0f);
     float cosThetaO = evalCosTheta(wo);
     float cosThetaI = evalCosTheta(wi);
@@ -186,7 +186,7 @@ HD V3 evaluateMicrofacetTransmission_TR(V3 T, int mode, V2 alpha, float etaI, fl
 }
 
 // bxdfs.cl:647-675
-HD V3 sampleTrowbridgeReitzDistribution_wh(V2 u, V3 wo, V2 alpha) {
+HD_BXDF V3 sampleTrowbridgeReitzDistribution_wh(V2 u, V3 wo, V2 alpha) {
     float cosTheta = 0.0f;
     float phi = (2.0f * PT_PI) * u.y;
     if (alpha.x == alpha.y) {

@@ -113,22 +113,41 @@ k_trace_shadow(PtState s) {
 // ---------------------------------------------------------------------------------------------
 // shade (PathTracing kernel body) over the live queue, with compaction of both outputs
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
+// Block size of the shade kernel, and an optional phase synchronisation of its warps (pt_shade.cuh).
+// The shading code is ~170 KB of SASS, far beyond the 32 KB L1.5 instruction cache (ncu r01:
+// gcc__cache_requests_type_instruction at 84 % of peak, stall no_instructions 22 %).  Measured on
+// C3 (profiles/r01_shade_variants.md): walking the phases in lock-step per CTA costs more in
+// barrier waits than it saves in instruction fetches (2.25 ms vs 2.00 ms per step), so it is off.
+#ifndef PT_SHADE_BLOCK
+#define PT_SHADE_BLOCK 512
+#endif
+#ifndef PT_SHADE_SYNC
+#define PT_SHADE_SYNC 0
+#endif
+#ifndef PT_SHADE_CTAS_PER_SM
+#define PT_SHADE_CTAS_PER_SM (512 / PT_SHADE_BLOCK > 0 ? 512 / PT_SHADE_BLOCK : 1)   // 16 resident warps at ~115 registers
+#endif
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, 1)
 k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
     const unsigned count = s.cnt[cur];
-    // grid-stride over whole warps so that the ballots below always see full warps
-    for (unsigned base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < count;
-         base += gridDim.x * blockDim.x) {
-        const unsigned i = base + (threadIdx.x & 31u);
-        bool pushNext = false, pushShadow = false;
+    const Scene sc = make_scene(s);
+    // CTA-uniform trip count: every thread reaches the barriers inside shade_vertex and the ballots below
+    for (unsigned cta_base = blockIdx.x * blockDim.x; cta_base < count; cta_base += gridDim.x * blockDim.x) {
+        const unsigned i = cta_base + threadIdx.x;
+        bool pushNext = false, pushShadow = false, active = false;
         ShadeOut out;
+        ShadeIn in;
         uint32_t px = 0;
+        in.pixel = 0;
+        in.shapeId = in.primId = 0;
+        in.bu = in.bv = 0.0f;
+        in.rayDir = in.throughput = v3(0.0f);
+        in.prevBsdfFlags = 0;
         if (i < count) {
             px = s.queue[cur][i];
             const int4 h = s.hit[px];
             if (h.x != -1 && h.y != -1) {
-                const Scene sc = make_scene(s);
-                ShadeIn in;
+                active = true;
                 in.pixel = (int)px;
                 in.shapeId = h.x;
                 in.primId = h.y;
@@ -139,19 +158,21 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
                 const float4 tp = s.throughput[px];
                 in.throughput = v3(tp.x, tp.y, tp.z);
                 in.prevBsdfFlags = __float_as_int(tp.w);
-                shade_vertex(sc, in, frame, s.width, s.height, bounce, maxDepth, &out);
-                if (out.hasEmission) {
-                    float4 r = s.radiance[px];
-                    r.x += out.emitted.x;
-                    r.y += out.emitted.y;
-                    r.z += out.emitted.z;
-                    s.radiance[px] = r;
-                } else {
-                    // a zero contribution adds nothing whatever the visibility: no shadow ray needed
-                    pushShadow = out.shadow.written &&
-                                 !(out.direct.x == 0.0f && out.direct.y == 0.0f && out.direct.z == 0.0f);
-                    pushNext = out.continues;
-                }
+            }
+        }
+        shade_vertex<PT_SHADE_SYNC != 0>(sc, in, active, frame, s.width, s.height, bounce, maxDepth, &out);
+        if (active) {
+            if (out.hasEmission) {
+                float4 r = s.radiance[px];
+                r.x += out.emitted.x;
+                r.y += out.emitted.y;
+                r.z += out.emitted.z;
+                s.radiance[px] = r;
+            } else {
+                // a zero contribution adds nothing whatever the visibility: no shadow ray needed
+                pushShadow = out.shadow.written &&
+                             !(out.direct.x == 0.0f && out.direct.y == 0.0f && out.direct.z == 0.0f);
+                pushNext = out.continues;
             }
         }
         const unsigned si = warp_push(pushShadow, s.cnt + 2);
@@ -178,7 +199,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
     if (n_pixels <= 0) return 0;
     const int sms = sm_count();
     const int trace_blocks = min(sms * 8, (n_pixels + 127) / 128);
-    const int shade_blocks = min(sms * 16, (n_pixels + 127) / 128);
+    const int shade_blocks = min(sms * PT_SHADE_CTAS_PER_SM, (n_pixels + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK);
     k_raygen<<<(n_pixels + 255) / 256, 256, 0, stream>>>(s, pixels, n_pixels);
     ++launches;
     if (s.numLights > 0) {   // RTPathTracingPass::update returns early without lights (:42-43); PathTracing.cl:72
@@ -188,7 +209,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
             if (timer) timer->mark(stream);
             k_trace_closest<<<trace_blocks, 128, 0, stream>>>(s, cur);
             if (timer) timer->mark(stream);
-            k_shade<<<shade_blocks, 128, 0, stream>>>(s, cur, frame, b, max_depth);
+            k_shade<<<shade_blocks, PT_SHADE_BLOCK, 0, stream>>>(s, cur, frame, b, max_depth);
             if (timer) timer->mark(stream);
             k_trace_shadow<<<trace_blocks, 128, 0, stream>>>(s);
             if (timer) timer->mark(stream);

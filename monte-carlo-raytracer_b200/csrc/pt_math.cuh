@@ -31,6 +31,24 @@ struct V3 {
 };
 
 #define HD __device__ __forceinline__
+// Large helpers with several call sites can be kept out of line to shrink the shade kernels (their
+// SASS otherwise exceeds the instruction cache); results do not depend on it (no contraction).
+#ifndef PT_TEX_NOINLINE
+#define PT_TEX_NOINLINE 0
+#endif
+#ifndef PT_BXDF_NOINLINE
+#define PT_BXDF_NOINLINE 0
+#endif
+#if PT_TEX_NOINLINE
+#define HD_TEX static __device__ __noinline__
+#else
+#define HD_TEX __device__ __forceinline__
+#endif
+#if PT_BXDF_NOINLINE
+#define HD_BXDF static __device__ __noinline__
+#else
+#define HD_BXDF __device__ __forceinline__
+#endif
 
 HD V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
 HD V3 v3(float a) { return v3(a, a, a); }

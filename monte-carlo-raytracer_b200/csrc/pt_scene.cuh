@@ -131,8 +131,25 @@ HD RTInteraction computeSurfaceInteraction(const Scene& sc, int shapeId, int pri
     return si;
 }
 
+// `i % n` of the reference (textures.cl:104-107) for the operands that occur: after wrapping, uv is in
+// [0, 1], so floor(uv * n) is in [0, n] and the +1 neighbour in [1, n + 1].  One conditional subtract
+// gives the same integer as the modulo without the integer-division sequence; anything outside
+// [0, 2n) takes the general path.
+static __device__ __noinline__ int wrap_index_general(int i, int n) { return i % n; }
+HD int wrap_index(int i, int n) {
+    if ((unsigned)i < (unsigned)n) return i;
+    if ((unsigned)i < 2u * (unsigned)n) return i - n;
+    return wrap_index_general(i, n);
+}
+// convert_float4(uchar4): exact for 0..255.  The magic-number form keeps the conversion on the FP32
+// pipe instead of 16 I2F per fetch on the quarter-rate XU pipe; the value is identical.
+HD float byte_to_float(unsigned b) { return __uint_as_float(0x4B000000u | b) - 8388608.0f; }
+HD float4 texel_to_float4(uchar4 c) {
+    return make_float4(byte_to_float(c.x), byte_to_float(c.y), byte_to_float(c.z), byte_to_float(c.w));
+}
+
 // textures.cl:70-125 readTexture2Df_linear (the only filter reached: textures.cl:204-209)
-HD float4 readTexture2Df(const Scene& sc, int texId, V2 uv) {
+HD_TEX float4 readTexture2Df(const Scene& sc, int texId, V2 uv) {
     const TextureDesc2D tex = sc.textures2D[texId];
     const int tw = tex.width, th = tex.height;
     uv.x -= 1.0f / tw * 0.5f;
@@ -154,10 +171,10 @@ HD float4 readTexture2Df(const Scene& sc, int texId, V2 uv) {
             break;
     }
     const float fx = uv.x * tw, fy = uv.y * th;
-    int x0 = ((int)floorf(fx)) % tw;
-    int y0 = ((int)floorf(fy)) % th;
-    int x1 = (x0 + 1) % tw;
-    int y1 = (y0 + 1) % th;
+    int x0 = wrap_index((int)floorf(fx), tw);
+    int y0 = wrap_index((int)floorf(fy), th);
+    int x1 = wrap_index(x0 + 1, tw);
+    int y1 = wrap_index(y0 + 1, th);
     x0 = min(max(x0, 0), tw - 1);
     y0 = min(max(y0, 0), th - 1);
     x1 = min(max(x1, 0), tw - 1);
@@ -166,8 +183,8 @@ HD float4 readTexture2Df(const Scene& sc, int texId, V2 uv) {
     const uchar4* texD = (const uchar4*)(sc.texData2D + tex.memOffset);
     const uchar4 c00 = __ldg(texD + x0 + y0 * tw), c10 = __ldg(texD + x1 + y0 * tw);
     const uchar4 c01 = __ldg(texD + x0 + y1 * tw), c11 = __ldg(texD + x1 + y1 * tw);
-    const float4 v00 = make_float4(c00.x, c00.y, c00.z, c00.w), v10 = make_float4(c10.x, c10.y, c10.z, c10.w);
-    const float4 v01 = make_float4(c01.x, c01.y, c01.z, c01.w), v11 = make_float4(c11.x, c11.y, c11.z, c11.w);
+    const float4 v00 = texel_to_float4(c00), v10 = texel_to_float4(c10);
+    const float4 v01 = texel_to_float4(c01), v11 = texel_to_float4(c11);
     const float4 r = mix4(mix4(v00, v10, tx), mix4(v01, v11, tx), ty);
     const float k = 1.0f / 255.0f;
     return make_float4(r.x * k, r.y * k, r.z * k, r.w * k);

@@ -32,8 +32,17 @@ struct ShadeOut {
     int bsdfFlags;
 };
 
-HD void shade_vertex(const Scene& sc, const ShadeIn& in, int frame, int width, int height, int bounce, int maxDepth,
-                     ShadeOut* out) {
+// SYNC = true: the CTA's warps are kept in the same phase of this (very long) function with
+// __syncthreads() so that they share the instruction stream in the SM's instruction cache; every
+// thread of the CTA must then call it, `active` telling whether it has a vertex to shade.
+template <bool SYNC>
+HD void phase_barrier() {
+    if (SYNC) __syncthreads();
+}
+
+template <bool SYNC>
+HD void shade_vertex(const Scene& sc, const ShadeIn& in, bool active, int frame, int width, int height, int bounce,
+                     int maxDepth, ShadeOut* out) {
     out->hasEmission = false;
     out->emitted = v3(0.0f);
     out->direct = v3(0.0f);
@@ -43,48 +52,62 @@ HD void shade_vertex(const Scene& sc, const ShadeIn& in, int frame, int width, i
     V3 throughput = bounce == 0 ? v3(1.0f) : in.throughput;
     out->throughput = throughput;
 
-    RTInteraction si = computeSurfaceInteraction(sc, in.shapeId, in.primId, in.bu, in.bv);
-    si.wo = -in.rayDir;
-    const bool isBackfacing = dot(si.gn, si.wo) < 0.0f;
-    si.traceErrorOffset = isBackfacing ? -RT_TRACE_OFFSET : RT_TRACE_OFFSET;
-    const RTShape* shape = sc.shapes + in.shapeId;
-    const int materialId = shape->materialId;
-    applyNormalMapping(sc, materialId, &si);
-
-    const int lightID = shape->lightID;
-    const bool isEmitter = lightID != RT_INVALID_ID;
-    const bool sampledSpecular = (BSDF_SPECULAR & in.prevBsdfFlags) == BSDF_SPECULAR;
-    if (isEmitter && (bounce == 0 || sampledSpecular)) {
-        V3 Le = evalLightLe(sc.lights + lightID, si.gn, si.wo);
-        out->emitted = throughput * Le;
-        out->hasEmission = true;
-        return;
+    RTInteraction si;
+    int materialId = RT_INVALID_ID, lightID = RT_INVALID_ID;
+    if (active) {
+        si = computeSurfaceInteraction(sc, in.shapeId, in.primId, in.bu, in.bv);
+        si.wo = -in.rayDir;
+        const bool isBackfacing = dot(si.gn, si.wo) < 0.0f;
+        si.traceErrorOffset = isBackfacing ? -RT_TRACE_OFFSET : RT_TRACE_OFFSET;
+        const RTShape* shape = sc.shapes + in.shapeId;
+        materialId = shape->materialId;
+        lightID = shape->lightID;
     }
+    phase_barrier<SYNC>();
+    if (active) applyNormalMapping(sc, materialId, &si);
+
+    if (active) {
+        const bool isEmitter = lightID != RT_INVALID_ID;
+        const bool sampledSpecular = (BSDF_SPECULAR & in.prevBsdfFlags) == BSDF_SPECULAR;
+        if (isEmitter && (bounce == 0 || sampledSpecular)) {
+            V3 Le = evalLightLe(sc.lights + lightID, si.gn, si.wo);
+            out->emitted = throughput * Le;
+            out->hasEmission = true;
+            active = false;      // the path ends here (PathTracing.cl:91-101)
+        }
+    }
+    phase_barrier<SYNC>();
 
     Sampler sampler = makeSampler(in.pixel, frame, width, height, bounce);
     UberProps um;
     const bool hasMaterial = materialId != RT_INVALID_ID;
-    if (hasMaterial) getUberMaterialProperties(sc, materialId, &si, &um);
+    if (active && hasMaterial) getUberMaterialProperties(sc, materialId, &si, &um);
+    phase_barrier<SYNC>();
 
-    {   // direct lighting: one light, one sample (PathTracing.cl:106-134)
-        float lightPdf = 0.0f;
+    // direct lighting: one light, one sample (PathTracing.cl:106-134)
+    float lightPdf = 0.0f;
+    V3 wiL = v3(0.0f), Li = v3(0.0f);
+    if (active) {
         uint32_t lightIdx = ((uint32_t)floorf(getSample1D(&sampler) * sc.numLights));
         lightIdx %= (uint32_t)sc.numLights;
-        V3 wi = v3(0.0f);
         V2 u = getSample2D(&sampler);
         V3 unusedN, unusedP;
-        V3 Li = sampleLightLi((int)lightIdx, sc, &si, u, &unusedP, &unusedN, &wi, &lightPdf, &out->shadow);
+        Li = sampleLightLi((int)lightIdx, sc, &si, u, &unusedP, &unusedN, &wiL, &lightPdf, &out->shadow);
         lightPdf *= sc.lights[lightIdx].choicePdf;
+    }
+    phase_barrier<SYNC>();
+    if (active) {
         V3 L = v3(0.0f);
         if (hasMaterial) {
-            V3 bsdf = evaluateUberBSDF(um, &si, si.wo, wi, TRANSPORT_MODE_RADIANCE);
-            bsdf *= absDot(wi, si.sn);
+            V3 bsdf = evaluateUberBSDF(um, &si, si.wo, wiL, TRANSPORT_MODE_RADIANCE);
+            bsdf *= absDot(wiL, si.sn);
             if (!isNearZero(lightPdf)) L = Li * bsdf / lightPdf;
         }
         out->direct = throughput * L;
     }
+    phase_barrier<SYNC>();
 
-    if (bounce + 1 < maxDepth) {   // extend the path (PathTracing.cl:137-172)
+    if (active && bounce + 1 < maxDepth) {   // extend the path (PathTracing.cl:137-172)
         V2 bsdfSample = getSample2D(&sampler);
         if (hasMaterial) {
             float pdf = 0.0f;

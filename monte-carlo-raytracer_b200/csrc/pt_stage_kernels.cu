@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(128) k_pt_shade_aos(PtState s, int frame, int 
         in.throughput = v3(tp->throughput);
         in.prevBsdfFlags = tp->prevBsdfFlags;
         ShadeOut out;
-        shade_vertex(sc, in, frame, s.width, s.height, bounce, maxDepth, &out);
+        shade_vertex<false>(sc, in, true, frame, s.width, s.height, bounce, maxDepth, &out);
         if (bounce == 0) tp->throughput = make_float4(1.f, 1.f, 1.f, tp->throughput.w);
         if (out.hasEmission) {
             radiance = make_float4(out.emitted.x, out.emitted.y, out.emitted.z, 0.f);

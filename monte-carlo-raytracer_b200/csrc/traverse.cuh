@@ -41,7 +41,7 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
 __device__ __forceinline__ uint32_t extract_byte(uint32_t x, uint32_t i) { return (x >> (i * 8)) & 0xffu; }
 
 __device__ __forceinline__ float safe_inv(float d) {
-    return 1.0f / (fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d));
+    return __fdiv_rn(1.0f, fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d));
 }
 
 // fp32 helpers that the compiler may not contract into FMAs
