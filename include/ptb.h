@@ -81,6 +81,11 @@ int ptb_destroy(ptb_context* ctx);
 int ptb_upload_scene(ptb_context* ctx, const ptb_scene_desc* scene);
 /* PathTracerSettings::GI.imageResolution; (re)allocates every per-pixel buffer, zero-filled. */
 int ptb_resize(ptb_context* ctx, int width, int height);
+/* Sampler variant (samplers.cl:15-17,75-84; a compile-time switch in the reference): kind 0 = Sobol,
+ * 1 = random (default).  `matrices` (may be NULL to keep the table uploaded with the scene) holds
+ * num_dimensions x 52 uint32 generator-matrix columns in the layout of sampling/sobol.h:31-34.  A frame
+ * uses at most 5 dimensions per bounce in PT and 3 * maxDepth + 5 in BDPT. */
+int ptb_set_sampler(ptb_context* ctx, int kind, const uint32_t* matrices, int num_dimensions);
 /* WriteBuffer(camera) of RTPrimaryRaysPass.cpp:106-107 / RTBDPTPass.cpp:168-169: 176 bytes. */
 int ptb_set_camera(ptb_context* ctx, const void* rt_pinhole_camera);
 /* Multi-GPU image partition: this context renders only pixels whose 64x64 tile index t satisfies

@@ -289,7 +289,7 @@ k_bdpt_start(PtState s, BdptState b, const uint32_t* __restrict__ pixels, int n,
     b.cam_beta[px] = make_float4(1.0f, 1.0f, 1.0f, pdfDir);
 
     // light ray and vertex
-    Sampler sampler = makeSampler((int)px, frame, s.width, s.height, 0);
+    Sampler sampler = makeSampler(sc.sobolMatrices, (int)px, frame, s.width, s.height, 0);
     const int chosen = (int)(((uint32_t)floorf(getSample1D(&sampler) * sc.numLights)) % (uint32_t)sc.numLights);
     const float lightPdf = sc.lights[chosen].choicePdf;
     const V2 u1 = getSample2D(&sampler);
@@ -428,7 +428,7 @@ k_bdpt_extend(PtState s, BdptState b, int cur, int frame, int curDepth) {
                 if (curDepth == maxDepth + (IS_CAMERA ? 1 : 0)) {              // last vertex (:387-394)
                     if (hasMaterialNonDeltaComponents(sc, materialIdx, &si)) v.flags |= VF_CONNECTIBLE;
                 } else {
-                    Sampler sampler = makeSampler((int)px, frame, s.width, s.height,
+                    Sampler sampler = makeSampler(sc.sobolMatrices, (int)px, frame, s.width, s.height,
                                                   curDepth + (maxDepth + 1) * (IS_CAMERA ? 1 : 0));
                     const V2 bsdfSample = getSample2D(&sampler);
                     UberProps um;
@@ -557,14 +557,10 @@ k_bdpt_prepare(PtState s, BdptState b, const uint32_t* __restrict__ pixels, int 
                 // next-event estimation at camera vertex t-1 with a fresh light sample (:563-597)
                 const BVertex cv = load_vertex<3>(vptr(b.cam_vertices, P, t - 1, px));
                 if (vConnectible(cv)) {
-                    Sampler sampler = makeSampler((int)px, frame, s.width, s.height, (D + 1) + (D + 2));
+                    Sampler sampler = makeSampler(sc.sobolMatrices, (int)px, frame, s.width, s.height, (D + 1) + (D + 2));
                     for (int j = 1; j <= t - 2; ++j) {      // draws of the connectible camera vertices before this one
                         const int tf = __float_as_int(vptr(b.cam_vertices, P, j, px)[0].z);
-                        if (((tf >> 8) & VF_CONNECTIBLE) != 0) {
-                            randUInt(&sampler.idx);
-                            randUInt(&sampler.idx);
-                            randUInt(&sampler.idx);
-                        }
+                        if (((tf >> 8) & VF_CONNECTIBLE) != 0) skipSamples(&sampler, 3);
                     }
                     const int chosen = min((int)floorf(getSample1D(&sampler) * sc.numLights), sc.numLights - 1);
                     const float lightPdf = sc.lights[chosen].choicePdf;

@@ -23,6 +23,7 @@ struct PtState {
     const void* lights;
     const void* materials;
     const void* camera;
+    const uint32_t* sobol;   // Sobol generator matrices when that sampler is selected, else NULL
     int numLights;
     int width, height;
     // acceleration structure

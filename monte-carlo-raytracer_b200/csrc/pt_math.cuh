@@ -140,21 +140,56 @@ HD uint32_t randUInt(uint32_t* seed) {
 // (float)u / 0xffffffff: the divisor converts to 2^32 in fp32, so 1.0f can be returned (E6)
 HD float randFloat(uint32_t* seed) { return ((float)randUInt(seed)) / 4294967296.0f; }
 
-// samplers.cl:83-84, random variant; all arithmetic wraps in 32 bits (E14).  `bufferIdx`, `width`
-// and `height` are the GLOBAL pixel index and image size on every rank.
+// Sampler (samplers.cl:19-25,75-128).  The reference picks the variant at compile time
+// (RT_SAMPLER, random by default); here it is a run-time choice: `sobol` == NULL selects the random
+// variant.  All index arithmetic wraps in 32 bits (E14); `bufferIdx`, `width` and `height` are the
+// GLOBAL pixel index and image size on every rank.
+#define SOBOL_MATRIX_SIZE 52
 struct Sampler {
     uint32_t idx;
+    uint32_t dimension;
+    uint32_t scramble;
+    const uint32_t* sobol;
 };
-HD Sampler makeSampler(int bufferIdx, int frame, int width, int height, int offset) {
+// random:  idx = wang_hash(bufferIdx + (frame+1) * W * H * (offset+1))                       (:83-84)
+// Sobol:   idx = bufferIdx + frame * W * H, dimension 0, scramble = xorshift(wang_hash((frame+1)*(offset+1)))  (:75-80)
+HD Sampler makeSampler(const uint32_t* sobol, int bufferIdx, int frame, int width, int height, int offset) {
     Sampler s;
-    s.idx = wang_hash((uint32_t)bufferIdx + (uint32_t)(frame + 1) * (uint32_t)width * (uint32_t)height * (uint32_t)(offset + 1));
+    s.sobol = sobol;
+    s.dimension = 0;
+    s.scramble = 0;
+    if (sobol) {
+        s.idx = (uint32_t)bufferIdx + (uint32_t)frame * (uint32_t)width * (uint32_t)height;
+        uint32_t seed = wang_hash((uint32_t)(frame + 1) * (uint32_t)(offset + 1));
+        s.scramble = randUInt(&seed);
+    } else {
+        s.idx = wang_hash((uint32_t)bufferIdx + (uint32_t)(frame + 1) * (uint32_t)width * (uint32_t)height * (uint32_t)(offset + 1));
+    }
     return s;
 }
-HD float getSample1D(Sampler* s) { return randFloat(&s->idx); }
+// samplers.cl:64-72: v * 0x1p-32f
+HD float sobolSample(uint32_t idx, uint32_t dimension, uint32_t scramble, const uint32_t* __restrict__ m) {
+    uint32_t v = scramble;
+    for (uint32_t i = dimension * SOBOL_MATRIX_SIZE; idx != 0; idx >>= 1, ++i)
+        if (idx & 1u) v ^= __ldg(m + i);
+    return (float)v * 2.3283064365386963e-10f;
+}
+HD float getSample1D(Sampler* s) {
+    if (s->sobol) return sobolSample(s->idx, s->dimension++, s->scramble, s->sobol);
+    return randFloat(&s->idx);
+}
 HD V2 getSample2D(Sampler* s) {
-    float a = randFloat(&s->idx);
-    float b = randFloat(&s->idx);
+    float a = getSample1D(s);
+    float b = getSample1D(s);
     return v2(a, b);
+}
+// advance past n one-dimensional draws without using them
+HD void skipSamples(Sampler* s, int n) {
+    if (s->sobol) {
+        s->dimension += (uint32_t)n;
+    } else {
+        for (int i = 0; i < n; ++i) randUInt(&s->idx);
+    }
 }
 
 // ------------------------------------------------------------------ sampling (samplers.cl:129-285)

@@ -65,6 +65,7 @@ struct Scene {              // kernel_data.h:353-370 (device pointers)
     const RTLight* __restrict__ lights;
     const RTMaterial* __restrict__ materials;
     const RTPinholeCamera* __restrict__ camera;
+    const uint32_t* __restrict__ sobolMatrices;   // NULL = random sampler
     int numLights;
 };
 

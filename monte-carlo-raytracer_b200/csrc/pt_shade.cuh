@@ -78,7 +78,7 @@ HD void shade_vertex(const Scene& sc, const ShadeIn& in, bool active, int frame,
     }
     phase_barrier<SYNC>();
 
-    Sampler sampler = makeSampler(in.pixel, frame, width, height, bounce);
+    Sampler sampler = makeSampler(sc.sobolMatrices, in.pixel, frame, width, height, bounce);
     UberProps um;
     const bool hasMaterial = materialId != RT_INVALID_ID;
     if (active && hasMaterial) getUberMaterialProperties(sc, materialId, &si, &um);

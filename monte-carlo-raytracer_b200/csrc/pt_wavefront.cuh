@@ -20,6 +20,7 @@ __device__ __forceinline__ Scene make_scene(const PtState& s) {
     sc.lights = (const RTLight*)s.lights;
     sc.materials = (const RTMaterial*)s.materials;
     sc.camera = (const RTPinholeCamera*)s.camera;
+    sc.sobolMatrices = s.sobol;
     sc.numLights = s.numLights;
     return sc;
 }

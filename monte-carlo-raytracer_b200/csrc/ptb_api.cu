@@ -51,6 +51,9 @@ struct ptb_context {
     int n_pixels = 0;
     int bdpt_depth = -1;
     int64_t launches = 0;
+    int sampler_kind = 1;                         // RT_SAMPLER_RANDOM (samplers.cl:17)
+    const uint32_t* d_sobol = nullptr;
+    int sobol_dims = 0;
     bool profiling = false;
     mcrt::StageTimer timer;
     ptb_context() {
@@ -102,6 +105,22 @@ int upload(ptb_context* c, const std::string& name, const void* src, size_t byte
         if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("cudaMemcpyAsync: ") + cudaGetErrorString(e));
     }
     *out = p;
+    return 0;
+}
+
+// The Sobol table outlives scene uploads (it is not scene data); owned by the context.
+int set_sobol_table(ptb_context* c, const uint32_t* matrices, int num_dimensions) {
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->d_sobol) cudaFree((void*)c->d_sobol);
+    c->d_sobol = nullptr;
+    void* p = nullptr;
+    const size_t bytes = (size_t)num_dimensions * 52 * 4;
+    PTB_CUDA(cudaMalloc(&p, bytes));
+    PTB_CUDA(cudaMemcpyAsync(p, matrices, bytes, cudaMemcpyHostToDevice, c->stream));
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    c->d_sobol = (const uint32_t*)p;
+    c->sobol_dims = num_dimensions;
+    if (c->sampler_kind == 0) c->st.sobol = c->d_sobol;
     return 0;
 }
 
@@ -196,6 +215,7 @@ int ptb_destroy(ptb_context* c) {
         if (it != c->named.end() && it->second.p) cudaFree(it->second.p);
     }
     if (c->d_pixels) cudaFree(c->d_pixels);
+    if (c->d_sobol) cudaFree((void*)c->d_sobol);
     c->timer.destroy();
     delete c;
     return 0;
@@ -228,8 +248,24 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
     if ((rc = upload(c, "materials", d->materials, (size_t)d->num_materials * 128, &p))) return rc;
     c->st.materials = p;
     c->st.numLights = d->num_lights;
+    if (d->sobol && (rc = set_sobol_table(c, d->sobol, 1024))) return rc;   // the engine's table (scene/RTScene.cpp:55)
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->scene_loaded = true;
+    return 0;
+}
+
+int ptb_set_sampler(ptb_context* c, int kind, const uint32_t* matrices, int num_dimensions) {
+    if (!c || (kind != 0 && kind != 1)) return pfail(RRB_ERROR_INVALID_ARGUMENT, "sampler kind must be 0 (Sobol) or 1 (random)");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    if (matrices) {
+        if (num_dimensions < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "num_dimensions must be >= 1");
+        if ((rc = set_sobol_table(c, matrices, num_dimensions))) return rc;
+    }
+    if (kind == 0 && !c->d_sobol) return pfail(RRB_ERROR_INVALID_ARGUMENT, "the Sobol sampler needs its generator matrices");
+    c->sampler_kind = kind;
+    c->st.sobol = kind == 0 ? c->d_sobol : nullptr;
     return 0;
 }
 

@@ -62,6 +62,7 @@ def _lib():
             "ptb_get_buffer": [vp, ctypes.c_char_p, pp, ctypes.POINTER(sz)],
             "ptb_read_buffer": [vp, ctypes.c_char_p, vp, sz], "ptb_synchronize": [vp],
             "ptb_get_counters": [vp, ctypes.POINTER(PtbCounters)], "ptb_reset_counters": [vp],
+            "ptb_set_sampler": [vp, i, vp, i],
             "ptb_profile_enable": [vp, ctypes.c_int],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
                                     ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
@@ -233,6 +234,14 @@ class RenderPipeline:
 
     def set_partition(self, part, num_parts):
         _check(_lib().ptb_set_partition(self.scene._h, int(part), int(num_parts)))
+
+    def set_sampler(self, kind, matrices=None):
+        """samplers.cl:15-17: kind 0 = Sobol (needs the generator matrices, sobol.matrices()), 1 = random."""
+        n = 0
+        if matrices is not None:
+            matrices = np.ascontiguousarray(matrices, np.uint32)
+            n = matrices.size // 52
+        _check(_lib().ptb_set_sampler(self.scene._h, int(kind), _ptr(matrices), n))
 
 
 class RenderPass:

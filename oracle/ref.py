@@ -32,12 +32,13 @@ class RefSceneDesc(ctypes.Structure):
                 ("texdata_bytes", ctypes.c_int64)]
 
 
-def lib_path(fast: bool = False) -> str:
-    return os.path.join(_HERE, "_ref", "libmcrt_ref_fast.so" if fast else "libmcrt_ref.so")
+def lib_path(fast: bool = False, sobol: bool = False) -> str:
+    name = "libmcrt_ref_sobol.so" if sobol else ("libmcrt_ref_fast.so" if fast else "libmcrt_ref.so")
+    return os.path.join(_HERE, "_ref", name)
 
 
-def available(fast: bool = False) -> bool:
-    return os.path.exists(lib_path(fast))
+def available(fast: bool = False, sobol: bool = False) -> bool:
+    return os.path.exists(lib_path(fast, sobol))
 
 
 def _ptr(a):
@@ -47,8 +48,10 @@ def _ptr(a):
 class RefOracle:
     """The compiled reference, one NDRange per call."""
 
-    def __init__(self, fast: bool = False):
-        self.lib = ctypes.CDLL(lib_path(fast))
+    def __init__(self, fast: bool = False, sobol_table=None):
+        """sobol_table: uint32 generator matrices -> the Sobol-sampler build of the kernels is used."""
+        self.sobol_table = None if sobol_table is None else np.ascontiguousarray(sobol_table, np.uint32)
+        self.lib = ctypes.CDLL(lib_path(fast, self.sobol_table is not None))
         lib = self.lib
         lib.ref_rr_world_create.restype = ctypes.c_void_p
         lib.ref_rr_world_destroy.argtypes = [ctypes.c_void_p]
@@ -116,7 +119,7 @@ class RefOracle:
         d = RefSceneDesc()
         d.shapes, d.indices, d.positions = _ptr(scene.shapes), _ptr(scene.indices), _ptr(scene.positions)
         d.uvs, d.normals = _ptr(scene.uvs), _ptr(scene.normals)
-        d.textures, d.texdata, d.sobol = _ptr(scene.textures), _ptr(scene.texdata), None
+        d.textures, d.texdata, d.sobol = _ptr(scene.textures), _ptr(scene.texdata), _ptr(self.sobol_table)
         d.lights, d.materials, d.camera = _ptr(scene.lights), _ptr(scene.materials), _ptr(camera)
         d.num_shapes, d.num_textures = len(scene.shapes), len(scene.textures)
         d.num_lights, d.num_materials = len(scene.lights), len(scene.materials)

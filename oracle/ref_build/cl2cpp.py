@@ -13,6 +13,9 @@ purely mechanical -- no arithmetic, control flow or constant is touched:
   2. `#ifdef __cplusplus` in kernel_data.h -> `#ifdef MCRT_REF_HOST_BRANCH` so that the
      OpenCL branch of that shared header (the device-side struct layouts) is the one compiled.
   3. `#include <../RadeonRays/src/kernels/CL/common.cl>` -> `#include "common.cl"`.
+  4. samplers.cl's compile-time sampler choice `#define RT_SAMPLER RT_SAMPLER_RANDOM` is wrapped in
+     `#ifndef RT_SAMPLER` so the Sobol variant of the same source can be built with -DRT_SAMPLER=0
+     (the reference selects it by editing that line).
 
 Everything else (swizzles, address-space qualifiers, builtins) is supplied by clshim.hpp.
 """
@@ -46,6 +49,8 @@ def rewrite(text: str) -> str:
     text = rewrite_literals(text)
     text = text.replace("#ifdef __cplusplus", "#ifdef MCRT_REF_HOST_BRANCH")
     text = text.replace("#include <../RadeonRays/src/kernels/CL/common.cl>", '#include "common.cl"')
+    text = re.sub(r"^#define RT_SAMPLER RT_SAMPLER_RANDOM\s*$",
+                  "#ifndef RT_SAMPLER\n#define RT_SAMPLER RT_SAMPLER_RANDOM\n#endif", text, flags=re.M)
     return text
 
 

@@ -133,3 +133,27 @@ def test_bdpt_tile_partition_sums_to_full_frame(cornell):
     parts = [gpu_frames(cornell, w, h, 4, 1, partition=(p, 2))[0][0] for p in range(2)]
     merged = parts[0] + parts[1]
     assert np.allclose(merged[:, :3], full[0][:, :3], rtol=1e-5, atol=1e-6)
+
+
+def test_bdpt_sobol_sampler_variant_vs_reference(cornell):
+    from mcrt_b200 import sobol
+    if not ref.available(sobol=True):
+        pytest.skip("oracle/_ref Sobol variant not built")
+    table = sobol.matrices()
+    w = h = 64
+    api = rr.IntersectionApi.Create(0)
+    try:
+        pl = pt.make_bdpt_pipeline(api, cornell, w, h, 3)
+        pl.set_sampler(sobol.RT_SAMPLER_SOBOL, table)
+        got = []
+        for _ in range(2):
+            pl.update()
+            got.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+        pl.scene.destroy()
+    finally:
+        rr.IntersectionApi.Delete(api)
+    o = ref.RefOracle(sobol_table=table)
+    rb = ref.RefBDPT(o, cornell, o.build_scene_bvh(cornell), w, h, 3)
+    for f in range(2):
+        cam = camera.make_camera(cornell.camera, w, h, camera.taa_pixel_offset(f))
+        check(got[f], rb.render_sample(cam, f), 0.97)

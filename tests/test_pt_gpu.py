@@ -174,3 +174,36 @@ def test_textured_normal_mapped_scene_vs_reference(api):
     want, _ = ref_frames(scene, w, h, 5, 2)
     for f in range(2):
         check_against(got[f], want[f], 0.97)
+
+
+def test_sobol_sampler_variant_vs_reference(api, cornell):
+    """samplers.cl's other compile-time variant (RT_SAMPLER_SOBOL): the compiled reference built with
+    -DRT_SAMPLER=0 against the run-time switch ptb_set_sampler, same generator matrices."""
+    from mcrt_b200 import sobol
+    if not ref.available(sobol=True):
+        pytest.skip("oracle/_ref Sobol variant not built")
+    table = sobol.matrices()
+    w = h = 96
+    pl = pt.make_pt_pipeline(api, cornell, w, h, 4)
+    pl.set_sampler(sobol.RT_SAMPLER_SOBOL, table)
+    got = []
+    for _ in range(3):
+        pl.update()
+        got.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+    pl.set_sampler(sobol.RT_SAMPLER_RANDOM)
+    pl.update()
+    rnd = pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy()
+    pl.scene.destroy()
+    o = ref.RefOracle(sobol_table=table)
+    rp = ref.RefPathTracer(o, cornell, o.build_scene_bvh(cornell), w, h)
+    for f in range(3):
+        cam = camera.make_camera(cornell.camera, w, h, camera.taa_pixel_offset(f))
+        check_against(got[f], rp.render_sample(cam, f, 4), 0.995)
+    # and it is a different estimate from the random sampler's frame 3
+    assert not np.array_equal(rnd, got[2])
+    with pytest.raises(pt.PathTracerError):
+        pl2 = pt.make_pt_pipeline(api, cornell, 32, 32, 2)
+        try:
+            pl2.set_sampler(sobol.RT_SAMPLER_SOBOL)      # no table given
+        finally:
+            pl2.scene.destroy()
