@@ -207,3 +207,51 @@ def test_sobol_sampler_variant_vs_reference(api, cornell):
             pl2.set_sampler(sobol.RT_SAMPLER_SOBOL)      # no table given
         finally:
             pl2.scene.destroy()
+
+
+def test_all_five_pixel_filters_vs_reference_reconstruction_kernel(api, cornell):
+    """ReconstructionPass with box / triangle / Gaussian / Mitchell / Lanczos-sinc filters (filters.cl:12-69)
+    against the reference's own ReconstructionPassAllFilters kernel compiled for the host: the per-sample
+    radiance comes from the CUDA path, both accumulate it over 4 jittered frames."""
+    import ctypes
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    lib = ref.RefOracle().lib
+    lib.ref_reconstruction_all_filters.argtypes = [ctypes.c_int] * 3 + [ctypes.c_void_p] * 4
+    w, h, frames = 64, 48, 4
+    P = w * h
+    images = {}
+    samples = None
+    for ftype in range(5):
+        a2 = rr.IntersectionApi.Create(0)
+        try:
+            pl = pt.make_pt_pipeline(a2, cornell, w, h, 3)
+            pl.GI.filterType = ftype
+            rad = []
+            for _ in range(frames):
+                pl.update()
+                rad.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+            images[ftype] = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+            props0 = pl.GI.filter_props()
+            pl.scene.destroy()
+        finally:
+            rr.IntersectionApi.Delete(a2)
+        if samples is None:
+            samples = rad
+        else:      # the filter only changes the weights, never the samples
+            assert all(np.array_equal(x, y) for x, y in zip(samples, rad))
+    weighted = np.zeros((5 * P, 4), np.float32)
+    weights = np.zeros(5 * P, np.float32)
+    for f in range(frames):
+        ox, oy = camera.taa_pixel_offset(f)
+        props = np.array([props0.radius[0], props0.radius[1], props0.mitchell_b, props0.mitchell_c,
+                          props0.lanczos_sinc_tau, props0.gaussian_alpha, props0.gaussian_exp_x, props0.gaussian_exp_y,
+                          ox, oy], np.float32)
+        r = samples[f].copy()
+        lib.ref_reconstruction_all_filters(w, h, f, props.ctypes.data, r.ctypes.data, weighted.ctypes.data,
+                                           weights.ctypes.data)
+    for ftype in range(5):
+        want = weighted[ftype * P:(ftype + 1) * P] / weights[ftype * P:(ftype + 1) * P, None]
+        ok = np.isfinite(want).all(axis=1)      # a filter whose weights sum to 0 gives 0/0 in both
+        assert ok.mean() > 0.99
+        assert np.allclose(images[ftype][ok, :3], want[ok, :3], rtol=2e-6, atol=1e-7), ftype
