@@ -121,6 +121,15 @@ int ptb_profile_collect(ptb_context* ctx, double* ms_closest, double* ms_shade, 
 int ptb_accumulate(ptb_context* ctx, int frame, const ptb_filter_props* filter);
 int ptb_reset_accumulation(ptb_context* ctx);
 
+/* Post-processing on float4[P] buffers named as in ptb_get_buffer (the GL-interop images of the reference
+ * become device buffers; the display pass itself is out of scope).
+ *  ptb_denoise: BilateralDenoise (Denoise.cl:6-47, RTDenoisePass.cpp:33-75)   src -> "DenoisedImageCL";
+ *               radius <= 0 or a sigma <= 0 writes nothing, like the kernel's early return.
+ *  ptb_tonemap: ReinhardToneMapping (ToneMapping.cl:41-63, RTToneMappingPass.cpp:38-87; the host passes
+ *               GI.minLuminance as Lwhite)                                     src -> "TonemappedImageCL". */
+int ptb_denoise(ptb_context* ctx, const char* src_name, int radius, float sigma_spatial, float sigma_range);
+int ptb_tonemap(ptb_context* ctx, const char* src_name, float lwhite);
+
 int ptb_get_buffer(ptb_context* ctx, const char* name, void** device_ptr, size_t* bytes);
 /* Blocking device->host read of a named buffer (the step's result for the end-to-end leg). */
 int ptb_read_buffer(ptb_context* ctx, const char* name, void* host_dst, size_t bytes);

@@ -95,4 +95,10 @@ struct FilterProps {
 cudaError_t launch_accumulate(const PtState& s, const FilterProps& f, int frame, const uint32_t* pixels, int n_pixels,
                               cudaStream_t stream);
 
+// post-processing (postfx_kernels.cu)
+cudaError_t launch_bilateral_denoise(int width, int height, int radius, float sigmaSpatial, float sigmaRange,
+                                     const float4* src, float4* dst, cudaStream_t stream);
+cudaError_t launch_reinhard_tonemap(int width, int height, float Lwhite, const float4* src, float4* dst,
+                                    cudaStream_t stream);
+
 }  // namespace mcrt

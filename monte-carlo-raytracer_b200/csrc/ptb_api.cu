@@ -51,6 +51,8 @@ struct ptb_context {
     int n_pixels = 0;
     int bdpt_depth = -1;
     int64_t launches = 0;
+    float4* denoised = nullptr;                   // RTDenoisePass / RTToneMappingPass outputs
+    float4* tonemapped = nullptr;
     int sampler_kind = 1;                         // RT_SAMPLER_RANDOM (samplers.cl:17)
     const uint32_t* d_sobol = nullptr;
     int sobol_dims = 0;
@@ -309,6 +311,8 @@ int ptb_resize(ptb_context* c, int width, int height) {
         {"weighted_radiance", 16, (void**)&s.weighted_radiance, "WeightedRadianceBuffer"},
         {"filter_weights", 4, (void**)&s.filter_weights, "FilterWeightsBuffer"},
         {"image", 16, (void**)&s.image, "NextFrameImageCL"},
+        {"denoised", 16, (void**)&c->denoised, "DenoisedImageCL"},
+        {"tonemapped", 16, (void**)&c->tonemapped, "TonemappedImageCL"},
     };
     for (const Spec& sp : specs) {
         void* p = nullptr;
@@ -484,6 +488,42 @@ int ptb_accumulate(ptb_context* c, int frame, const ptb_filter_props* f) {
     fp.pixel_offset[0] = f->pixel_offset[0];
     fp.pixel_offset[1] = f->pixel_offset[1];
     PTB_CUDA(mcrt::launch_accumulate(c->st, fp, frame, c->d_pixels, c->n_pixels, c->stream));
+    c->launches += 1;
+    return 0;
+}
+
+namespace {
+int named_image(ptb_context* c, const char* name, float4** out) {
+    auto it = c->named.find(name ? name : "");
+    const size_t P = (size_t)c->width * c->height;
+    if (it == c->named.end() || it->second.bytes != P * 16)
+        return pfail(RRB_ERROR_INVALID_ARGUMENT, std::string("not a float4[P] image buffer: ") + (name ? name : "(null)"));
+    *out = (float4*)it->second.p;
+    return 0;
+}
+}  // namespace
+
+int ptb_denoise(ptb_context* c, const char* src_name, int radius, float sigma_spatial, float sigma_range) {
+    int rc = ready(c);
+    if (rc) return rc;
+    float4* src = nullptr;
+    if ((rc = named_image(c, src_name, &src))) return rc;
+    if (src == c->denoised) return pfail(RRB_ERROR_INVALID_ARGUMENT, "denoise cannot run in place");
+    if (radius > 32) return pfail(RRB_ERROR_INVALID_ARGUMENT, "denoise radius > 32");
+    cudaError_t e = mcrt::launch_bilateral_denoise(c->width, c->height, radius, sigma_spatial, sigma_range, src,
+                                                   c->denoised, c->stream);
+    if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("denoise launch: ") + cudaGetErrorString(e));
+    c->launches += 1;
+    return 0;
+}
+
+int ptb_tonemap(ptb_context* c, const char* src_name, float lwhite) {
+    int rc = ready(c);
+    if (rc) return rc;
+    float4* src = nullptr;
+    if ((rc = named_image(c, src_name, &src))) return rc;
+    cudaError_t e = mcrt::launch_reinhard_tonemap(c->width, c->height, lwhite, src, c->tonemapped, c->stream);
+    if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("tonemap launch: ") + cudaGetErrorString(e));
     c->launches += 1;
     return 0;
 }

@@ -63,6 +63,8 @@ def _lib():
             "ptb_read_buffer": [vp, ctypes.c_char_p, vp, sz], "ptb_synchronize": [vp],
             "ptb_get_counters": [vp, ctypes.POINTER(PtbCounters)], "ptb_reset_counters": [vp],
             "ptb_set_sampler": [vp, i, vp, i],
+            "ptb_denoise": [vp, ctypes.c_char_p, i, ctypes.c_float, ctypes.c_float],
+            "ptb_tonemap": [vp, ctypes.c_char_p, ctypes.c_float],
             "ptb_profile_enable": [vp, ctypes.c_int],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
                                     ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
@@ -102,6 +104,13 @@ class GISettings:
         self.lanczosSincTau = 3.0
         self.gaussianAlpha = 1.0
         self.curPixelOffset = (0.0, 0.0)
+        # post-processing (PathTracingSettings.h:82-87)
+        self.denoiseKernelRadius = 1
+        self.bilateralDenoiseSigmaRange = 0.1
+        self.bilateralDenoiseSigmaSpatial = 1.0
+        self.useDenoise = False
+        self.useTonemapping = False
+        self.minLuminance = 2.0
 
     def filter_props(self) -> PtbFilterProps:
         f = PtbFilterProps()
@@ -336,6 +345,44 @@ class RTReconstructionPass(RenderPass):
         f = pl.GI.filter_props()
         _check(_lib().ptb_accumulate(pl.scene._h, pl.frameIndex - 1, ctypes.byref(f)))
         pl.put("NextFrameImageCL", pl.device_buffer("NextFrameImageCL")[0])
+        pl.put("NextFrameImageName", "NextFrameImageCL")
+
+
+class RTDenoisePass(RenderPass):
+    """RTDenoisePass::update (RTDenoisePass.cpp:33-75): bilateral filter of "NextFrameImageCL"; its output
+    replaces that blackboard entry for the passes after it."""
+
+    def update(self):
+        pl = self.m_renderPipeline
+        if not pl.GI.useDenoise or pl.fetch("NextFrameImageCL") is None:
+            return
+        src = pl.fetch("NextFrameImageName") or "NextFrameImageCL"
+        _check(_lib().ptb_denoise(pl.scene._h, src.encode(), int(pl.GI.denoiseKernelRadius),
+                                  float(pl.GI.bilateralDenoiseSigmaSpatial), float(pl.GI.bilateralDenoiseSigmaRange)))
+        pl.put("NextFrameImageCL", pl.device_buffer("DenoisedImageCL")[0])
+        pl.put("NextFrameImageName", "DenoisedImageCL")
+
+
+class RTToneMappingPass(RenderPass):
+    """RTToneMappingPass::applyReinhardToneMapping (RTToneMappingPass.cpp:38-87); GI.minLuminance is passed
+    as the kernel's Lwhite (:60)."""
+
+    def update(self):
+        pl = self.m_renderPipeline
+        if not pl.GI.useTonemapping or pl.fetch("NextFrameImageCL") is None:
+            return
+        src = pl.fetch("NextFrameImageName") or "NextFrameImageCL"
+        _check(_lib().ptb_tonemap(pl.scene._h, src.encode(), float(pl.GI.minLuminance)))
+        pl.put("NextFrameImageCL", pl.device_buffer("TonemappedImageCL")[0])
+        pl.put("NextFrameImageName", "TonemappedImageCL")
+
+
+def write_pfm(path, image, width, height):
+    """Headless stand-in for RTDisplayPass: dump a float4[P] buffer as a little-endian RGB PFM."""
+    rgb = np.asarray(image, np.float32).reshape(height, width, -1)[::-1, :, :3]
+    with open(path, "wb") as f:
+        f.write(b"PF\n%d %d\n-1.0\n" % (width, height))
+        f.write(np.ascontiguousarray(rgb, "<f4").tobytes())
 
 
 def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=True):
@@ -350,6 +397,7 @@ def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=T
         pl.addRenderPasses(RTPathTracingPass(True), RTReconstructionPass())
     else:
         pl.addRenderPasses(RTPrimaryRaysPass(), RTPathTracingPass(False), RTReconstructionPass())
+    pl.addRenderPasses(RTDenoisePass(), RTToneMappingPass())      # both off by default, as in the GUI
     return pl
 
 
@@ -378,5 +426,5 @@ def make_bdpt_pipeline(api, scene, width, height, max_depth, use_taa=True):
     gi.maxDepth = max_depth
     gi.useTAA = use_taa
     pl = RenderPipeline(rts, gi)
-    pl.addRenderPasses(RTBDPTPass(), RTReconstructionPass())
+    pl.addRenderPasses(RTBDPTPass(), RTReconstructionPass(), RTDenoisePass(), RTToneMappingPass())
     return pl

@@ -26,7 +26,8 @@ import sys
 REF = os.environ.get("MCRT_REFERENCE", "/root/reference")
 APP_KERNELS = ["PathTracing.cl", "BDPT.cl", "bxdfs.cl", "materials.cl", "lights.cl", "geometry.cl",
                "textures.cl", "samplers.cl", "rng.cl", "cameras.cl", "math.cl", "matrix.cl",
-               "image_samplers.cl", "kernel_data.h", "reconstruction.cl", "filters.cl"]
+               "image_samplers.cl", "kernel_data.h", "reconstruction.cl", "filters.cl", "ToneMapping.cl", "Denoise.cl",
+               "colors.cl"]
 RR_KERNELS = ["common.cl", "intersect_bvh2_lds.cl"]
 
 VEC_LITERAL = re.compile(r"\((float[234]|int[23]|uint2)\)\s*\(")

@@ -234,8 +234,19 @@ static inline uint atomic_cmpxchg(volatile uint* p, uint cmp, uint val) {
     return cmp;
 }
 
-// ---------------------------------------------------------------- images (only in out-of-scope kernels)
-typedef void* image2d_t;
+// component-wise log / exp on float4 (ToneMapping.cl's log-average kernels)
+static inline float4 log(float4 v) { return float4{logf(v.x), logf(v.y), logf(v.z), logf(v.w)}; }
+static inline float4 exp(float4 v) { return float4{expf(v.x), expf(v.y), expf(v.z), expf(v.w)}; }
+
+// ---------------------------------------------------------------- images
+// The reference's post-processing kernels (ToneMapping.cl, Denoise.cl) read and write GL-interop
+// image2d_t objects.  Here an image is a plain RGBA32F buffer; the only sampler those kernels use is
+// non-normalised / nearest / clamp-to-edge (image_samplers.cl).
+struct clshim_image {
+    float4* data;
+    int width, height;
+};
+typedef clshim_image* image2d_t;
 typedef int sampler_t;
 #define write_only
 #define read_only
@@ -243,6 +254,14 @@ typedef int sampler_t;
 #define CLK_ADDRESS_CLAMP_TO_EDGE 0
 #define CLK_ADDRESS_CLAMP 0
 #define CLK_FILTER_NEAREST 0
-static inline void write_imagef(image2d_t, int2, float4) {}
-static inline float4 read_imagef(image2d_t, sampler_t, int2) { return float4(); }
-static inline float4 read_imagef(image2d_t, int2) { return float4(); }
+static inline int get_image_width(image2d_t im) { return im->width; }
+static inline int get_image_height(image2d_t im) { return im->height; }
+static inline void write_imagef(image2d_t im, int2 p, float4 v) {
+    if (im && p.x >= 0 && p.y >= 0 && p.x < im->width && p.y < im->height) im->data[p.y * im->width + p.x] = v;
+}
+static inline float4 read_imagef(image2d_t im, sampler_t, int2 p) {
+    int x = p.x < 0 ? 0 : (p.x >= im->width ? im->width - 1 : p.x);
+    int y = p.y < 0 ? 0 : (p.y >= im->height ? im->height - 1 : p.y);
+    return im->data[y * im->width + x];
+}
+static inline float4 read_imagef(image2d_t im, int2 p) { return read_imagef(im, 0, p); }

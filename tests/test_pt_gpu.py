@@ -255,3 +255,40 @@ def test_all_five_pixel_filters_vs_reference_reconstruction_kernel(api, cornell)
         ok = np.isfinite(want).all(axis=1)      # a filter whose weights sum to 0 gives 0/0 in both
         assert ok.mean() > 0.99
         assert np.allclose(images[ftype][ok, :3], want[ok, :3], rtol=2e-6, atol=1e-7), ftype
+
+
+def test_denoise_and_tonemap_passes_vs_reference_kernels(api, cornell):
+    """RTDenoisePass + RTToneMappingPass on device buffers against the reference's BilateralDenoise /
+    ReinhardToneMapping kernels compiled for the host, chained like the reference pipeline
+    (reconstruction -> denoise -> tone map)."""
+    import ctypes
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    lib = ref.RefOracle().lib
+    lib.ref_bilateral_denoise.argtypes = [ctypes.c_int] * 3 + [ctypes.c_float] * 2 + [ctypes.c_void_p] * 2
+    lib.ref_reinhard_tonemap.argtypes = [ctypes.c_int] * 2 + [ctypes.c_float] + [ctypes.c_void_p] * 2
+    w, h = 100, 70      # not a multiple of the tile size: exercises the clamped halo
+    for radius in (1, 4):
+        a2 = rr.IntersectionApi.Create(0)
+        try:
+            pl = pt.make_pt_pipeline(a2, cornell, w, h, 3)
+            pl.GI.useDenoise, pl.GI.useTonemapping = True, True
+            pl.GI.denoiseKernelRadius = radius
+            pl.GI.bilateralDenoiseSigmaRange = 0.5
+            for _ in range(2):
+                pl.update()
+            img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+            den = pl.read_buffer("DenoisedImageCL").reshape(-1, 4).copy()
+            tm = pl.read_buffer("TonemappedImageCL").reshape(-1, 4).copy()
+            assert pl.fetch("NextFrameImageName") == "TonemappedImageCL"
+            pl.scene.destroy()
+        finally:
+            rr.IntersectionApi.Delete(a2)
+        want_den = np.zeros_like(img)
+        lib.ref_bilateral_denoise(w, h, radius, 1.0, 0.5, img.ctypes.data, want_den.ctypes.data)
+        assert np.allclose(den, want_den, rtol=1e-5, atol=1e-7)
+        want_tm = np.zeros_like(img)
+        lib.ref_reinhard_tonemap(w, h, 2.0, want_den.ctypes.data, want_tm.ctypes.data)
+        ok = np.isfinite(want_tm).all(axis=1)      # black pixels: tL / L = 0 / 0 in both
+        assert np.allclose(tm[ok], want_tm[ok], rtol=1e-5, atol=1e-7)
+        assert (np.isfinite(tm).all(axis=1) == ok).all()
