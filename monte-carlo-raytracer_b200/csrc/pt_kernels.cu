@@ -10,6 +10,8 @@
 // the device.
 #include "pt_kernels.h"
 
+#include <cstdlib>
+
 #include "pt_shade.cuh"
 #include "pt_wavefront.cuh"
 
@@ -192,14 +194,23 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
     }
 }
 
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
 int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int frame, int max_depth,
                      cudaStream_t stream, cudaError_t* err, StageTimer* timer) {
     int launches = 0;
     *err = cudaSuccess;
     if (n_pixels <= 0) return 0;
     const int sms = sm_count();
-    const int trace_blocks = min(sms * 8, (n_pixels + 127) / 128);
-    const int shade_blocks = min(sms * PT_SHADE_CTAS_PER_SM, (n_pixels + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK);
+    // CTAs per SM of the persistent kernels; the environment overrides exist for co-scheduling experiments
+    // (two contexts on two streams sharing the SMs) and are read once.
+    static const int trace_per_sm = env_int("MCRT_TRACE_CTAS_PER_SM", 8);
+    static const int shade_per_sm = env_int("MCRT_SHADE_CTAS_PER_SM", PT_SHADE_CTAS_PER_SM);
+    const int trace_blocks = min(sms * trace_per_sm, (n_pixels + 127) / 128);
+    const int shade_blocks = min(sms * shade_per_sm, (n_pixels + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK);
     k_raygen<<<(n_pixels + 255) / 256, 256, 0, stream>>>(s, pixels, n_pixels);
     ++launches;
     if (s.numLights > 0) {   // RTPathTracingPass::update returns early without lights (:42-43); PathTracing.cl:72

@@ -30,7 +30,9 @@ _CORNELL = {
         [(0.53, 0.00, 0.75), (0.53, 0.60, 0.75), (-0.05, 0.60, 0.57), (-0.05, 0.00, 0.57)],
         [(0.70, 0.00, 0.17), (0.70, 0.60, 0.17), (0.53, 0.60, 0.75), (0.53, 0.00, 0.75)],
         [(0.13, 0.00, 0.00), (0.13, 0.60, 0.00), (0.70, 0.60, 0.17), (0.70, 0.00, 0.17)],
-        [(0.53, 0.00, 0.75), (0.70, 0.00, 0.17), (0.13, 0.00, 0.00), (-0.05, 0.00, 0.57)],
+        # the file's "bottom face" is `f -12 -11 -10 -9`, which addresses the RIGHT face's vertices again
+        # (CornellBox-Original.obj:107): the imported box has that face twice and no bottom
+        [(0.70, 0.00, 0.17), (0.70, 0.60, 0.17), (0.53, 0.60, 0.75), (0.53, 0.00, 0.75)],
     ],
     "tallBox": [
         [(-0.53, 1.20, 0.09), (0.04, 1.20, -0.09), (-0.14, 1.20, -0.67), (-0.71, 1.20, -0.49)],
@@ -38,7 +40,8 @@ _CORNELL = {
         [(-0.71, 0.00, -0.49), (-0.71, 1.20, -0.49), (-0.14, 1.20, -0.67), (-0.14, 0.00, -0.67)],
         [(-0.14, 0.00, -0.67), (-0.14, 1.20, -0.67), (0.04, 1.20, -0.09), (0.04, 0.00, -0.09)],
         [(0.04, 0.00, -0.09), (0.04, 1.20, -0.09), (-0.53, 1.20, 0.09), (-0.53, 0.00, 0.09)],
-        [(-0.53, 0.00, 0.09), (0.04, 0.00, -0.09), (-0.14, 0.00, -0.67), (-0.71, 0.00, -0.49)],
+        # likewise `f -8 -7 -6 -5` (CornellBox-Original.obj:155) repeats the FRONT face
+        [(0.04, 0.00, -0.09), (0.04, 1.20, -0.09), (-0.53, 1.20, 0.09), (-0.53, 0.00, 0.09)],
     ],
     "light": [[(-0.24, 1.98, 0.16), (-0.24, 1.98, -0.22), (0.23, 1.98, -0.22), (0.23, 1.98, 0.16)]],
 }
