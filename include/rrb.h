@@ -76,7 +76,11 @@ int rrb_shape_set_linear_velocity(rrb_shape* shape, const float v[3]);   /* stor
 int rrb_shape_set_angular_velocity(rrb_shape* shape, const float q[4]); /* stored, no reachable consumer */
 
 /* ---- options: SetOption(char const*, char const*) / (char const*, float) (radeon_rays.h:279-296).
- * Unknown keys are stored and never an error (util/options.cpp). */
+ * Unknown keys are stored and never an error (util/options.cpp).
+ * Extension key (f32)  "bvh.refit" != 0 : rrb_commit keeps the tree topology and refits it on the device when the
+ *   attached shapes are those of the last full build and only transforms / ids changed (the reference always
+ *   rebuilds on the CPU, intersector_lds.cpp:166).  Device pointers returned by rrb_get_bvh stay valid across a
+ *   refit.  Set it before the first rrb_commit; rrb_stats.refits counts the commits served this way. */
 int rrb_set_option_str(rrb_api* api, const char* name, const char* value);
 int rrb_set_option_f32(rrb_api* api, const char* name, float value);
 
@@ -117,6 +121,8 @@ typedef struct rrb_stats {
     int64_t triangle_bytes;
     double build_seconds;       /* wall time of the last rrb_commit */
     int64_t launches;           /* traversal kernels launched since creation */
+    int64_t refits;             /* commits served by the device refit (option "bvh.refit") since creation */
+    int64_t last_commit_refit;  /* 1 when the last rrb_commit was a refit, 0 when it was a full build */
 } rrb_stats;
 int rrb_get_stats(rrb_api* api, rrb_stats* out);
 /* Instrumented query: per-ray visited-node and tested-triangle counts into int32[2*numrays]. */
@@ -135,6 +141,10 @@ int rrb_host_bvh_build(const float* vertices, int vnum, const int* indices, int 
                        int use_sah, rrb_host_bvh** out);
 int rrb_host_bvh_get(const rrb_host_bvh* bvh, const uint32_t** nodes, int64_t* num_nodes, const float** triangles,
                      int64_t* num_tris);
+/* Refit metadata of the build: mesh index (run of equal shape ids) of every emitted triangle, and the node index
+ * each breadth-first tree level starts at (num_levels + 1 entries). */
+int rrb_host_bvh_get_refit_info(const rrb_host_bvh* bvh, const int32_t** tri_mesh, const int32_t** level_offsets,
+                                int* num_levels);
 int rrb_host_bvh_free(rrb_host_bvh* bvh);
 
 #ifdef __cplusplus

@@ -43,6 +43,10 @@ struct Bvh8 {
     std::vector<float> triangles;      // 12 floats per triangle
     int64_t num_nodes = 0;
     int64_t num_tris = 0;
+    // for the device refit (rrb_kernels.cu: refit_bvh8): which input mesh each emitted triangle came from,
+    // and where each tree level starts in the node array (nodes are emitted breadth-first)
+    std::vector<int32_t> tri_mesh;        // [num_tris] index into the build's mesh list
+    std::vector<int32_t> level_offsets;   // [num_levels + 1]
     float scene_min[3] = {0, 0, 0};
     float scene_max[3] = {0, 0, 0};
 };

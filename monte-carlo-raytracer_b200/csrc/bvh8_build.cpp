@@ -220,12 +220,15 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
     if (total > (int64_t)0x3fffffff) throw std::runtime_error("too many triangles");
     const size_t N = (size_t)total;
     std::vector<float> tri(12 * N);
+    std::vector<int32_t> tri_mesh_in(N);
     Builder B(opt);
     B.pbox.resize(N);
     B.pcent.resize(3 * N);
     B.prim.resize(N);
     size_t t = 0;
+    int32_t mesh_index = -1;
     for (const auto& m : meshes) {
+        ++mesh_index;
         const int vstride = m.vstride ? m.vstride : 12;
         const int istride = m.istride ? m.istride : 12;
         for (int f = 0; f < m.numfaces; ++f, ++t) {
@@ -248,6 +251,7 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
             B.pbox[t] = b;
             for (int a = 0; a < 3; ++a) B.pcent[3 * t + a] = 0.5f * (b.lo[a] + b.hi[a]);
             B.prim[t] = (int)t;
+            tri_mesh_in[t] = mesh_index;
         }
     }
 
@@ -264,8 +268,11 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
     wide.reserve(N / 2 + 16);
     wide_src.push_back(root);
     wide.emplace_back();
+    std::vector<int> wide_depth(1, 0);
     out.nodes.clear();
     out.triangles.clear();
+    out.tri_mesh.clear();
+    out.tri_mesh.reserve(N);
     out.triangles.reserve(12 * N);
     std::vector<uint32_t>& W = out.nodes;
 
@@ -377,12 +384,14 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
                 imask |= (uint8_t)(1u << s);
                 meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
                 wide_src.push_back(ch[i]);
+                wide_depth.push_back(wide_depth[wi] + 1);
             } else {
                 static const uint8_t unary[4] = {0, 1, 3, 7};
                 meta[s] = (uint8_t)((unary[c.count] << 5) | (uint32_t)tri_off);
                 for (int k = 0; k < c.count; ++k) {
                     const float* src_tri = &tri[12 * (size_t)B.prim[(size_t)(c.first + k)]];
                     out.triangles.insert(out.triangles.end(), src_tri, src_tri + 12);
+                    out.tri_mesh.push_back(tri_mesh_in[(size_t)B.prim[(size_t)(c.first + k)]]);
                 }
                 tri_off += c.count;
             }
@@ -405,6 +414,10 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
     }
     out.num_nodes = (int64_t)wide_src.size();
     out.num_tris = (int64_t)(out.triangles.size() / 12);
+    out.level_offsets.clear();      // breadth-first emission: depths are non-decreasing
+    for (size_t i = 0; i < wide_depth.size(); ++i)
+        if (i == 0 || wide_depth[i] != wide_depth[i - 1]) out.level_offsets.push_back((int32_t)i);
+    out.level_offsets.push_back((int32_t)wide_depth.size());
     for (int a = 0; a < 3; ++a) {
         out.scene_min[a] = n2[(size_t)root].box.lo[a];
         out.scene_max[a] = n2[(size_t)root].box.hi[a];

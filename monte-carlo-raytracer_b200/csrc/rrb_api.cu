@@ -84,6 +84,18 @@ struct rrb_api {
     int64_t num_nodes = 0, num_tris = 0;
     double build_seconds = 0.0;
     int64_t launches = 0;
+    // device refit state of the last full build (option "bvh.refit")
+    std::vector<const rrb_shape*> built_world;     // shapes of the last full build, in build order
+    std::vector<int> built_mesh_of_shape;          // world index -> mesh index of the build (-1: contributed nothing)
+    std::vector<int32_t> level_offsets;
+    std::vector<mcrt::RefitMesh> refit_meshes;
+    float* d_ref_vertices = nullptr;
+    int* d_ref_indices = nullptr;
+    int* d_tri_mesh = nullptr;
+    float* d_boxes = nullptr;
+    mcrt::RefitMesh* d_refit_meshes = nullptr;
+    int64_t refits = 0;
+    bool last_commit_was_refit = false;
     unsigned int* d_counter = nullptr;
     std::vector<rrb_event*> event_pool;
     // staging for the host-buffer entry points
@@ -131,11 +143,57 @@ int wait_on(rrb_api* api, const rrb_event* wait) {
     return RRB_OK;
 }
 
+void free_refit(rrb_api* api) {
+    if (api->d_ref_vertices) cudaFree(api->d_ref_vertices);
+    if (api->d_ref_indices) cudaFree(api->d_ref_indices);
+    if (api->d_tri_mesh) cudaFree(api->d_tri_mesh);
+    if (api->d_boxes) cudaFree(api->d_boxes);
+    if (api->d_refit_meshes) cudaFree(api->d_refit_meshes);
+    api->d_ref_vertices = nullptr;
+    api->d_ref_indices = nullptr;
+    api->d_tri_mesh = nullptr;
+    api->d_boxes = nullptr;
+    api->d_refit_meshes = nullptr;
+    api->built_world.clear();
+    api->built_mesh_of_shape.clear();
+    api->refit_meshes.clear();
+    api->level_offsets.clear();
+}
+
 void free_bvh(rrb_api* api) {
     if (api->d_nodes) cudaFree(api->d_nodes);
     if (api->d_tris) cudaFree(api->d_tris);
     api->d_nodes = api->d_tris = nullptr;
     api->num_nodes = api->num_tris = 0;
+    free_refit(api);
+}
+
+bool refit_enabled(const rrb_api* api) {
+    auto it = api->f32_options.find("bvh.refit");
+    return it != api->f32_options.end() && it->second != 0.0f;
+}
+
+void fill_refit_transform(mcrt::RefitMesh& rm, const rrb_shape* s) {
+    std::memcpy(rm.m, s->m, 12 * sizeof(float));
+    rm.shape_id = s->id;
+}
+
+// Transform-only update of the committed tree (refit_kernels.cu).  Preconditions checked by the caller.
+int refit_committed(rrb_api* api) {
+    for (size_t w = 0; w < api->world.size(); ++w) {
+        const int mi = api->built_mesh_of_shape[w];
+        if (mi >= 0) fill_refit_transform(api->refit_meshes[(size_t)mi], api->world[w]);
+    }
+    RRB_CUDA(cudaMemcpyAsync(api->d_refit_meshes, api->refit_meshes.data(),
+                             api->refit_meshes.size() * sizeof(mcrt::RefitMesh), cudaMemcpyHostToDevice, api->stream));
+    cudaError_t e = mcrt::refit_bvh8(api->d_nodes, api->d_tris, api->d_boxes, api->d_tri_mesh, api->d_refit_meshes,
+                                     api->d_ref_vertices, api->d_ref_indices, (int)api->num_tris,
+                                     api->level_offsets.data(), (int)api->level_offsets.size() - 1, api->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "refit_bvh8");
+    RRB_CUDA(cudaStreamSynchronize(api->stream));      // Commit is blocking (radeon_rays.h:240-242)
+    api->launches += (int64_t)api->level_offsets.size();
+    api->refits += 1;
+    return RRB_OK;
 }
 
 int query_common(rrb_api* api, bool any_hit, const rrb_buffer* rays, const rrb_buffer* numrays_buf, int numrays,
@@ -335,11 +393,31 @@ int rrb_commit(rrb_api* api) {
     int rc = set_device(api);
     if (rc) return rc;
     auto t0 = std::chrono::steady_clock::now();
+    api->last_commit_was_refit = false;
+    // Option "bvh.refit" (an extension; the reference always rebuilds, intersector_lds.cpp:166): when the world
+    // holds the same shapes as at the last full build and only transforms / ids changed, keep the topology
+    // and refit on the device.
+    if (refit_enabled(api) && api->d_nodes && !api->world_changed && api->d_boxes && api->built_world == api->world) {
+        rc = refit_committed(api);
+        if (rc) return rc;
+        for (const rrb_shape* s : api->world) {
+            const_cast<rrb_shape*>(s)->changed = false;
+            if (s->base) const_cast<rrb_shape*>(s->base)->changed = false;
+        }
+        api->last_commit_was_refit = true;
+        api->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        return RRB_OK;
+    }
     std::vector<mcrt::BuildInputMesh> meshes;
+    std::vector<int> mesh_of_shape;
     meshes.reserve(api->world.size());
     for (const rrb_shape* s : api->world) {
         const rrb_shape* g = s->is_instance ? s->base : s;
-        if (!g || g->indices.empty()) continue;   // Intersection_1Ray_InstanceNoShape: nothing to add
+        if (!g || g->indices.empty()) {   // Intersection_1Ray_InstanceNoShape: nothing to add
+            mesh_of_shape.push_back(-1);
+            continue;
+        }
+        mesh_of_shape.push_back((int)meshes.size());
         mcrt::BuildInputMesh m;
         m.vertices = g->vertices.data();
         m.vnum = (int)(g->vertices.size() / 3);
@@ -372,6 +450,38 @@ int rrb_commit(rrb_api* api) {
     RRB_CUDA(cudaStreamSynchronize(api->stream));
     api->num_nodes = bvh.num_nodes;
     api->num_tris = bvh.num_tris;
+    if (refit_enabled(api)) {
+        // pooled object-space geometry + per-triangle mesh index + per-node exact boxes for later refits
+        std::vector<float> pv;
+        std::vector<int> pi;
+        api->refit_meshes.clear();
+        size_t w = 0;
+        for (const rrb_shape* s : api->world) {
+            const rrb_shape* g = s->is_instance ? s->base : s;
+            if (mesh_of_shape[w++] < 0) continue;
+            mcrt::RefitMesh rm;
+            std::memset(&rm, 0, sizeof(rm));
+            rm.vertex_base = (int)(pv.size() / 3);
+            rm.index_base = (int)pi.size();
+            fill_refit_transform(rm, s);
+            pv.insert(pv.end(), g->vertices.begin(), g->vertices.end());
+            pi.insert(pi.end(), g->indices.begin(), g->indices.end());
+            api->refit_meshes.push_back(rm);
+        }
+        RRB_CUDA(cudaMalloc((void**)&api->d_ref_vertices, pv.size() * sizeof(float)));
+        RRB_CUDA(cudaMalloc((void**)&api->d_ref_indices, pi.size() * sizeof(int)));
+        RRB_CUDA(cudaMalloc((void**)&api->d_tri_mesh, bvh.tri_mesh.size() * sizeof(int)));
+        RRB_CUDA(cudaMalloc((void**)&api->d_boxes, (size_t)bvh.num_nodes * 6 * sizeof(float)));
+        RRB_CUDA(cudaMalloc((void**)&api->d_refit_meshes, api->refit_meshes.size() * sizeof(mcrt::RefitMesh)));
+        RRB_CUDA(cudaMemcpyAsync(api->d_ref_vertices, pv.data(), pv.size() * sizeof(float), cudaMemcpyHostToDevice, api->stream));
+        RRB_CUDA(cudaMemcpyAsync(api->d_ref_indices, pi.data(), pi.size() * sizeof(int), cudaMemcpyHostToDevice, api->stream));
+        RRB_CUDA(cudaMemcpyAsync(api->d_tri_mesh, bvh.tri_mesh.data(), bvh.tri_mesh.size() * sizeof(int),
+                                 cudaMemcpyHostToDevice, api->stream));
+        RRB_CUDA(cudaStreamSynchronize(api->stream));
+        api->level_offsets = bvh.level_offsets;
+        api->built_world = api->world;
+        api->built_mesh_of_shape = mesh_of_shape;
+    }
     api->world_changed = false;
     for (const rrb_shape* s : api->world) {
         const_cast<rrb_shape*>(s)->changed = false;
@@ -623,6 +733,8 @@ int rrb_get_stats(rrb_api* api, rrb_stats* out) {
     out->triangle_bytes = api->num_tris * 48;
     out->build_seconds = api->build_seconds;
     out->launches = api->launches;
+    out->refits = api->refits;
+    out->last_commit_refit = api->last_commit_was_refit ? 1 : 0;
     return RRB_OK;
 }
 
@@ -689,6 +801,15 @@ int rrb_host_bvh_get(const rrb_host_bvh* bvh, const uint32_t** nodes, int64_t* n
     if (num_nodes) *num_nodes = bvh->bvh.num_nodes;
     if (triangles) *triangles = bvh->bvh.triangles.data();
     if (num_tris) *num_tris = bvh->bvh.num_tris;
+    return RRB_OK;
+}
+
+int rrb_host_bvh_get_refit_info(const rrb_host_bvh* bvh, const int32_t** tri_mesh, const int32_t** level_offsets,
+                                int* num_levels) {
+    if (!bvh) return fail(RRB_ERROR_INVALID_ARGUMENT, "null bvh");
+    if (tri_mesh) *tri_mesh = bvh->bvh.tri_mesh.data();
+    if (level_offsets) *level_offsets = bvh->bvh.level_offsets.data();
+    if (num_levels) *num_levels = (int)bvh->bvh.level_offsets.size() - 1;
     return RRB_OK;
 }
 

@@ -12,4 +12,18 @@ cudaError_t launch_query(bool any_hit, bool counted, const void* nodes, const vo
                          const int* numrays_dev, int numrays_max, void* out, unsigned int* work_counter,
                          int* counts, cudaStream_t stream);
 
+// ---- device refit (refit_kernels.cu)
+struct RefitMesh {
+    float m[12];          // rows 0..2 of the row-major object -> world matrix
+    int vertex_base;      // first vertex of the mesh in the pooled object-space vertex array
+    int index_base;       // first index of the mesh in the pooled index array
+    int shape_id;
+    int pad;
+};
+// Recomputes the triangle records and re-fits all nodes (levels given on the host, breadth-first node order).
+// Returns the number of kernels launched through *launches when not NULL.
+cudaError_t refit_bvh8(void* nodes, void* tris, float* boxes, const int* tri_mesh, const RefitMesh* meshes,
+                       const float* vertices, const int* indices, int num_tris, const int* level_offsets_host,
+                       int num_levels, cudaStream_t stream);
+
 }  // namespace mcrt

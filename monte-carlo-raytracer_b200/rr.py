@@ -27,7 +27,8 @@ class RadeonRaysError(RuntimeError):
 
 class RrbStats(ctypes.Structure):
     _fields_ = [("num_triangles", ctypes.c_int64), ("num_nodes", ctypes.c_int64), ("node_bytes", ctypes.c_int64),
-                ("triangle_bytes", ctypes.c_int64), ("build_seconds", ctypes.c_double), ("launches", ctypes.c_int64)]
+                ("triangle_bytes", ctypes.c_int64), ("build_seconds", ctypes.c_double), ("launches", ctypes.c_int64),
+                ("refits", ctypes.c_int64), ("last_commit_refit", ctypes.c_int64)]
 
 
 def lib_path() -> str:
@@ -68,6 +69,7 @@ def load_library():
         "rrb_get_stream": [vp, ctypes.POINTER(i), pp],
         "rrb_host_bvh_build": [vp, i, vp, i, vp, i, pp],
         "rrb_host_bvh_get": [vp, pp, ctypes.POINTER(ctypes.c_int64), pp, ctypes.POINTER(ctypes.c_int64)],
+        "rrb_host_bvh_get_refit_info": [vp, pp, pp, ctypes.POINTER(i)],
         "rrb_host_bvh_free": [vp],
     }
     for name, args in sig.items():
@@ -320,6 +322,13 @@ class IntersectionApi:
         _check(self._lib.rrb_get_stats(self._h, ctypes.byref(s)))
         return {k: getattr(s, k) for k, _ in RrbStats._fields_}
 
+    def GetBvh(self):
+        """(nodes device pointer, triangles device pointer, num_nodes, num_tris) of the committed tree."""
+        pn, pt = ctypes.c_void_p(), ctypes.c_void_p()
+        nn, nt = ctypes.c_int64(), ctypes.c_int64()
+        _check(self._lib.rrb_get_bvh(self._h, ctypes.byref(pn), ctypes.byref(pt), ctypes.byref(nn), ctypes.byref(nt)))
+        return pn.value, pt.value, nn.value, nt.value
+
     def QueryIntersectionCounted(self, rays, numrays, hits, counts):
         _check(self._lib.rrb_query_intersection_counted(self._h, rays._h, int(numrays), hits._h, counts._h))
 
@@ -338,8 +347,9 @@ def attach_scene(api: IntersectionApi, scene):
     return shapes
 
 
-def host_bvh(vertices, indices, face_shape_ids=None, use_sah=True):
-    """Build the compressed wide BVH on the host only (no CUDA): returns (nodes u32 (N,20), tris f32 (T,12))."""
+def host_bvh(vertices, indices, face_shape_ids=None, use_sah=True, refit_info=False):
+    """Build the compressed wide BVH on the host only (no CUDA): returns (nodes u32 (N,20), tris f32 (T,12));
+    with refit_info also (tri_mesh i32 (T,), level_offsets i32 (levels + 1,))."""
     lib = load_library()
     v = np.ascontiguousarray(vertices, np.float32)
     ix = np.ascontiguousarray(indices, np.int32)
@@ -353,6 +363,12 @@ def host_bvh(vertices, indices, face_shape_ids=None, use_sah=True):
         _check(lib.rrb_host_bvh_get(h, ctypes.byref(pn), ctypes.byref(nn), ctypes.byref(pt), ctypes.byref(nt)))
         nodes = np.frombuffer(ctypes.string_at(pn.value, nn.value * 80), np.uint32).reshape(-1, 20).copy()
         tris = np.frombuffer(ctypes.string_at(pt.value, nt.value * 48), np.float32).reshape(-1, 12).copy()
+        extra = ()
+        if refit_info:
+            pm, pl, nl = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_int()
+            _check(lib.rrb_host_bvh_get_refit_info(h, ctypes.byref(pm), ctypes.byref(pl), ctypes.byref(nl)))
+            extra = (np.frombuffer(ctypes.string_at(pm.value, nt.value * 4), np.int32).copy(),
+                     np.frombuffer(ctypes.string_at(pl.value, (nl.value + 1) * 4), np.int32).copy())
     finally:
         lib.rrb_host_bvh_free(h)
-    return nodes, tris
+    return (nodes, tris) + extra

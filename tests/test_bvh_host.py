@@ -151,3 +151,50 @@ def test_cpp_adaptor_compiles_against_reference_header_and_fails_loudly_without_
         assert out.stdout.startswith("NO_DEVICE") and "no CPU fallback" in out.stdout
     else:
         assert "OK" in out.stdout
+
+
+def test_refit_metadata_and_node_encoding_is_a_function_of_child_bounds():
+    """What the device refit (csrc/refit_kernels.cu) relies on: (1) nodes are stored level by level and the
+    builder reports where each level starts, (2) every emitted triangle knows the input mesh it came from,
+    (3) a node's origin / exponents / quantised planes are a pure function of the exact bounds of its
+    children -- recomputing them here from the triangle records reproduces the builder's bytes."""
+    v, idx = soup(4000, 5)
+    ids = np.repeat(np.arange(8, dtype=np.int32) * 3 + 1, 500)     # 8 meshes with ids 1, 4, 7, ...
+    nodes, tris, tri_mesh, levels = rr.host_bvh(v, idx, ids, True, refit_info=True)
+    assert levels[0] == 0 and levels[-1] == nodes.shape[0] and (np.diff(levels) > 0).all()
+    level_of = np.searchsorted(levels, np.arange(nodes.shape[0]), side="right") - 1
+    assert tri_mesh.shape[0] == tris.shape[0]
+    assert np.array_equal(tris[:, 3].view(np.int32), tri_mesh * 3 + 1)
+    bounds = bvh8_emul.subtree_bounds(nodes, tris)
+    children = {}
+    for ni, s, leaf, lo, hi, ref in bvh8_emul.walk_tree(nodes, tris):
+        if not leaf:
+            assert level_of[ref] == level_of[ni] + 1
+            cb = bounds[ref]
+        else:
+            p = tris[ref][:, [0, 1, 2, 4, 5, 6, 8, 9, 10]].reshape(-1, 3).astype(np.float64)
+            cb = (p.min(0), p.max(0))
+        children.setdefault(ni, []).append((s, cb))
+    for ni in range(nodes.shape[0]):
+        node = nodes[ni]
+        lo, hi = bounds[ni]
+        assert np.array_equal(node[0:3].view(np.float32), lo.astype(np.float32))
+        q = node[8:20].view(np.uint8).reshape(6, 8)
+        for a in range(3):
+            ext = hi[a] - lo[a]
+            ex = -100
+            if ext > 0:
+                ex = int(np.ceil(np.log2(ext / 255.0)))
+                while np.ceil(ext / np.ldexp(1.0, ex)) > 255.0:
+                    ex += 1
+            ex = max(-126, min(127, ex))
+            assert ((int(node[3]) >> (8 * a)) & 0xFF) == ex + 127
+            scale = np.float32(np.ldexp(1.0, ex))
+            for s, (clo, chi) in children[ni]:
+                qlo = int(max(0.0, min(255.0, np.floor((clo[a] - lo[a]) / float(scale)))))
+                qhi = int(max(0.0, min(255.0, np.ceil((chi[a] - lo[a]) / float(scale)))))
+                while qlo > 0 and np.float32(lo[a]) + np.float32(qlo) * scale > np.float32(clo[a]):
+                    qlo -= 1
+                while qhi < 255 and np.float32(lo[a]) + np.float32(qhi) * scale < np.float32(chi[a]):
+                    qhi += 1
+                assert q[a][s] == qlo and q[3 + a][s] == qhi

@@ -256,6 +256,105 @@ def test_large_soup_bit_exact(api):
     assert st["num_triangles"] == n and st["num_nodes"] > 0
 
 
+def _rot_y(deg, t=(0.0, 0.0, 0.0)):
+    a = np.deg2rad(deg)
+    m = np.eye(4, dtype=np.float32)
+    m[0, 0], m[0, 2], m[2, 0], m[2, 2] = np.cos(a), np.sin(a), -np.sin(a), np.cos(a)
+    m[:3, 3] = t
+    return m
+
+
+def test_device_refit_equals_rebuild(api, cornell):
+    """Dynamic updates: with option "bvh.refit" a transform-only Commit refits the tree on
+    the device.  Hits must equal the brute-force oracle on the moved geometry AND a from-scratch build, the
+    device pointers of the tree must not move, and a topology change must fall back to a full build."""
+    shapes = rr.attach_scene(api, cornell)
+    inst = api.CreateInstance(shapes[len(shapes) - 1])
+    inst.SetId(77)
+    inst.SetTransform(_rot_y(10.0, (0.2, 0.5, -0.1)))
+    api.AttachShape(inst)
+    api.SetOption("bvh.refit", 1.0)
+    api.Commit()
+    st0 = api.GetStats()
+    assert st0["refits"] == 0 and st0["last_commit_refit"] == 0
+    ptrs0 = api.GetBvh()[:2]
+    lo, hi = cornell.world_bounds()
+    rays = random_rays(20000, lo - 1.0, hi + 1.0, seed=4711)
+    xf = {}
+    for step, (deg, t) in enumerate([(25.0, (0.3, 0.0, 0.2)), (-40.0, (-0.4, 0.3, 0.0)), (0.0, (0.0, 0.0, 0.0))]):
+        for k in (len(shapes) - 1, len(shapes) - 2):          # the two boxes move, the room stays
+            xf[k] = _rot_y(deg * (1 if k % 2 else -1), t)
+            shapes[k].SetTransform(xf[k])
+        inst_m = _rot_y(3.0 * deg, (0.2 + 0.1 * step, 0.5, -0.1))
+        inst.SetTransform(inst_m)
+        inst.SetId(77 + step)
+        api.Commit()
+        st = api.GetStats()
+        assert st["refits"] == step + 1 and st["last_commit_refit"] == 1
+        assert api.GetBvh()[:2] == ptrs0
+        meshes = [(m.positions, m.indices, i, xf.get(i, m.transform)) for i, m in enumerate(cornell.meshes)]
+        last = cornell.meshes[len(shapes) - 1]
+        meshes.append((last.positions, last.indices, 77 + step, inst_m))
+        tris = port.mesh_triangles(meshes)
+        got = api.QueryIntersectionHost(rays)
+        res = port.compare_hits(got, port.intersect(tris, rays), tris, rays)
+        assert res["bad"] == 0 and res["tie_ok"] == 0, res
+        assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
+        # a from-scratch build of the same world gives the same answers
+        fresh = rr.IntersectionApi.Create(0)
+        try:
+            for pos, idx, sid, m in meshes:
+                sh = fresh.CreateMesh(pos, pos.shape[0], 12, idx, 0, None, idx.shape[0])
+                sh.SetId(sid)
+                if m is not None:
+                    sh.SetTransform(m)
+                fresh.AttachShape(sh)
+            fresh.Commit()
+            ref_hits = fresh.QueryIntersectionHost(rays)
+        finally:
+            rr.IntersectionApi.Delete(fresh)
+        for f in ("shapeid", "primid"):
+            assert np.array_equal(got[f], ref_hits[f])
+        hit = got["shapeid"] >= 0
+        assert np.array_equal(got["uvwt"][hit].view(np.uint32), ref_hits["uvwt"][hit].view(np.uint32))
+    # topology change -> full build again, and refits resume afterwards
+    api.DetachShape(inst)
+    api.Commit()
+    assert api.GetStats()["last_commit_refit"] == 0
+    shapes[0].SetTransform(_rot_y(0.0, (0.0, 0.01, 0.0)))
+    api.Commit()
+    assert api.GetStats()["last_commit_refit"] == 1
+
+
+def test_device_refit_large_soup(api):
+    """Refit at a size where every level of the tree has many nodes: 100k-triangle soup in 16 shapes, each shape
+    given its own rigid motion."""
+    rng = np.random.RandomState(11)
+    shapes, geo = [], []
+    per = 6250
+    for k in range(16):
+        c = rng.rand(per, 1, 3) * 10.0 + np.array([[(k % 4) * 10.0, (k // 4) * 10.0, 0.0]])
+        v = (c + (rng.rand(per, 3, 3) - 0.5) * 0.4).reshape(-1, 3).astype(np.float32)
+        idx = np.arange(3 * per, dtype=np.int32).reshape(per, 3)
+        sh = api.CreateMesh(v, 3 * per, 12, idx, 12, None, per)
+        sh.SetId(k)
+        api.AttachShape(sh)
+        shapes.append(sh)
+        geo.append((v, idx))
+    api.SetOption("bvh.refit", 1.0)
+    api.Commit()
+    xfs = [_rot_y(rng.uniform(-60, 60), rng.uniform(-3, 3, 3)) for _ in range(16)]
+    for sh, m in zip(shapes, xfs):
+        sh.SetTransform(m)
+    api.Commit()
+    assert api.GetStats()["last_commit_refit"] == 1
+    rays = random_rays(20000, np.array([-5.0, -5.0, -5.0]), np.array([45.0, 45.0, 15.0]), 5, maxt=30.0)
+    tris = port.mesh_triangles([(v, idx, k, xfs[k]) for k, (v, idx) in enumerate(geo)])
+    res = port.compare_hits(api.QueryIntersectionHost(rays), port.intersect(tris, rays), tris, rays)
+    assert res["bad"] == 0 and res["tie_ok"] == 0, res
+    assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
+
+
 def test_golden_intersections(api, cornell):
     """Committed vectors from the reference's own kernel (tests/golden/cornell_isect_4096.npz)."""
     import os
