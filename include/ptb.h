@@ -80,6 +80,11 @@ int ptb_destroy(ptb_context* ctx);
 /* RTScene::uploadShapes/uploadLights/uploadMaterials/uploadTextures + buffer creation. Blocking. */
 int ptb_upload_scene(ptb_context* ctx, const ptb_scene_desc* scene);
 /* PathTracerSettings::GI.imageResolution; (re)allocates every per-pixel buffer, zero-filled. */
+/* Hot update of one scene array, in place and stream-ordered: `array` is "shapes", "lights" or "materials";
+ * `bytes` must equal the size uploaded by ptb_upload_scene.  Replaces the whole-array WriteBuffer calls of
+ * RTScene::updateDynamicEntities (scene/RTScene.cpp:356-389); the matching BVH update is rrb_commit
+ * (a device refit when the rrb option "bvh.refit" is set). */
+int ptb_update_scene_array(ptb_context* ctx, const char* array, const void* data, size_t bytes);
 int ptb_resize(ptb_context* ctx, int width, int height);
 /* Sampler variant (samplers.cl:15-17,75-84; a compile-time switch in the reference): kind 0 = Sobol,
  * 1 = random (default).  `matrices` (may be NULL to keep the table uploaded with the scene) holds

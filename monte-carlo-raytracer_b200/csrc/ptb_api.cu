@@ -256,6 +256,21 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
     return 0;
 }
 
+int ptb_update_scene_array(ptb_context* c, const char* array, const void* data, size_t bytes) {
+    if (!c || !array || !data) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    if (!c->scene_loaded) return pfail(RRB_ERROR_INVALID_ARGUMENT, "ptb_upload_scene has not been called");
+    const std::string name(array);
+    if (name != "shapes" && name != "lights" && name != "materials")
+        return pfail(RRB_ERROR_INVALID_ARGUMENT, "only shapes, lights and materials can be updated in place");
+    auto it = c->scene_bufs.find(name);
+    if (it == c->scene_bufs.end() || it->second.bytes != bytes || bytes == 0)
+        return pfail(RRB_ERROR_INVALID_ARGUMENT, "size of '" + name + "' differs from the uploaded array");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaMemcpyAsync(it->second.p, data, bytes, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+
 int ptb_set_sampler(ptb_context* c, int kind, const uint32_t* matrices, int num_dimensions) {
     if (!c || (kind != 0 && kind != 1)) return pfail(RRB_ERROR_INVALID_ARGUMENT, "sampler kind must be 0 (Sobol) or 1 (random)");
     int rc = set_dev(c);

@@ -55,6 +55,7 @@ def _lib():
         pp = ctypes.POINTER(ctypes.c_void_p)
         sig = {
             "ptb_create": [vp, pp], "ptb_destroy": [vp], "ptb_upload_scene": [vp, ctypes.POINTER(PtbSceneDesc)],
+            "ptb_update_scene_array": [vp, ctypes.c_char_p, vp, ctypes.c_size_t],
             "ptb_resize": [vp, i, i], "ptb_set_camera": [vp, vp], "ptb_set_partition": [vp, i, i],
             "ptb_generate_primary_rays": [vp], "ptb_pt_shade": [vp, i, i, i], "ptb_pt_shadow_resolve": [vp, i],
             "ptb_pt_render_sample": [vp, i, i], "ptb_bdpt_render_sample": [vp, i, i],
@@ -130,10 +131,12 @@ class RTScene:
     """Device scene + Radeon Rays world: RTScene's constructor, attachMesh and commit
     (scene/RTScene.cpp:28-56,199-267,564-678) for a headless host scene."""
 
-    def __init__(self, api: rr.IntersectionApi, scene):
+    def __init__(self, api: rr.IntersectionApi, scene, refit=False):
         self.api = api
         self.host = scene
         self.shapes = rr.attach_scene(api, scene)
+        if refit:       # extension: transform-only commits refit the tree on the device (include/rrb.h)
+            api.SetOption("bvh.refit", 1.0)
         # RTScene::commit: acc.type / bvh.builder from the GUI defaults (PathTracingSettings.h:241-249)
         api.SetOption("acc.type", "fatbvh")
         api.SetOption("bvh.builder", "sah")
@@ -157,6 +160,32 @@ class RTScene:
         d.num_indices, d.num_vertices = s.indices.size, s.positions.shape[0]
         d.texdata_bytes = s.texdata.size
         _check(_lib().ptb_upload_scene(self._h, ctypes.byref(d)))
+
+    def updateDynamicEntities(self, transforms=None, lights=None, materials=None):
+        """RTScene::updateDynamicEntities (scene/RTScene.cpp:317-389): `transforms` maps an RTShape index to its
+        new row-major local-to-world matrix -> Shape::SetTransform, RTShape::toWorldTransform /
+        toWorldInverseTranspose, one write of the shapes array, Commit; `lights` / `materials` are whole
+        replacement arrays (same length)."""
+        s = self.host
+        if transforms:
+            for i, m in transforms.items():
+                m = np.ascontiguousarray(m, np.float32)
+                self.shapes[i].SetTransform(m)
+                s.meshes[i].transform = m
+                s.shapes[i]["toWorldTransform"] = m
+                s.shapes[i]["toWorldInverseTranspose"] = np.linalg.inv(m.astype(np.float64)).T.astype(np.float32)
+            _check(_lib().ptb_update_scene_array(self._h, b"shapes", _ptr(s.shapes), s.shapes.nbytes))
+            self.api.Commit()
+        if lights is not None:
+            lights = np.ascontiguousarray(lights, L.LIGHT)
+            assert lights.shape == s.lights.shape
+            s.lights = lights
+            _check(_lib().ptb_update_scene_array(self._h, b"lights", _ptr(s.lights), s.lights.nbytes))
+        if materials is not None:
+            materials = np.ascontiguousarray(materials, L.MATERIAL)
+            assert materials.shape == s.materials.shape
+            s.materials = materials
+            _check(_lib().ptb_update_scene_array(self._h, b"materials", _ptr(s.materials), s.materials.nbytes))
 
     def destroy(self):
         if self._h:
@@ -385,9 +414,9 @@ def write_pfm(path, image, width, height):
         f.write(np.ascontiguousarray(rgb, "<f4").tobytes())
 
 
-def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=True):
+def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=True, refit=False):
     """PathTracingApp::startPathTracing's PT pipeline (:248-255) without denoise / tonemap / display."""
-    rts = RTScene(api, scene)
+    rts = RTScene(api, scene, refit=refit)
     gi = GISettings()
     gi.imageResolution = (width, height)
     gi.maxDepth = max_depth

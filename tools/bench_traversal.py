@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--quads", type=int, default=707)
     ap.add_argument("--res", type=int, default=2048)
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--refit", action="store_true", help="also time a device refit against a full rebuild")
     a = ap.parse_args()
     scene = scene_library.traversal_bench_scene(a.quads)
     api = rr.IntersectionApi.Create(0)
@@ -97,6 +98,40 @@ def main():
                           "bytes_per_ray": c[0] * 80 + c[1] * 48, "hit_frac": hitfrac}))
         for b in (rb, hb, ob, cb):
             api.DeleteBuffer(b)
+    if a.refit:
+        refit_section(scene, sets["incoherent"], a.reps)
+
+
+def refit_section(scene, rays, reps):
+    """Commit after a transform change: full host rebuild vs device refit (option bvh.refit), and what the kept
+    topology costs in traversal speed after every shape was rotated by 30 degrees."""
+    def rot_y(deg):
+        c, s_ = np.cos(np.deg2rad(deg)), np.sin(np.deg2rad(deg))
+        m = np.eye(4, dtype=np.float32)
+        m[0, 0], m[0, 2], m[2, 0], m[2, 2] = c, s_, -s_, c
+        return m
+
+    out = {}
+    for mode in ("rebuild", "refit"):
+        api = rr.IntersectionApi.Create(0)
+        shapes = rr.attach_scene(api, scene)
+        if mode == "refit":
+            api.SetOption("bvh.refit", 1.0)
+        api.Commit()
+        ts = []
+        for k in range(3):
+            for sh in shapes:
+                sh.SetTransform(rot_y(10.0 * (k + 1)))
+            t0 = time.perf_counter()
+            api.Commit()
+            ts.append(time.perf_counter() - t0)
+        n = rays.shape[0]
+        rb, hb = api.CreateBuffer(n * 48, rays), api.CreateBuffer(n * 32)
+        tmin, _ = time_query(api, api.QueryIntersection, rb, n, hb, reps)
+        out[mode] = {"commit_ms": [round(t * 1e3, 3) for t in ts], "incoherent_closest_Mrays_s": n / tmin / 1e6,
+                     "last_commit_refit": api.GetStats()["last_commit_refit"]}
+        rr.IntersectionApi.Delete(api)
+    print(json.dumps({"refit_vs_rebuild": out}))
 
 
 if __name__ == "__main__":
