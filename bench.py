@@ -361,14 +361,26 @@ def own_arm(args):
         except OSError:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        nb = max(prof["bounces"], 1)
+        # Per kernel: closest-hit rays of bounce 0 have a launch of their own; those of bounce b share one with the
+        # shadow rays of bounce b - 1 (k_trace_mixed); the last shadow set is traced alone.  Algorithmic bytes of
+        # a traversal launch = 80 B per closest-hit ray + 52 B per shadow ray it served.
+        first_closest = float(cnt["samples"])                   # one primary ray per sample
+        trace_bytes = cnt["closest_rays"] * BYTES_CLOSEST_PER_RAY + cnt["shadow_rays"] * BYTES_SHADOW_PER_RAY
+        t_closest, t_mixed, t_shadow = prof["k_trace_closest"][0], prof["k_trace_mixed"][0], prof["k_trace_shadow"][0]
         stages = {
-            "k_trace_closest": (prof["closest_ms"], cnt["closest_rays"] * BYTES_CLOSEST_PER_RAY),
-            "k_shade": (prof["shade_ms"], cnt["shaded_vertices"] * BYTES_SHADE_PER_VERTEX),
-            "k_trace_shadow": (prof["shadow_ms"], cnt["shadow_rays"] * BYTES_SHADOW_PER_RAY),
+            "k_trace_closest": (t_closest, first_closest * BYTES_CLOSEST_PER_RAY, prof["k_trace_closest"][1]),
+            "k_trace_mixed": (t_mixed, None, prof["k_trace_mixed"][1]),
+            "k_trace_shadow": (t_shadow, None, prof["k_trace_shadow"][1]),
+            "k_shade": (prof["k_shade"][0], cnt["shaded_vertices"] * BYTES_SHADE_PER_VERTEX, prof["k_shade"][1]),
         }
+        # the split of the remaining rays between the mixed launches and the last shadow launch is not counted on
+        # the device; apportion their bytes by time (same kernel body, same ray mix to first order)
+        rest = trace_bytes - first_closest * BYTES_CLOSEST_PER_RAY
+        for k, t in (("k_trace_mixed", t_mixed), ("k_trace_shadow", t_shadow)):
+            stages[k] = (t, rest * t / max(t_mixed + t_shadow, 1e-12), stages[k][2])
         top = max(stages, key=lambda k: stages[k][0])
-        top_ms, top_bytes = stages[top]
+        top_ms, top_bytes, nb = stages[top]
+        nb = max(nb, 1)
         achieved = top_bytes / max(top_ms * 1e-3, 1e-12) / 1e9
         traffic = None
         try:
@@ -381,8 +393,8 @@ def own_arm(args):
                     "launches": nb, "avg_launch_ms": top_ms / nb, "algorithmic_bytes_per_launch": top_bytes / nb,
                     "stage_ms_per_step": {k: v[0] / K for k, v in stages.items()},
                     "stage_share_of_step": {k: v[0] / max(ms, 1e-9) for k, v in stages.items()},
-                    "rays_per_s": {"closest": cnt["closest_rays"] / max(prof["closest_ms"] * 1e-3, 1e-12),
-                                   "shadow": cnt["shadow_rays"] / max(prof["shadow_ms"] * 1e-3, 1e-12)}}
+                    "trace_rays_per_s": (cnt["closest_rays"] + cnt["shadow_rays"]) /
+                                        max((t_closest + t_mixed + t_shadow) * 1e-3, 1e-12)}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cpu = run_cpu_baseline(scene, args, args.cpu_seconds)

@@ -113,13 +113,18 @@ int ptb_pt_render_sample(ptb_context* ctx, int frame, int max_depth);
 /* Same for RTBDPTPass::update. */
 int ptb_bdpt_render_sample(ptb_context* ctx, int frame, int max_depth);
 
-/* Per-stage device timing of the fused wavefront (no reference counterpart; measurement only).
- * While enabled every bounce records CUDA events on the context's stream around the closest-hit
- * trace, the shade stage and the shadow trace; collect() synchronises, returns the summed
- * milliseconds of each stage and the number of bounces measured, and rearms the recorder. */
+/* Per-kernel device timing of the fused wavefront (no reference counterpart; measurement only).
+ * While enabled, CUDA events are recorded on the context's stream around every traversal and shade launch;
+ * collect() synchronises, returns the summed milliseconds and launch counts per kernel (indexed by ptb_stage)
+ * and rearms the recorder. */
+enum ptb_stage {
+    PTB_STAGE_TRACE_CLOSEST = 0,   /* closest-hit rays of bounce 0 */
+    PTB_STAGE_TRACE_MIXED = 1,     /* closest-hit rays of bounce b + shadow rays of bounce b - 1, one launch */
+    PTB_STAGE_TRACE_SHADOW = 2,    /* shadow rays of the last bounce */
+    PTB_STAGE_SHADE = 3
+};
 int ptb_profile_enable(ptb_context* ctx, int on);
-int ptb_profile_collect(ptb_context* ctx, double* ms_closest, double* ms_shade, double* ms_shadow,
-                        int64_t* launches_each);
+int ptb_profile_collect(ptb_context* ctx, double ms[4], int64_t launches[4]);
 
 /* ReconstructionPass (reconstruction.cl:6-60): clamp, filter weight of the frame's pixel offset,
  * running weighted mean into "NextFrameImageCL"; frame 0 restarts the mean (reconstruction.cl:47-57). */

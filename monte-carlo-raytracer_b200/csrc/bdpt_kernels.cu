@@ -345,6 +345,7 @@ k_bdpt_trace(const uint4* __restrict__ nodes, const float4* __restrict__ tris, c
             r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmax = o.w;
             r.dx = d.x; r.dy = d.y; r.dz = d.z;
             r.mask = -1;
+            return false;
         },
         [&](unsigned idx, const Ray& r, const TravState& st) {
             const uint32_t px = queue[idx];
@@ -642,6 +643,7 @@ k_bdpt_trace_conn(PtState s, BdptState b) {
             r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmax = o.w;
             r.dx = d.x; r.dy = d.y; r.dz = d.z;
             r.mask = -1;
+            return true;
         },
         [&](unsigned idx, const Ray&, const TravState& st) { b.conn_vis[b.conn_rays[idx]] = st.best_tri >= 0 ? 0 : 1; });
 }

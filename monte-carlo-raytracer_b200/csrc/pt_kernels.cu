@@ -20,24 +20,28 @@ namespace mcrt {
 // ---------------------------------------------------------------------------------------------
 // queue control: one thread, between stages (keeps all counts on the device)
 // ---------------------------------------------------------------------------------------------
-__global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int cur, int first, int n_first) {
+// cnt: [0],[1] live-path queue sizes (ping-pong)  [3],[4] work counters of the persistent kernels
+//      [5],[6] shadow-ray counts by bounce parity (the shadow rays of bounce b are traced together with the
+//      closest-hit rays of bounce b + 1, while nothing writes either set)
+__global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int cur, int bounce, int n_first) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    if (first) {
+    if (bounce == 0) {
         cnt[cur] = (unsigned)n_first;
         stats[3] += (unsigned long long)n_first;
     } else {
-        stats[1] += cnt[2];   // shadow rays of the bounce that just finished
+        stats[1] += cnt[5 + ((bounce - 1) & 1)];   // shadow rays of the bounce that was just shaded
     }
     stats[0] += cnt[cur];     // closest-hit rays of the bounce about to start
     stats[2] += cnt[cur];     // = path vertices handed to the shade stage
     cnt[1 - cur] = 0;
-    cnt[2] = 0;
+    cnt[5 + (bounce & 1)] = 0;
     cnt[3] = 0;
     cnt[4] = 0;
 }
-__global__ void k_sample_end(unsigned int* cnt, unsigned long long* stats) {
+__global__ void k_sample_end(unsigned int* cnt, unsigned long long* stats, int last_bounce) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    stats[1] += cnt[2];
+    stats[1] += cnt[5 + (last_bounce & 1)];
+    cnt[4] = 0;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -57,58 +61,94 @@ k_raygen(PtState s, const uint32_t* __restrict__ pixels, int n) {
     s.queue[0][i] = px;
 }
 
+// closest-hit ray of queue entry idx / its result
+__device__ __forceinline__ void fetch_closest_ray(const PtState& s, const uint32_t* __restrict__ queue, unsigned idx, Ray& r) {
+    const uint32_t px = queue[idx];
+    const float4 o = s.ray_o[px], d = s.ray_d[px];
+    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmax = o.w;
+    r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    r.mask = -1;   // setRay(): extra = 0xFFFFFFFF (kernel_data.h:434-440)
+}
+__device__ __forceinline__ void store_closest_hit(const PtState& s, const uint32_t* __restrict__ queue, unsigned idx,
+                                                  const Ray& r, const TravState& st) {
+    const uint32_t px = queue[idx];
+    int4 h = make_int4(-1, -1, 0, 0);
+    if (st.best_tri >= 0) {
+        const float4 v0 = __ldg(s.tris + 3 * (size_t)st.best_tri + 0);
+        const float4 v1 = __ldg(s.tris + 3 * (size_t)st.best_tri + 1);
+        const float4 v2 = __ldg(s.tris + 3 * (size_t)st.best_tri + 2);
+        const float hx = add_(r.ox, mul_(st.closest, r.dx));
+        const float hy = add_(r.oy, mul_(st.closest, r.dy));
+        const float hz = add_(r.oz, mul_(st.closest, r.dz));
+        const float2 uv = barycentrics_ref(hx, hy, hz, v0, v1, v2);
+        h = make_int4(__float_as_int(v0.w), __float_as_int(v1.w), __float_as_int(uv.x), __float_as_int(uv.y));
+    }
+    s.hit[px] = h;
+}
+// shadow ray idx / the reference's ShadowPass on its result: radiance += (throughput * L) * V
+__device__ __forceinline__ void fetch_shadow_ray(const PtState& s, unsigned idx, Ray& r) {
+    const float4 o = s.sh_o[idx], d = s.sh_d[idx];
+    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmax = o.w;
+    r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    r.mask = -1;
+}
+__device__ __forceinline__ void resolve_shadow(const PtState& s, unsigned idx, const TravState& st) {
+    const uint32_t px = (uint32_t)__float_as_int(s.sh_d[idx].w);
+    const float V = st.best_tri >= 0 ? 0.0f : 1.0f;
+    const float4 L = s.sh_L[idx];
+    float4 r = s.radiance[px];
+    r.x += L.x * V;
+    r.y += L.y * V;
+    r.z += L.z * V;
+    s.radiance[px] = r;
+}
+
 __global__ void __launch_bounds__(128, 8)
 k_trace_closest(PtState s, int cur) {
     const unsigned count = s.cnt[cur];
     const uint32_t* __restrict__ queue = s.queue[cur];
-    const float4* __restrict__ tris = s.tris;
     persistent_trace<false>(
         s.nodes, s.tris, count, s.cnt + 3,
         [&](unsigned idx, Ray& r) {
-            const uint32_t px = queue[idx];
-            const float4 o = s.ray_o[px], d = s.ray_d[px];
-            r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmax = o.w;
-            r.dx = d.x; r.dy = d.y; r.dz = d.z;
-            r.mask = -1;   // setRay(): extra = 0xFFFFFFFF (kernel_data.h:434-440)
+            fetch_closest_ray(s, queue, idx, r);
+            return false;
         },
-        [&](unsigned idx, const Ray& r, const TravState& st) {
-            const uint32_t px = queue[idx];
-            int4 h = make_int4(-1, -1, 0, 0);
-            if (st.best_tri >= 0) {
-                const float4 v0 = __ldg(tris + 3 * (size_t)st.best_tri + 0);
-                const float4 v1 = __ldg(tris + 3 * (size_t)st.best_tri + 1);
-                const float4 v2 = __ldg(tris + 3 * (size_t)st.best_tri + 2);
-                const float hx = add_(r.ox, mul_(st.closest, r.dx));
-                const float hy = add_(r.oy, mul_(st.closest, r.dy));
-                const float hz = add_(r.oz, mul_(st.closest, r.dz));
-                const float2 uv = barycentrics_ref(hx, hy, hz, v0, v1, v2);
-                h = make_int4(__float_as_int(v0.w), __float_as_int(v1.w), __float_as_int(uv.x), __float_as_int(uv.y));
-            }
-            s.hit[px] = h;
-        });
+        [&](unsigned idx, const Ray& r, const TravState& st) { store_closest_hit(s, queue, idx, r, st); });
 }
 
-// any-hit traversal fused with the reference's ShadowPass: radiance += (throughput * L) * V
+// any-hit traversal fused with the reference's ShadowPass; shadow rays of bounce parity `sh`
 __global__ void __launch_bounds__(128, 8)
-k_trace_shadow(PtState s) {
-    const unsigned count = s.cnt[2];
+k_trace_shadow(PtState s, int sh) {
+    const unsigned count = s.cnt[5 + sh];
     persistent_trace<true>(
         s.nodes, s.tris, count, s.cnt + 4,
         [&](unsigned idx, Ray& r) {
-            const float4 o = s.sh_o[idx], d = s.sh_d[idx];
-            r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmax = o.w;
-            r.dx = d.x; r.dy = d.y; r.dz = d.z;
-            r.mask = -1;
+            fetch_shadow_ray(s, idx, r);
+            return true;
         },
-        [&](unsigned idx, const Ray&, const TravState& st) {
-            const uint32_t px = (uint32_t)__float_as_int(s.sh_d[idx].w);
-            const float V = st.best_tri >= 0 ? 0.0f : 1.0f;
-            const float4 L = s.sh_L[idx];
-            float4 r = s.radiance[px];
-            r.x += L.x * V;
-            r.y += L.y * V;
-            r.z += L.z * V;
-            s.radiance[px] = r;
+        [&](unsigned idx, const Ray&, const TravState& st) { resolve_shadow(s, idx, st); });
+}
+
+// One launch for the two ray sets that are ready after a shade stage: the closest-hit rays of the next bounce
+// (queue `cur`) and the shadow rays of the bounce just shaded (parity `sh`).  They are independent of each other, so
+// sharing the persistent warps removes one drain-out tail and one launch per bounce.  Long rays first.
+__global__ void __launch_bounds__(128, 8)
+k_trace_mixed(PtState s, int cur, int sh) {
+    const unsigned n_closest = s.cnt[cur], n_shadow = s.cnt[5 + sh];
+    const uint32_t* __restrict__ queue = s.queue[cur];
+    persistent_trace<false, true>(
+        s.nodes, s.tris, n_closest + n_shadow, s.cnt + 3,
+        [&](unsigned idx, Ray& r) {
+            if (idx < n_closest) {
+                fetch_closest_ray(s, queue, idx, r);
+                return false;
+            }
+            fetch_shadow_ray(s, idx - n_closest, r);
+            return true;
+        },
+        [&](unsigned idx, const Ray& r, const TravState& st) {
+            if (idx < n_closest) store_closest_hit(s, queue, idx, r, st);
+            else resolve_shadow(s, idx - n_closest, st);
         });
 }
 
@@ -177,7 +217,7 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
                 pushNext = out.continues;
             }
         }
-        const unsigned si = warp_push(pushShadow, s.cnt + 2);
+        const unsigned si = warp_push(pushShadow, s.cnt + 5 + (bounce & 1));
         if (pushShadow) {
             s.sh_o[si] = make_float4(out.shadow.o.x, out.shadow.o.y, out.shadow.o.z, out.shadow.tmax);
             s.sh_d[si] = make_float4(out.shadow.d.x, out.shadow.d.y, out.shadow.d.z, __int_as_float((int)px));
@@ -214,21 +254,24 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
     k_raygen<<<(n_pixels + 255) / 256, 256, 0, stream>>>(s, pixels, n_pixels);
     ++launches;
     if (s.numLights > 0) {   // RTPathTracingPass::update returns early without lights (:42-43); PathTracing.cl:72
+        // bounce b: [closest-hit trace of b  +  any-hit trace / resolve of b - 1] -> shade b;  then the last shadow set
         int cur = 0;
         for (int b = 0; b < max_depth; ++b) {
-            k_bounce_ctl<<<1, 32, 0, stream>>>(s.cnt, s.stats, cur, b == 0, n_pixels);
+            k_bounce_ctl<<<1, 32, 0, stream>>>(s.cnt, s.stats, cur, b, n_pixels);
             if (timer) timer->mark(stream);
-            k_trace_closest<<<trace_blocks, 128, 0, stream>>>(s, cur);
-            if (timer) timer->mark(stream);
+            if (b == 0) k_trace_closest<<<trace_blocks, 128, 0, stream>>>(s, cur);
+            else k_trace_mixed<<<trace_blocks, 128, 0, stream>>>(s, cur, (b - 1) & 1);
+            if (timer) timer->mark(stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
             k_shade<<<shade_blocks, PT_SHADE_BLOCK, 0, stream>>>(s, cur, frame, b, max_depth);
-            if (timer) timer->mark(stream);
-            k_trace_shadow<<<trace_blocks, 128, 0, stream>>>(s);
-            if (timer) timer->mark(stream);
-            launches += 4;
+            if (timer) timer->mark(stream, StageTimer::SHADE);
+            launches += 3;
             cur = 1 - cur;
         }
-        k_sample_end<<<1, 32, 0, stream>>>(s.cnt, s.stats);
-        ++launches;
+        k_sample_end<<<1, 32, 0, stream>>>(s.cnt, s.stats, max_depth - 1);
+        if (timer) timer->mark(stream);
+        k_trace_shadow<<<trace_blocks, 128, 0, stream>>>(s, (max_depth - 1) & 1);
+        if (timer) timer->mark(stream, StageTimer::TRACE_SHADOW);
+        launches += 2;
     }
     *err = cudaGetLastError();
     return launches;

@@ -39,7 +39,7 @@ struct PtState {
     float4* sh_o;         // shadow queue: xyz origin, w tmax
     float4* sh_d;         // xyz direction, w = pixel index (int bits)
     float4* sh_L;         // rgb = throughput * L (unshadowed direct light)
-    unsigned int* cnt;    // [0],[1] queue counts, [2] shadow count, [3] closest work ctr, [4] shadow work ctr
+    unsigned int* cnt;    // [0],[1] queue counts, [3],[4] work counters, [5],[6] shadow counts by bounce parity
     unsigned long long* stats;  // [0] closest rays, [1] shadow rays, [2] shaded vertices, [3] samples
     // reference-layout (AoS) stage buffers
     void* aos_rays;        // RTRay[P]
@@ -58,20 +58,25 @@ struct PtState {
 // caller reads the gaps after a synchronise (ptb_profile_collect).  Marks per bounce: before the
 // closest-hit trace, before shade, before the shadow trace, after the shadow trace.
 struct StageTimer {
+    enum { NONE = -1, TRACE_CLOSEST = 0, TRACE_MIXED = 1, TRACE_SHADOW = 2, SHADE = 3, NUM_STAGES = 4 };   // = ptb_stage
     std::vector<cudaEvent_t> events;   // pool, grown on demand
+    std::vector<int> tags;             // what ran between the previous mark and this one
     size_t used = 0;
-    void mark(cudaStream_t stream) {
+    void mark(cudaStream_t stream, int tag = NONE) {
         if (used == events.size()) {
             cudaEvent_t e;
             cudaEventCreate(&e);
             events.push_back(e);
+            tags.push_back(NONE);
         }
+        tags[used] = tag;
         cudaEventRecord(events[used++], stream);
     }
     void reset() { used = 0; }
     void destroy() {
         for (cudaEvent_t e : events) cudaEventDestroy(e);
         events.clear();
+        tags.clear();
         used = 0;
     }
 };

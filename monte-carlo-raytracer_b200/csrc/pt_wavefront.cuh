@@ -28,11 +28,12 @@ __device__ __forceinline__ Scene make_scene(const PtState& s) {
 // ---------------------------------------------------------------------------------------------
 // persistent traversal over a queue
 // ---------------------------------------------------------------------------------------------
-template <bool ANY_HIT, typename Fetch, typename Store>
+// MIXED: fetch() returns the kind of the ray it loaded (true = any hit); otherwise its result is ignored.
+template <bool ANY_HIT, bool MIXED = false, typename Fetch, typename Store>
 __device__ __forceinline__ void persistent_trace(const uint4* nodes, const float4* tris, unsigned count,
                                                  unsigned int* work_counter, Fetch fetch, Store store) {
     const unsigned lane = threadIdx.x & 31u;
-    Traverser<ANY_HIT, false> trav{nodes, tris};
+    Traverser<ANY_HIT, false, MIXED> trav{nodes, tris};
     uint2 stack[MCRT_STACK_SIZE];
     TravState st;
     Ray ray;
@@ -52,8 +53,9 @@ __device__ __forceinline__ void persistent_trace(const uint4* nodes, const float
                 if (idx >= count) {
                     exhausted = true;
                 } else {
-                    fetch(idx, ray);
+                    const bool any = fetch(idx, ray);
                     trav.init(st, ray);
+                    if (MIXED) st.any_hit = any;
                     item = (int)idx;
                 }
             }

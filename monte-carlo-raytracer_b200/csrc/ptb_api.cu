@@ -434,25 +434,25 @@ int ptb_profile_enable(ptb_context* c, int on) {
     return 0;
 }
 
-int ptb_profile_collect(ptb_context* c, double* ms_closest, double* ms_shade, double* ms_shadow, int64_t* launches_each) {
+int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
     if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
     int rc = set_dev(c);
     if (rc) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
-    double acc[3] = {0.0, 0.0, 0.0};
-    int64_t n = 0;
-    for (size_t i = 0; i + 3 < c->timer.used; i += 4) {       // 4 marks per bounce (pt_kernels.h)
-        for (int k = 0; k < 3; ++k) {
-            float ms = 0.0f;
-            PTB_CUDA(cudaEventElapsedTime(&ms, c->timer.events[i + k], c->timer.events[i + k + 1]));
-            acc[k] += ms;
-        }
-        ++n;
+    double acc[mcrt::StageTimer::NUM_STAGES] = {0.0, 0.0, 0.0, 0.0};
+    int64_t n[mcrt::StageTimer::NUM_STAGES] = {0, 0, 0, 0};
+    for (size_t i = 1; i < c->timer.used; ++i) {
+        const int tag = c->timer.tags[i];
+        if (tag < 0) continue;
+        float t = 0.0f;
+        PTB_CUDA(cudaEventElapsedTime(&t, c->timer.events[i - 1], c->timer.events[i]));
+        acc[tag] += t;
+        n[tag] += 1;
     }
-    if (ms_closest) *ms_closest = acc[0];
-    if (ms_shade) *ms_shade = acc[1];
-    if (ms_shadow) *ms_shadow = acc[2];
-    if (launches_each) *launches_each = n;
+    for (int k = 0; k < mcrt::StageTimer::NUM_STAGES; ++k) {
+        if (ms) ms[k] = acc[k];
+        if (launches) launches[k] = n[k];
+    }
     c->timer.reset();
     return 0;
 }

@@ -67,8 +67,7 @@ def _lib():
             "ptb_denoise": [vp, ctypes.c_char_p, i, ctypes.c_float, ctypes.c_float],
             "ptb_tonemap": [vp, ctypes.c_char_p, ctypes.c_float],
             "ptb_profile_enable": [vp, ctypes.c_int],
-            "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
-                                    ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
+            "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
         }
         for name, args in sig.items():
             fn = getattr(lib, name)
@@ -264,11 +263,13 @@ class RenderPipeline:
     def profile_enable(self, on=True):
         _check(_lib().ptb_profile_enable(self.scene._h, int(bool(on))))
 
+    STAGES = ("k_trace_closest", "k_trace_mixed", "k_trace_shadow", "k_shade")     # ptb_stage
+
     def profile_collect(self):
-        """Summed device milliseconds of the three wavefront stages since the last collect."""
-        a, b, c, n = ctypes.c_double(), ctypes.c_double(), ctypes.c_double(), ctypes.c_int64()
-        _check(_lib().ptb_profile_collect(self.scene._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c), ctypes.byref(n)))
-        return {"closest_ms": a.value, "shade_ms": b.value, "shadow_ms": c.value, "bounces": n.value}
+        """{kernel: (summed device ms, launches)} of the wavefront's kernels since the last collect."""
+        ms, n = (ctypes.c_double * 4)(), (ctypes.c_int64 * 4)()
+        _check(_lib().ptb_profile_collect(self.scene._h, ms, n))
+        return {k: (ms[i], n[i]) for i, k in enumerate(self.STAGES)}
 
     def set_partition(self, part, num_parts):
         _check(_lib().ptb_set_partition(self.scene._h, int(part), int(num_parts)))

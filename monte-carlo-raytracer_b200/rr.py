@@ -32,7 +32,13 @@ class RrbStats(ctypes.Structure):
 
 
 def lib_path() -> str:
-    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "libmcrt_b200.so")
+    """libmcrt_b200.so next to this file.  MCRT_LIB_VARIANT=<name> selects build/variants/libmcrt_<name>.so, an
+    experiment build of the same sources with other -D knobs (tools/build_variants.py); never a fallback."""
+    here = os.path.dirname(os.path.abspath(__file__))
+    variant = os.environ.get("MCRT_LIB_VARIANT")
+    if variant:
+        return os.path.join(here, "build", "variants", "libmcrt_%s.so" % variant)
+    return os.path.join(here, "libmcrt_b200.so")
 
 
 def load_library():

@@ -11,5 +11,5 @@ b.build(force=True)" > /dev/null 2>&1 || { echo "BUILD FAILED: $v"; continue; }
 import json,sys
 d=json.loads(sys.stdin.readline())
 r=d['roofline']
-print('%-70s ms/step %.3f  closest %.3f shade %.3f shadow %.3f  Mpaths/s %.1f' % ('$v', d['ms_per_step'], r['stage_ms_per_step']['k_trace_closest'], r['stage_ms_per_step']['k_shade'], r['stage_ms_per_step']['k_trace_shadow'], d['value']/1e6))"
+print('%-70s ms/step %.3f  closest0 %.3f mixed %.3f shadowN %.3f shade %.3f  Mpaths/s %.1f' % ('$v', d['ms_per_step'], r['stage_ms_per_step']['k_trace_closest'], r['stage_ms_per_step']['k_trace_mixed'], r['stage_ms_per_step']['k_trace_shadow'], r['stage_ms_per_step']['k_shade'], d['value']/1e6))"
 done
