@@ -112,6 +112,10 @@ int ptb_pt_shadow_resolve(ptb_context* ctx, int bounce);                        
 int ptb_pt_render_sample(ptb_context* ctx, int frame, int max_depth);
 /* Same for RTBDPTPass::update. */
 int ptb_bdpt_render_sample(ptb_context* ctx, int frame, int max_depth);
+/* How ptb_pt_render_sample issues a frame: 2 (default) = the pixel set is split in two halves whose wavefronts run
+ * on two streams, so that each kernel's drain-out tail is filled by the other half's kernels;
+ * 1 = one wavefront on the context's stream.  Per-sample results are identical. */
+int ptb_set_overlap(ptb_context* ctx, int halves);
 
 /* Per-kernel device timing of the fused wavefront (no reference counterpart; measurement only).
  * While enabled, CUDA events are recorded on the context's stream around every traversal and shade launch;

@@ -25,14 +25,15 @@ namespace mcrt {
 //      closest-hit rays of bounce b + 1, while nothing writes either set)
 __global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int cur, int bounce, int n_first) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    // stats are shared by the two halves of a frame (two streams): atomic adds
     if (bounce == 0) {
         cnt[cur] = (unsigned)n_first;
-        stats[3] += (unsigned long long)n_first;
+        atomicAdd(stats + 3, (unsigned long long)n_first);
     } else {
-        stats[1] += cnt[5 + ((bounce - 1) & 1)];   // shadow rays of the bounce that was just shaded
+        atomicAdd(stats + 1, (unsigned long long)cnt[5 + ((bounce - 1) & 1)]);   // shadow rays of the bounce just shaded
     }
-    stats[0] += cnt[cur];     // closest-hit rays of the bounce about to start
-    stats[2] += cnt[cur];     // = path vertices handed to the shade stage
+    atomicAdd(stats + 0, (unsigned long long)cnt[cur]);     // closest-hit rays of the bounce about to start
+    atomicAdd(stats + 2, (unsigned long long)cnt[cur]);     // = path vertices handed to the shade stage
     cnt[1 - cur] = 0;
     cnt[5 + (bounce & 1)] = 0;
     cnt[3] = 0;
@@ -40,7 +41,7 @@ __global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int c
 }
 __global__ void k_sample_end(unsigned int* cnt, unsigned long long* stats, int last_bounce) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    stats[1] += cnt[5 + (last_bounce & 1)];
+    atomicAdd(stats + 1, (unsigned long long)cnt[5 + (last_bounce & 1)]);
     cnt[4] = 0;
 }
 
@@ -48,10 +49,10 @@ __global__ void k_sample_end(unsigned int* cnt, unsigned long long* stats, int l
 // primary rays (GeneratePerspectiveRays, PathTracing.cl:13-35) + radiance clear + queue fill
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-k_raygen(PtState s, const uint32_t* __restrict__ pixels, int n) {
+k_raygen(PtState s, const uint32_t* __restrict__ pixels, int first, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint32_t px = pixels ? pixels[i] : (uint32_t)i;
+    const uint32_t px = pixels ? pixels[first + i] : (uint32_t)(first + i);
     const RTPinholeCamera* cam = (const RTPinholeCamera*)s.camera;
     const int x = (int)(px % (uint32_t)s.width), y = (int)(px / (uint32_t)s.width);
     const V3 d = primary_ray_dir(cam, x, y);
@@ -169,7 +170,10 @@ k_trace_mixed(PtState s, int cur, int sh) {
 #ifndef PT_SHADE_CTAS_PER_SM
 #define PT_SHADE_CTAS_PER_SM (512 / PT_SHADE_BLOCK > 0 ? 512 / PT_SHADE_BLOCK : 1)   // 16 resident warps at ~115 registers
 #endif
-__global__ void __launch_bounds__(PT_SHADE_BLOCK, 1)
+#ifndef PT_SHADE_MIN_BLOCKS
+#define PT_SHADE_MIN_BLOCKS 1      // register cap = 64K / (PT_SHADE_BLOCK * PT_SHADE_MIN_BLOCKS)
+#endif
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
 k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
     const unsigned count = s.cnt[cur];
     const Scene sc = make_scene(s);
@@ -240,38 +244,79 @@ static int env_int(const char* name, int dflt) {
 }
 
 int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int frame, int max_depth,
-                     cudaStream_t stream, cudaError_t* err, StageTimer* timer) {
+                     cudaStream_t stream, cudaError_t* err, StageTimer* timer, const PtOverlap* overlap) {
     int launches = 0;
     *err = cudaSuccess;
     if (n_pixels <= 0) return 0;
     const int sms = sm_count();
     // CTAs per SM of the persistent kernels; the environment overrides exist for co-scheduling experiments
-    // (two contexts on two streams sharing the SMs) and are read once.
+    // and are read once.
     static const int trace_per_sm = env_int("MCRT_TRACE_CTAS_PER_SM", 8);
     static const int shade_per_sm = env_int("MCRT_SHADE_CTAS_PER_SM", PT_SHADE_CTAS_PER_SM);
-    const int trace_blocks = min(sms * trace_per_sm, (n_pixels + 127) / 128);
-    const int shade_blocks = min(sms * shade_per_sm, (n_pixels + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK);
-    k_raygen<<<(n_pixels + 255) / 256, 256, 0, stream>>>(s, pixels, n_pixels);
-    ++launches;
+    static const int stagger = env_int("MCRT_OVERLAP_STAGGER", 0);   // measured: no gain from starting the halves a stage apart
+
+    // the frame as one wavefront, or as two half-frame wavefronts on two streams (PtOverlap)
+    struct Half {
+        PtState s;
+        int first, n;
+        cudaStream_t stream;
+    } half[2];
+    const int nh = (overlap && n_pixels >= 2 * 32768) ? 2 : 1;
+    half[0] = {s, 0, nh == 2 ? n_pixels / 2 : n_pixels, stream};
+    if (nh == 2) {
+        const int nA = half[0].n;
+        PtState t = s;           // compact (queue-indexed) arrays and the counters of the second half
+        t.queue[0] += nA;
+        t.queue[1] += nA;
+        t.sh_o += nA;
+        t.sh_d += nA;
+        t.sh_L += nA;
+        t.cnt += 8;
+        half[1] = {t, nA, n_pixels - nA, overlap->stream};
+        cudaEventRecord(overlap->fork, stream);
+        cudaStreamWaitEvent(overlap->stream, overlap->fork, 0);
+    }
+    int cur[2] = {0, 0};
+    auto blocks_trace = [&](int n) { return min(sms * trace_per_sm, (n + 127) / 128); };
+    auto blocks_shade = [&](int n) { return min(sms * shade_per_sm, (n + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK); };
+    for (int h = 0; h < nh; ++h) {
+        k_raygen<<<(half[h].n + 255) / 256, 256, 0, half[h].stream>>>(half[h].s, pixels, half[h].first, half[h].n);
+        ++launches;
+    }
     if (s.numLights > 0) {   // RTPathTracingPass::update returns early without lights (:42-43); PathTracing.cl:72
         // bounce b: [closest-hit trace of b  +  any-hit trace / resolve of b - 1] -> shade b;  then the last shadow set
-        int cur = 0;
         for (int b = 0; b < max_depth; ++b) {
-            k_bounce_ctl<<<1, 32, 0, stream>>>(s.cnt, s.stats, cur, b, n_pixels);
-            if (timer) timer->mark(stream);
-            if (b == 0) k_trace_closest<<<trace_blocks, 128, 0, stream>>>(s, cur);
-            else k_trace_mixed<<<trace_blocks, 128, 0, stream>>>(s, cur, (b - 1) & 1);
-            if (timer) timer->mark(stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
-            k_shade<<<shade_blocks, PT_SHADE_BLOCK, 0, stream>>>(s, cur, frame, b, max_depth);
-            if (timer) timer->mark(stream, StageTimer::SHADE);
-            launches += 3;
-            cur = 1 - cur;
+            for (int h = 0; h < nh; ++h) {
+                const Half& H = half[h];
+                k_bounce_ctl<<<1, 32, 0, H.stream>>>(H.s.cnt, H.s.stats, cur[h], b, H.n);
+                if (timer) timer->mark(h, H.stream);
+                if (b == 0) {
+                    // experiment knob: start the second half one stage behind the first
+                    if (h == 1 && stagger) cudaStreamWaitEvent(H.stream, overlap->stagger, 0);
+                    k_trace_closest<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h]);
+                    if (h == 0 && nh == 2 && stagger) cudaEventRecord(overlap->stagger, H.stream);
+                } else {
+                    k_trace_mixed<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1);
+                }
+                if (timer) timer->mark(h, H.stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
+                k_shade<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth);
+                if (timer) timer->mark(h, H.stream, StageTimer::SHADE);
+                launches += 3;
+                cur[h] = 1 - cur[h];
+            }
         }
-        k_sample_end<<<1, 32, 0, stream>>>(s.cnt, s.stats, max_depth - 1);
-        if (timer) timer->mark(stream);
-        k_trace_shadow<<<trace_blocks, 128, 0, stream>>>(s, (max_depth - 1) & 1);
-        if (timer) timer->mark(stream, StageTimer::TRACE_SHADOW);
-        launches += 2;
+        for (int h = 0; h < nh; ++h) {
+            const Half& H = half[h];
+            k_sample_end<<<1, 32, 0, H.stream>>>(H.s.cnt, H.s.stats, max_depth - 1);
+            if (timer) timer->mark(h, H.stream);
+            k_trace_shadow<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1);
+            if (timer) timer->mark(h, H.stream, StageTimer::TRACE_SHADOW);
+            launches += 2;
+        }
+    }
+    if (nh == 2) {
+        cudaEventRecord(overlap->join, overlap->stream);
+        cudaStreamWaitEvent(stream, overlap->join, 0);
     }
     *err = cudaGetLastError();
     return launches;

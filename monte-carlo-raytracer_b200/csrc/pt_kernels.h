@@ -59,32 +59,49 @@ struct PtState {
 // closest-hit trace, before shade, before the shadow trace, after the shadow trace.
 struct StageTimer {
     enum { NONE = -1, TRACE_CLOSEST = 0, TRACE_MIXED = 1, TRACE_SHADOW = 2, SHADE = 3, NUM_STAGES = 4 };   // = ptb_stage
-    std::vector<cudaEvent_t> events;   // pool, grown on demand
-    std::vector<int> tags;             // what ran between the previous mark and this one
-    size_t used = 0;
-    void mark(cudaStream_t stream, int tag = NONE) {
-        if (used == events.size()) {
+    // one sequence of marks per stream ("lane") the frame is issued on; intervals are taken between consecutive
+    // marks of a lane, so kernels of the two lanes that overlap on the device are each timed as they ran
+    struct Lane {
+        std::vector<cudaEvent_t> events;   // pool, grown on demand
+        std::vector<int> tags;             // what ran between the previous mark and this one
+        size_t used = 0;
+    };
+    Lane lanes[2];
+    void mark(int lane, cudaStream_t stream, int tag = NONE) {
+        Lane& l = lanes[lane];
+        if (l.used == l.events.size()) {
             cudaEvent_t e;
             cudaEventCreate(&e);
-            events.push_back(e);
-            tags.push_back(NONE);
+            l.events.push_back(e);
+            l.tags.push_back(NONE);
         }
-        tags[used] = tag;
-        cudaEventRecord(events[used++], stream);
+        l.tags[l.used] = tag;
+        cudaEventRecord(l.events[l.used++], stream);
     }
-    void reset() { used = 0; }
+    void reset() { lanes[0].used = lanes[1].used = 0; }
     void destroy() {
-        for (cudaEvent_t e : events) cudaEventDestroy(e);
-        events.clear();
-        tags.clear();
-        used = 0;
+        for (Lane& l : lanes) {
+            for (cudaEvent_t e : l.events) cudaEventDestroy(e);
+            l.events.clear();
+            l.tags.clear();
+            l.used = 0;
+        }
     }
+};
+
+// Second stream of a frame (owned by the context).  With it the frame's pixels are split in two halves whose
+// wavefronts are issued on the two streams, so that the drain-out tail of every kernel of one half is filled by
+// the other half's kernels (results are per-pixel and unchanged).
+struct PtOverlap {
+    cudaStream_t stream;
+    cudaEvent_t fork, join, stagger;
 };
 
 // One frame of the fused wavefront path tracer.  `pixels` (device, may be NULL = identity) lists the
 // n_pixels global pixel indices this context owns.  Returns the number of kernels launched.
 int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int frame, int max_depth,
-                     cudaStream_t stream, cudaError_t* err, StageTimer* timer = nullptr);
+                     cudaStream_t stream, cudaError_t* err, StageTimer* timer = nullptr,
+                     const PtOverlap* overlap = nullptr);
 
 // Stage-wise, reference layouts.
 cudaError_t launch_generate_primary_rays(const PtState& s, cudaStream_t stream);

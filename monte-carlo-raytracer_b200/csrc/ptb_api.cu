@@ -6,6 +6,7 @@
 // RTPrimaryRaysPass / RTPathTracingPass / RTReconstructionPass.  No CPU fallback.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -58,6 +59,8 @@ struct ptb_context {
     int sobol_dims = 0;
     bool profiling = false;
     mcrt::StageTimer timer;
+    mcrt::PtOverlap overlap{nullptr, nullptr, nullptr, nullptr};   // second stream of a frame (ptb_set_overlap)
+    int halves = 2;
     ptb_context() {
         std::memset(&st, 0, sizeof(st));
         std::memset(&bd, 0, sizeof(bd));
@@ -202,7 +205,21 @@ int ptb_create(rrb_api* api, ptb_context** out) {
     rc = alloc_into(c->named, "__camera", 176, true, c->stream, &p);
     if (rc) return rc;
     c->st.camera = p;
+    if (const char* v = getenv("MCRT_OVERLAP_HALVES")) c->halves = atoi(v) == 1 ? 1 : 2;   // profiling aid
+    PTB_CUDA(cudaStreamCreateWithFlags(&c->overlap.stream, cudaStreamNonBlocking));
+    PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.fork, cudaEventDisableTiming));
+    PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.join, cudaEventDisableTiming));
+    PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.stagger, cudaEventDisableTiming));
     *out = c.release();
+    return 0;
+}
+
+int ptb_set_overlap(ptb_context* c, int halves) {
+    if (!c || (halves != 1 && halves != 2)) return pfail(RRB_ERROR_INVALID_ARGUMENT, "halves must be 1 or 2");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    c->halves = halves;
     return 0;
 }
 
@@ -219,6 +236,13 @@ int ptb_destroy(ptb_context* c) {
     if (c->d_pixels) cudaFree(c->d_pixels);
     if (c->d_sobol) cudaFree((void*)c->d_sobol);
     c->timer.destroy();
+    if (c->overlap.stream) {
+        cudaStreamSynchronize(c->overlap.stream);
+        cudaStreamDestroy(c->overlap.stream);
+        cudaEventDestroy(c->overlap.fork);
+        cudaEventDestroy(c->overlap.join);
+        cudaEventDestroy(c->overlap.stagger);
+    }
     delete c;
     return 0;
 }
@@ -419,7 +443,7 @@ int ptb_pt_render_sample(ptb_context* c, int frame, int max_depth) {
     if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
     cudaError_t e = cudaSuccess;
     c->launches += mcrt::launch_pt_sample(c->st, c->d_pixels, c->n_pixels, frame, max_depth, c->stream, &e,
-                                          c->profiling ? &c->timer : nullptr);
+                                          c->profiling ? &c->timer : nullptr, c->halves == 2 ? &c->overlap : nullptr);
     if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("path tracer launch: ") + cudaGetErrorString(e));
     return 0;
 }
@@ -441,14 +465,15 @@ int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     double acc[mcrt::StageTimer::NUM_STAGES] = {0.0, 0.0, 0.0, 0.0};
     int64_t n[mcrt::StageTimer::NUM_STAGES] = {0, 0, 0, 0};
-    for (size_t i = 1; i < c->timer.used; ++i) {
-        const int tag = c->timer.tags[i];
-        if (tag < 0) continue;
-        float t = 0.0f;
-        PTB_CUDA(cudaEventElapsedTime(&t, c->timer.events[i - 1], c->timer.events[i]));
-        acc[tag] += t;
-        n[tag] += 1;
-    }
+    for (const mcrt::StageTimer::Lane& l : c->timer.lanes)
+        for (size_t i = 1; i < l.used; ++i) {
+            const int tag = l.tags[i];
+            if (tag < 0) continue;
+            float t = 0.0f;
+            PTB_CUDA(cudaEventElapsedTime(&t, l.events[i - 1], l.events[i]));
+            acc[tag] += t;
+            n[tag] += 1;
+        }
     for (int k = 0; k < mcrt::StageTimer::NUM_STAGES; ++k) {
         if (ms) ms[k] = acc[k];
         if (launches) launches[k] = n[k];

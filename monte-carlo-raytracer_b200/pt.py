@@ -66,7 +66,7 @@ def _lib():
             "ptb_set_sampler": [vp, i, vp, i],
             "ptb_denoise": [vp, ctypes.c_char_p, i, ctypes.c_float, ctypes.c_float],
             "ptb_tonemap": [vp, ctypes.c_char_p, ctypes.c_float],
-            "ptb_profile_enable": [vp, ctypes.c_int],
+            "ptb_profile_enable": [vp, ctypes.c_int], "ptb_set_overlap": [vp, ctypes.c_int],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
         }
         for name, args in sig.items():
@@ -270,6 +270,9 @@ class RenderPipeline:
         ms, n = (ctypes.c_double * 4)(), (ctypes.c_int64 * 4)()
         _check(_lib().ptb_profile_collect(self.scene._h, ms, n))
         return {k: (ms[i], n[i]) for i, k in enumerate(self.STAGES)}
+
+    def set_overlap(self, halves):
+        _check(_lib().ptb_set_overlap(self.scene._h, int(halves)))
 
     def set_partition(self, part, num_parts):
         _check(_lib().ptb_set_partition(self.scene._h, int(part), int(num_parts)))

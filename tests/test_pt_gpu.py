@@ -382,3 +382,33 @@ def test_dynamic_scene_refit_equals_fresh_scene(api):
         rp = ref.RefPathTracer(o, fresh, o.build_scene_bvh(fresh), w, h)
         cam = camera.make_camera(fresh.camera, w, h, camera.taa_pixel_offset(1))
         check_against(got[0], rp.render_sample(cam, 1, depth), 0.99)
+
+
+def test_two_stream_half_frames_equal_single_wavefront_bitwise(api, cornell):
+    """ptb_set_overlap: a frame issued as two half-frame wavefronts on two streams gives, bit for bit, the radiance
+    and the counters of the same frame issued as one wavefront."""
+    w, h, depth = 512, 320, 5          # 163,840 pixels: above the split threshold
+    res = []
+    for halves in (2, 1):
+        a = api if halves == 2 else rr.IntersectionApi.Create(0)
+        try:
+            pl = pt.make_pt_pipeline(a, cornell, w, h, depth)
+            pl.ensure_size()
+            pl.set_overlap(halves)
+            frames = []
+            for _ in range(3):
+                pl.update()
+                frames.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+            img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+            cnt = pl.counters()
+            pl.scene.destroy()
+        finally:
+            if halves == 1:
+                rr.IntersectionApi.Delete(a)
+        res.append((frames, img, cnt))
+    for f in range(3):
+        assert np.array_equal(res[0][0][f].view(np.uint32), res[1][0][f].view(np.uint32))
+    assert np.array_equal(res[0][1].view(np.uint32), res[1][1].view(np.uint32))
+    for k in ("samples", "closest_rays", "shadow_rays", "shaded_vertices"):
+        assert res[0][2][k] == res[1][2][k], k
+    assert res[0][2]["kernel_launches"] > res[1][2]["kernel_launches"]
