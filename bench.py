@@ -248,8 +248,9 @@ def own_arm(args):
     t_fw = torch.as_tensor(DevView(fw_ptr, fw_bytes), device=dev)
     t_img = torch.as_tensor(DevView(img_ptr, img_bytes), device=dev)
     merger = multi_gpu.PipelinedMerger(P, dev) if world > 1 else None
-    host_img = torch.empty(4 * P, dtype=torch.float32, pin_memory=True)
-    host_np = host_img.numpy()
+    host_imgs = [torch.empty(4 * P, dtype=torch.float32, pin_memory=True) for _ in range(2)]   # double-buffered
+    host_nps = [t.numpy() for t in host_imgs]
+    host_np = host_nps[0]
 
     def cam_for(frame):
         off = camera.taa_pixel_offset(frame, pl.GI.filterRadius, True)
@@ -274,13 +275,15 @@ def own_arm(args):
         if world > 1:
             merge()
 
-    def e2e_step(frame):
-        """The call a user makes: pipeline.update() (host camera build + upload) and the image on the host."""
+    def e2e_step(frame, slot=0):
+        """The call a user makes: pipeline.update() (host camera build + upload) and the image of every frame on
+        the host -- read back through the pipelined ptb_read_buffer_async (device snapshot, then a copy into pinned
+        memory behind the next frame's kernels; the last copy is waited for inside the timed region)."""
         pt_pass.m_frameIndex = frame
         pl.update()
         if world > 1:
             merge()
-        pt._check(lib.ptb_read_buffer(h, b"NextFrameImageCL", host_np.ctypes.data_as(ctypes.c_void_p), host_np.nbytes))
+        pl.read_buffer_async("NextFrameImageCL", host_nps[slot & 1])
 
     def barrier():
         if world > 1:
@@ -345,18 +348,20 @@ def own_arm(args):
         # ---------------- end to end through the pipeline mirror, image read back every step
         pt._check(lib.ptb_reset_accumulation(h))
         for s in range(Wm):
-            e2e_step(frames[s])
+            e2e_step(frames[s], s)
         merge_flush()
+        pl.read_wait()
         barrier()
         ev0.record(stream)
         for s in range(Wm, Wm + K):
-            e2e_step(frames[s])
+            e2e_step(frames[s], s)
         merge_flush()
+        pl.read_wait()                      # the last frame's image is on the host before the clock stops
         ev1.record(stream)
         barrier()
         ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
         clocks = sampler.stop() if rank == 0 else None
-        img_mean = float(host_np.reshape(-1, 4)[:, :3].mean())
+        img_mean = float(host_nps[(Wm + K - 1) & 1].reshape(-1, 4)[:, :3].mean())
 
     paths_total = sum_over_ranks(float(cnt["samples"]))
     closest_total = sum_over_ranks(float(cnt["closest_rays"]))

@@ -147,6 +147,12 @@ int ptb_tonemap(ptb_context* ctx, const char* src_name, float lwhite);
 int ptb_get_buffer(ptb_context* ctx, const char* name, void** device_ptr, size_t* bytes);
 /* Blocking device->host read of a named buffer (the step's result for the end-to-end leg). */
 int ptb_read_buffer(ptb_context* ctx, const char* name, void* host_dst, size_t bytes);
+/* Pipelined read-back for a consumer that wants the image every frame (the role of RTDisplayPass): snapshots the
+ * buffer on the context's stream (device-to-device), then copies the snapshot to `host_dst` (pinned memory) on a
+ * copy stream while the next frame renders.  `host_dst` is valid after ptb_read_wait, or after the next
+ * ptb_read_buffer_async (which waits for the previous copy first).  One copy in flight per context. */
+int ptb_read_buffer_async(ptb_context* ctx, const char* name, void* host_dst, size_t bytes);
+int ptb_read_wait(ptb_context* ctx);
 int ptb_synchronize(ptb_context* ctx);
 int ptb_get_counters(ptb_context* ctx, ptb_counters* out);
 int ptb_reset_counters(ptb_context* ctx);

@@ -60,6 +60,12 @@ struct ptb_context {
     bool profiling = false;
     mcrt::StageTimer timer;
     mcrt::PtOverlap overlap{nullptr, nullptr, nullptr, nullptr};   // second stream of a frame (ptb_set_overlap)
+    // asynchronous read-back (ptb_read_buffer_async): device snapshot + copy stream
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t snap_ready = nullptr, copy_done = nullptr;
+    void* snapshot = nullptr;
+    size_t snapshot_bytes = 0;
+    bool copy_pending = false;
     int halves = 2;
     ptb_context() {
         std::memset(&st, 0, sizeof(st));
@@ -236,6 +242,13 @@ int ptb_destroy(ptb_context* c) {
     if (c->d_pixels) cudaFree(c->d_pixels);
     if (c->d_sobol) cudaFree((void*)c->d_sobol);
     c->timer.destroy();
+    if (c->copy_stream) {
+        cudaStreamSynchronize(c->copy_stream);
+        cudaStreamDestroy(c->copy_stream);
+        cudaEventDestroy(c->snap_ready);
+        cudaEventDestroy(c->copy_done);
+        if (c->snapshot) cudaFree(c->snapshot);
+    }
     if (c->overlap.stream) {
         cudaStreamSynchronize(c->overlap.stream);
         cudaStreamDestroy(c->overlap.stream);
@@ -596,6 +609,46 @@ int ptb_read_buffer(ptb_context* c, const char* name, void* host_dst, size_t byt
     if ((rc = set_dev(c))) return rc;
     PTB_CUDA(cudaMemcpyAsync(host_dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
     PTB_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int ptb_read_wait(ptb_context* c) {
+    if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
+    if (!c->copy_pending) return 0;
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaEventSynchronize(c->copy_done));
+    c->copy_pending = false;
+    return 0;
+}
+
+int ptb_read_buffer_async(ptb_context* c, const char* name, void* host_dst, size_t bytes) {
+    void* p = nullptr;
+    size_t n = 0;
+    int rc = ptb_get_buffer(c, name, &p, &n);
+    if (rc) return rc;
+    if (!host_dst || bytes > n) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad destination or size");
+    if ((rc = set_dev(c))) return rc;
+    if (!c->copy_stream) {
+        PTB_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        PTB_CUDA(cudaEventCreateWithFlags(&c->snap_ready, cudaEventDisableTiming));
+        PTB_CUDA(cudaEventCreateWithFlags(&c->copy_done, cudaEventDisableTiming));
+    }
+    if ((rc = ptb_read_wait(c))) return rc;            // the one snapshot is free again
+    if (c->snapshot_bytes < bytes) {
+        if (c->snapshot) cudaFree(c->snapshot);
+        c->snapshot = nullptr;
+        c->snapshot_bytes = 0;
+        cudaError_t e = cudaMalloc(&c->snapshot, bytes);
+        if (e != cudaSuccess) return pfail(RRB_ERROR_OUT_OF_MEMORY, std::string("cudaMalloc(snapshot): ") + cudaGetErrorString(e));
+        c->snapshot_bytes = bytes;
+    }
+    PTB_CUDA(cudaMemcpyAsync(c->snapshot, p, bytes, cudaMemcpyDeviceToDevice, c->stream));
+    PTB_CUDA(cudaEventRecord(c->snap_ready, c->stream));
+    PTB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->snap_ready, 0));
+    PTB_CUDA(cudaMemcpyAsync(host_dst, c->snapshot, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    PTB_CUDA(cudaEventRecord(c->copy_done, c->copy_stream));
+    c->copy_pending = true;
     return 0;
 }
 

@@ -67,6 +67,7 @@ def _lib():
             "ptb_denoise": [vp, ctypes.c_char_p, i, ctypes.c_float, ctypes.c_float],
             "ptb_tonemap": [vp, ctypes.c_char_p, ctypes.c_float],
             "ptb_profile_enable": [vp, ctypes.c_int], "ptb_set_overlap": [vp, ctypes.c_int],
+            "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
         }
         for name, args in sig.items():
@@ -248,6 +249,13 @@ class RenderPipeline:
             out = np.empty(n // np.dtype(dtype).itemsize, dtype=dtype)
         _check(_lib().ptb_read_buffer(self.scene._h, name.encode(), _ptr(out), out.nbytes))
         return out
+
+    def read_buffer_async(self, name, out):
+        """Snapshot + copy to the (pinned) array `out` behind the next frame; valid after read_wait()."""
+        _check(_lib().ptb_read_buffer_async(self.scene._h, name.encode(), _ptr(out), out.nbytes))
+
+    def read_wait(self):
+        _check(_lib().ptb_read_wait(self.scene._h))
 
     def counters(self):
         c = PtbCounters()

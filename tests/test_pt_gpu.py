@@ -412,3 +412,23 @@ def test_two_stream_half_frames_equal_single_wavefront_bitwise(api, cornell):
     for k in ("samples", "closest_rays", "shadow_rays", "shaded_vertices"):
         assert res[0][2][k] == res[1][2][k], k
     assert res[0][2]["kernel_launches"] > res[1][2]["kernel_launches"]
+
+
+def test_pipelined_readback_equals_blocking_read(api, cornell):
+    """ptb_read_buffer_async: the snapshot copied behind the next frame is the image of the frame it was issued
+    after, even though the next frame's accumulate has overwritten the device buffer in the meantime."""
+    import torch
+    w = h = 128
+    pl = pt.make_pt_pipeline(api, cornell, w, h, 3)
+    host = [torch.empty(4 * w * h, dtype=torch.float32, pin_memory=True).numpy() for _ in range(2)]
+    want = []
+    for f in range(3):
+        pl.update()
+        pl.read_buffer_async("NextFrameImageCL", host[f & 1])
+        want.append(pl.read_buffer("NextFrameImageCL").copy())      # blocking read of the same frame
+        if f >= 1:
+            # slot (f - 1) & 1 was waited for by the async call above and holds frame f - 1
+            assert np.array_equal(host[(f - 1) & 1].view(np.uint32), want[f - 1].view(np.uint32))
+    pl.read_wait()
+    assert np.array_equal(host[0].view(np.uint32), want[2].view(np.uint32))
+    pl.scene.destroy()
