@@ -198,7 +198,7 @@ def reference_arm(args):
                              "sample": hr.describe(), "bvh_build_s": hr.build_s},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -428,7 +428,7 @@ def own_arm(args):
                         "d2h_bytes_per_step": int(host_np.nbytes), "image_mean": img_mean},
                 "gpu_launches": launches_total, "clocks": clocks,
                 "bvh": {"build_and_upload_s": setup_s, "nodes": int(stats.get("num_nodes", 0)) if isinstance(stats, dict) else None}}
-        print(json.dumps(line), flush=True)
+        emit(line)
     pl.scene.destroy()
     rr.IntersectionApi.Delete(api)
     if world > 1:
@@ -436,7 +436,26 @@ def own_arm(args):
     return 0
 
 
+_RESULT_FD = None
+
+
+def emit(line):
+    """The ONE JSON line of the contract, on the process's real stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    # Libraries (NCCL prints its version banner, torchrun its OMP note) write to stdout; the contract is one JSON
+    # line there.  Everything but that line goes to stderr.
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         return reference_arm(args)
