@@ -116,6 +116,13 @@ int ptb_bdpt_render_sample(ptb_context* ctx, int frame, int max_depth);
  * on two streams, so that each kernel's drain-out tail is filled by the other half's kernels;
  * 1 = one wavefront on the context's stream.  Per-sample results are identical. */
 int ptb_set_overlap(ptb_context* ctx, int halves);
+/* Order of the live-path queues of ptb_pt_render_sample.  The reference's sampler is a pure function of (pixel, frame,
+ * bounce) (samplers.cl:75-84), so which light a vertex will sample and which half of the lobe-selection variate it
+ * will draw are known before its ray is traced: 1 = queues of bounces >= 1 are bucketed by that key (warps of the
+ * shade kernel take the same light / lobe branches), 2 = bounce 0 as well, 0 = push order.  Per-sample results are
+ * identical in all modes. */
+#define PTB_DEFAULT_COHERENCE 1
+int ptb_set_coherence(ptb_context* ctx, int mode);
 
 /* Per-kernel device timing of the fused wavefront (no reference counterpart; measurement only).
  * While enabled, CUDA events are recorded on the context's stream around every traversal and shade launch;

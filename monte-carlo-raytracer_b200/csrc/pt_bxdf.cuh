@@ -37,13 +37,13 @@ HD float evalTanTheta(V3 w) { return evalSinTheta(w) / evalCosTheta(w); }
 HD float evalTanSqTheta(V3 w) { return evalSinSqTheta(w) / evalCosSqTheta(w); }
 HD float evalCosPhi(V3 w) {
     float st = evalSinTheta(w);
-    return st == 0 ? 1.0f : clampf(w.x / st, -1.0f, 1.0f);
+    return st == 0 ? 1.0f : clampf(fdiv(w.x, st), -1.0f, 1.0f);
 }
 // bxdfs.cl:35-39 compares a function pointer with 0, so the division always happens (E8);
 // clamp(NaN) is defined as fmin(fmax(x,-1),1) = -1 here and in the oracle.
 HD float evalSinPhi(V3 w) {
     float st = evalSinTheta(w);
-    return clampf(w.z / st, -1.0f, 1.0f);
+    return clampf(fdiv(w.z, st), -1.0f, 1.0f);
 }
 HD float evalCosSqPhi(V3 w) { return evalCosPhi(w) * evalCosPhi(w); }
 HD float evalSinSqPhi(V3 w) { return evalSinPhi(w) * evalSinPhi(w); }
@@ -76,8 +76,8 @@ HD_BXDF float evaluateFresnelDielectric(float cosThetaI, float etaI, float etaT)
     float sinThetaT = etaI / etaT * sinThetaI;
     if (sinThetaT >= 1.0f) return 1.0f;
     float cosThetaT = sqrtf(fmaxf(0.0f, 1.0f - sinThetaT * sinThetaT));
-    float rparl = ((etaT * cosThetaI) - (etaI * cosThetaT)) / ((etaT * cosThetaI) + (etaI * cosThetaT));
-    float rperp = ((etaI * cosThetaI) - (etaT * cosThetaT)) / ((etaI * cosThetaI) + (etaT * cosThetaT));
+    float rparl = fdiv((etaT * cosThetaI) - (etaI * cosThetaT), (etaT * cosThetaI) + (etaI * cosThetaT));
+    float rperp = fdiv((etaI * cosThetaI) - (etaT * cosThetaT), (etaI * cosThetaI) + (etaT * cosThetaT));
     return (rparl * rparl + rperp * rperp) * 0.5f;
 }
 

@@ -23,8 +23,19 @@ namespace mcrt {
 // cnt: [0],[1] live-path queue sizes (ping-pong)  [3],[4] work counters of the persistent kernels
 //      [5],[6] shadow-ray counts by bounce parity (the shadow rays of bounce b are traced together with the
 //      closest-hit rays of bounce b + 1, while nothing writes either set)
-__global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int cur, int bounce, int n_first) {
+//      [8..15] coherence-bucket counts of the queue being filled, [16..24] prefix sums of the queue about to be read
+__global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int cur, int bounce, int n_first, int bucketed) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (bucketed) {   // the queue of this bounce sits in the staging regions: k_queue_gather makes it contiguous
+        unsigned sum = 0;
+        for (int k = 0; k < PT_NUM_BUCKETS; ++k) {
+            cnt[16 + k] = sum;
+            sum += cnt[8 + k];
+            cnt[8 + k] = 0;
+        }
+        cnt[16 + PT_NUM_BUCKETS] = sum;
+        cnt[cur] = sum;
+    }
     // stats are shared by the two halves of a frame (two streams): atomic adds
     if (bounce == 0) {
         cnt[cur] = (unsigned)n_first;
@@ -48,18 +59,67 @@ __global__ void k_sample_end(unsigned int* cnt, unsigned long long* stats, int l
 // ---------------------------------------------------------------------------------------------
 // primary rays (GeneratePerspectiveRays, PathTracing.cl:13-35) + radiance clear + queue fill
 // ---------------------------------------------------------------------------------------------
+// Coherence key of the vertex that pixel `px` will shade at `bounce`: the sampler is a pure function of
+// (pixel, frame, bounce) (samplers.cl:75-84), so the light the vertex will pick (first 1D draw) and the half of
+// the lobe-selection variate (fourth draw; PathTracing.cl:106-139 draws 1D light pick, 2D light sample, 2D BSDF
+// sample) are known before the ray is even traced.  Queues ordered by this key give the shade kernel warps whose
+// lanes take the same light-sampling and lobe-sampling branches; per-path results do not depend on queue order.
+__device__ __forceinline__ unsigned coherence_key(const PtState& s, uint32_t px, int frame, int bounce) {
+    Sampler sp = makeSampler(s.sobol, (int)px, frame, s.width, s.height, bounce);
+    uint32_t lightIdx = ((uint32_t)floorf(getSample1D(&sp) * s.numLights));
+    lightIdx %= (uint32_t)s.numLights;
+    skipSamples(&sp, 2);
+    const float u = getSample1D(&sp);
+    return (lightIdx < 3u ? lightIdx : 3u) * 2u + (u >= 0.5f ? 1u : 0u);
+}
+// one atomic per distinct key in the warp; returns the lane's slot within its key's region
+__device__ __forceinline__ unsigned warp_push_keyed(bool pred, unsigned key, unsigned int* counters) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned m = __match_any_sync(0xffffffffu, pred ? key : 0xffffffffu);
+    const int leader = __ffs(m) - 1;
+    unsigned base = 0;
+    if (pred && (int)lane == leader) base = atomicAdd(counters + key, (unsigned)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+
 __global__ void __launch_bounds__(256)
-k_raygen(PtState s, const uint32_t* __restrict__ pixels, int first, int n) {
+k_raygen(PtState s, const uint32_t* __restrict__ pixels, int first, int n, int frame) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t px = pixels ? pixels[first + i] : (uint32_t)(first + i);
-    const RTPinholeCamera* cam = (const RTPinholeCamera*)s.camera;
-    const int x = (int)(px % (uint32_t)s.width), y = (int)(px / (uint32_t)s.width);
-    const V3 d = primary_ray_dir(cam, x, y);
-    s.ray_o[px] = make_float4(cam->pos.x, cam->pos.y, cam->pos.z, 1000.0f);
-    s.ray_d[px] = make_float4(d.x, d.y, d.z, 0.0f);
-    s.radiance[px] = make_float4(0.f, 0.f, 0.f, 0.f);
-    s.queue[0][i] = px;
+    const bool live = i < n;
+    uint32_t px = 0;
+    if (live) {
+        px = pixels ? pixels[first + i] : (uint32_t)(first + i);
+        const RTPinholeCamera* cam = (const RTPinholeCamera*)s.camera;
+        const int x = (int)(px % (uint32_t)s.width), y = (int)(px / (uint32_t)s.width);
+        const V3 d = primary_ray_dir(cam, x, y);
+        s.ray_o[px] = make_float4(cam->pos.x, cam->pos.y, cam->pos.z, 1000.0f);
+        s.ray_d[px] = make_float4(d.x, d.y, d.z, 0.0f);
+        s.radiance[px] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (s.coherence >= 2 && s.numLights > 0) {   // without lights no bounce runs (launch_pt_sample)
+        const unsigned key = live ? coherence_key(s, px, frame, 0) : 0u;
+        const unsigned slot = warp_push_keyed(live, key, s.cnt + 8);
+        if (live) s.bucket[(size_t)key * (size_t)n + slot] = px;
+    } else if (live) {
+        s.queue[0][i] = px;
+    }
+}
+
+// staging regions -> contiguous queue, bucket by bucket (prefix sums written by k_bounce_ctl)
+__global__ void __launch_bounds__(256)
+k_queue_gather(PtState s, int cur, int cap) {
+    __shared__ unsigned prefix[PT_NUM_BUCKETS + 1];
+    if (threadIdx.x <= PT_NUM_BUCKETS) prefix[threadIdx.x] = s.cnt[16 + threadIdx.x];
+    __syncthreads();
+    const unsigned total = prefix[PT_NUM_BUCKETS];
+    uint32_t* __restrict__ q = s.queue[cur];
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        unsigned k = 0;
+#pragma unroll
+        for (int j = 1; j < PT_NUM_BUCKETS; ++j) k += (i >= prefix[j]) ? 1u : 0u;
+        q[i] = s.bucket[(size_t)k * (size_t)cap + (i - prefix[k])];
+    }
 }
 
 // closest-hit ray of queue entry idx / its result
@@ -174,7 +234,7 @@ k_trace_mixed(PtState s, int cur, int sh) {
 #define PT_SHADE_MIN_BLOCKS 1      // register cap = 64K / (PT_SHADE_BLOCK * PT_SHADE_MIN_BLOCKS)
 #endif
 __global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
-k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
+k_shade(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
     const unsigned count = s.cnt[cur];
     const Scene sc = make_scene(s);
     // CTA-uniform trip count: every thread reaches the barriers inside shade_vertex and the ballots below
@@ -227,13 +287,19 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth) {
             s.sh_d[si] = make_float4(out.shadow.d.x, out.shadow.d.y, out.shadow.d.z, __int_as_float((int)px));
             s.sh_L[si] = make_float4(out.direct.x, out.direct.y, out.direct.z, 0.0f);
         }
-        const unsigned ni = warp_push(pushNext, s.cnt + (1 - cur));
+        if (s.coherence >= 1) {   // next bounce's queue goes to the staging regions, by coherence key
+            const unsigned key = pushNext ? coherence_key(s, px, frame, bounce + 1) : 0u;
+            const unsigned slot = warp_push_keyed(pushNext, key, s.cnt + 8);
+            if (pushNext) s.bucket[(size_t)key * (size_t)cap + slot] = px;
+        } else {
+            const unsigned ni = warp_push(pushNext, s.cnt + (1 - cur));
+            if (pushNext) s.queue[1 - cur][ni] = px;
+        }
         if (pushNext) {
             s.ray_o[px] = make_float4(out.nextO.x, out.nextO.y, out.nextO.z, RT_MAX_TRACE_DISTANCE);
             s.ray_d[px] = make_float4(out.nextD.x, out.nextD.y, out.nextD.z, 0.0f);
             s.throughput[px] = make_float4(out.throughput.x, out.throughput.y, out.throughput.z,
                                            __int_as_float(out.bsdfFlags));
-            s.queue[1 - cur][ni] = px;
         }
     }
 }
@@ -271,7 +337,8 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         t.sh_o += nA;
         t.sh_d += nA;
         t.sh_L += nA;
-        t.cnt += 8;
+        t.cnt += PT_CNT_STRIDE;
+        t.bucket += (size_t)PT_NUM_BUCKETS * nA;
         half[1] = {t, nA, n_pixels - nA, overlap->stream};
         cudaEventRecord(overlap->fork, stream);
         cudaStreamWaitEvent(overlap->stream, overlap->fork, 0);
@@ -280,7 +347,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
     auto blocks_trace = [&](int n) { return min(sms * trace_per_sm, (n + 127) / 128); };
     auto blocks_shade = [&](int n) { return min(sms * shade_per_sm, (n + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK); };
     for (int h = 0; h < nh; ++h) {
-        k_raygen<<<(half[h].n + 255) / 256, 256, 0, half[h].stream>>>(half[h].s, pixels, half[h].first, half[h].n);
+        k_raygen<<<(half[h].n + 255) / 256, 256, 0, half[h].stream>>>(half[h].s, pixels, half[h].first, half[h].n, frame);
         ++launches;
     }
     if (s.numLights > 0) {   // RTPathTracingPass::update returns early without lights (:42-43); PathTracing.cl:72
@@ -288,7 +355,12 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         for (int b = 0; b < max_depth; ++b) {
             for (int h = 0; h < nh; ++h) {
                 const Half& H = half[h];
-                k_bounce_ctl<<<1, 32, 0, H.stream>>>(H.s.cnt, H.s.stats, cur[h], b, H.n);
+                const bool bucketed = s.coherence >= 2 || (s.coherence == 1 && b >= 1);
+                k_bounce_ctl<<<1, 32, 0, H.stream>>>(H.s.cnt, H.s.stats, cur[h], b, H.n, bucketed ? 1 : 0);
+                if (bucketed) {
+                    k_queue_gather<<<min(sms * 4, (H.n + 255) / 256), 256, 0, H.stream>>>(H.s, cur[h], H.n);
+                    ++launches;
+                }
                 if (timer) timer->mark(h, H.stream);
                 if (b == 0) {
                     // experiment knob: start the second half one stage behind the first
@@ -299,7 +371,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                     k_trace_mixed<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1);
                 }
                 if (timer) timer->mark(h, H.stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
-                k_shade<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth);
+                k_shade<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
                 if (timer) timer->mark(h, H.stream, StageTimer::SHADE);
                 launches += 3;
                 cur[h] = 1 - cur[h];

@@ -9,6 +9,8 @@ namespace mcrt {
 
 struct SceneDev;  // opaque here; defined in pt_kernels.cu as mcrt::Scene
 
+enum { PT_NUM_BUCKETS = 8, PT_CNT_STRIDE = 32 };   // coherence buckets; uint32 counters per half frame
+
 // Everything a kernel needs, passed by value.  Per-pixel arrays are full-frame (P = width*height)
 // and indexed by the GLOBAL pixel index; queues hold pixel indices of live paths.
 struct PtState {
@@ -39,7 +41,10 @@ struct PtState {
     float4* sh_o;         // shadow queue: xyz origin, w tmax
     float4* sh_d;         // xyz direction, w = pixel index (int bits)
     float4* sh_L;         // rgb = throughput * L (unshadowed direct light)
-    unsigned int* cnt;    // [0],[1] queue counts, [3],[4] work counters, [5],[6] shadow counts by bounce parity
+    unsigned int* cnt;    // [0],[1] queue counts, [3],[4] work counters, [5],[6] shadow counts by bounce parity,
+                          // [8..15] coherence-bucket counts, [16..24] their prefix sums (PT_CNT_STRIDE per half frame)
+    uint32_t* bucket;     // coherence staging: PT_NUM_BUCKETS regions per half frame (pt_kernels.cu)
+    int coherence;        // 0 = queues in push order, 1 = bounces >= 1 bucketed by sampler decisions, 2 = bounce 0 too
     unsigned long long* stats;  // [0] closest rays, [1] shadow rays, [2] shaded vertices, [3] samples
     // reference-layout (AoS) stage buffers
     void* aos_rays;        // RTRay[P]

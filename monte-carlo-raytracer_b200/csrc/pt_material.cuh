@@ -185,7 +185,7 @@ HD V3 sampleUberBSDF(const UberProps& um, const RTInteraction* si, V2 u, int mod
         f += evaluateLambertianReflection(kd);
         *pdf += evaluateLambertianReflectionPdf(wo, wi);
     }
-    *pdf /= numBxDFs;
+    *pdf = fdiv(*pdf, (float)numBxDFs);
     *wiWorld = dirFromShadingToWorld(wi, si);
     return f;
 }

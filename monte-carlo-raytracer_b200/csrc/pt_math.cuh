@@ -55,13 +55,33 @@ HD V3 v3(float a) { return v3(a, a, a); }
 HD V3 v3(const float4& f) { return v3(f.x, f.y, f.z); }
 HD V2 v2(float x, float y) { V2 r; r.x = x; r.y = y; return r; }
 
+// IEEE a / b.  The hardware division sequence range-checks its operands (FCHK) and sends a ZERO numerator down a
+// ~25-instruction subroutine; components of axis-aligned normals, tangents and colours are zero all the time
+// (ncu r01: every warp of k_shade took that subroutine at 21 call sites, 10 % of its instructions).  Branch-free
+// shortcut: a zero numerator is replaced by 2^-40, whose quotient t cannot overflow for any finite b (>= 2^-149),
+// and the result is a * t: a signed zero with sign(a) ^ sign(b) for finite non-zero b and for b = inf (t = 0),
+// NaN for b = 0 (t = inf) and b = NaN -- exactly what 0 / b gives.  Non-zero numerators are untouched.
+#ifndef PT_FDIV_ZERO_SHORTCUT
+#define PT_FDIV_ZERO_SHORTCUT 1
+#endif
+HD float fdiv(float a, float b) {
+#if PT_FDIV_ZERO_SHORTCUT
+    const bool zero = a == 0.0f;
+    const float q = (zero ? 9.094947017729282e-13f : a) / b;
+    const float z = a * q;
+    return zero ? z : q;
+#else
+    return a / b;
+#endif
+}
+
 HD V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
 HD V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
 HD V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
-HD V3 operator/(V3 a, V3 b) { return v3(a.x / b.x, a.y / b.y, a.z / b.z); }
+HD V3 operator/(V3 a, V3 b) { return v3(fdiv(a.x, b.x), fdiv(a.y, b.y), fdiv(a.z, b.z)); }
 HD V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
 HD V3 operator*(float s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
-HD V3 operator/(V3 a, float s) { return v3(a.x / s, a.y / s, a.z / s); }
+HD V3 operator/(V3 a, float s) { return v3(fdiv(a.x, s), fdiv(a.y, s), fdiv(a.z, s)); }
 HD V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
 HD V3& operator+=(V3& a, V3 b) { a = a + b; return a; }
 HD V3& operator*=(V3& a, V3 b) { a = a * b; return a; }

@@ -6,6 +6,7 @@
 // RTPrimaryRaysPass / RTPathTracingPass / RTReconstructionPass.  No CPU fallback.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -202,7 +203,7 @@ int ptb_create(rrb_api* api, ptb_context** out) {
     rc = set_dev(c.get());
     if (rc) return rc;
     void* p = nullptr;
-    rc = alloc_into(c->named, "__cnt", 64, true, c->stream, &p);
+    rc = alloc_into(c->named, "__cnt", 2 * mcrt::PT_CNT_STRIDE * sizeof(unsigned int), true, c->stream, &p);
     if (rc) return rc;
     c->st.cnt = (unsigned int*)p;
     rc = alloc_into(c->named, "__stats", 64, true, c->stream, &p);
@@ -212,6 +213,8 @@ int ptb_create(rrb_api* api, ptb_context** out) {
     if (rc) return rc;
     c->st.camera = p;
     if (const char* v = getenv("MCRT_OVERLAP_HALVES")) c->halves = atoi(v) == 1 ? 1 : 2;   // profiling aid
+    c->st.coherence = PTB_DEFAULT_COHERENCE;
+    if (const char* v = getenv("MCRT_COHERENCE")) c->st.coherence = std::max(0, std::min(2, atoi(v)));   // variant runs
     PTB_CUDA(cudaStreamCreateWithFlags(&c->overlap.stream, cudaStreamNonBlocking));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.fork, cudaEventDisableTiming));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.join, cudaEventDisableTiming));
@@ -226,6 +229,15 @@ int ptb_set_overlap(ptb_context* c, int halves) {
     if (rc) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->halves = halves;
+    return 0;
+}
+
+int ptb_set_coherence(ptb_context* c, int mode) {
+    if (!c || mode < 0 || mode > 2) return pfail(RRB_ERROR_INVALID_ARGUMENT, "coherence mode must be 0, 1 or 2");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    c->st.coherence = mode;
     return 0;
 }
 
@@ -351,6 +363,7 @@ int ptb_resize(ptb_context* c, int width, int height) {
         {"radiance", 16, (void**)&s.radiance, "RadianceBufferCL"},
         {"queue0", 4, (void**)&s.queue[0], nullptr},
         {"queue1", 4, (void**)&s.queue[1], nullptr},
+        {"bucket", 4 * mcrt::PT_NUM_BUCKETS, (void**)&s.bucket, nullptr},
         {"sh_o", 16, (void**)&s.sh_o, nullptr},
         {"sh_d", 16, (void**)&s.sh_d, nullptr},
         {"sh_L", 16, (void**)&s.sh_L, nullptr},

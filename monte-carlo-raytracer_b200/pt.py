@@ -67,6 +67,7 @@ def _lib():
             "ptb_denoise": [vp, ctypes.c_char_p, i, ctypes.c_float, ctypes.c_float],
             "ptb_tonemap": [vp, ctypes.c_char_p, ctypes.c_float],
             "ptb_profile_enable": [vp, ctypes.c_int], "ptb_set_overlap": [vp, ctypes.c_int],
+            "ptb_set_coherence": [vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
         }
@@ -281,6 +282,11 @@ class RenderPipeline:
 
     def set_overlap(self, halves):
         _check(_lib().ptb_set_overlap(self.scene._h, int(halves)))
+
+    def set_coherence(self, mode):
+        """Queue order of the fused wavefront: 0 push order, 1 bounces >= 1 bucketed by the sampler's light / lobe
+        decisions, 2 bounce 0 too (include/ptb.h)."""
+        _check(_lib().ptb_set_coherence(self.scene._h, int(mode)))
 
     def set_partition(self, part, num_parts):
         _check(_lib().ptb_set_partition(self.scene._h, int(part), int(num_parts)))

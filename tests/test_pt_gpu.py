@@ -414,6 +414,40 @@ def test_two_stream_half_frames_equal_single_wavefront_bitwise(api, cornell):
     assert res[0][2]["kernel_launches"] > res[1][2]["kernel_launches"]
 
 
+@pytest.mark.parametrize("halves", [1, 2])
+def test_coherence_bucketed_queues_equal_push_order_bitwise(api, halves):
+    """ptb_set_coherence: ordering the live-path queues by the sampler's coming light / lobe decisions changes which
+    lanes shade which path, not what any path computes -- radiance, image and counters are bit-identical."""
+    scene = scene_library.sponza_class(64)     # three light types, textured two-lobe materials, alpha masks
+    w, h, depth = 512, 320, 5
+    res = []
+    for mode in (0, 1, 2):
+        a = api if mode == 0 else rr.IntersectionApi.Create(0)
+        try:
+            pl = pt.make_pt_pipeline(a, scene, w, h, depth)
+            pl.ensure_size()
+            pl.set_overlap(halves)
+            pl.set_coherence(mode)
+            frames = []
+            for _ in range(3):
+                pl.update()
+                frames.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+            img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+            cnt = pl.counters()
+            pl.scene.destroy()
+        finally:
+            if mode != 0:
+                rr.IntersectionApi.Delete(a)
+        res.append((frames, img, cnt))
+    assert res[0][2]["shaded_vertices"] > 2 * w * h      # paths do go several bounces deep
+    for mode in (1, 2):
+        for f in range(3):
+            assert np.array_equal(res[0][0][f].view(np.uint32), res[mode][0][f].view(np.uint32)), (mode, f)
+        assert np.array_equal(res[0][1].view(np.uint32), res[mode][1].view(np.uint32))
+        for k in ("samples", "closest_rays", "shadow_rays", "shaded_vertices"):
+            assert res[0][2][k] == res[mode][2][k], (mode, k)
+
+
 def test_pipelined_readback_equals_blocking_read(api, cornell):
     """ptb_read_buffer_async: the snapshot copied behind the next frame is the image of the frame it was issued
     after, even though the next frame's accumulate has overwritten the device buffer in the meantime."""
