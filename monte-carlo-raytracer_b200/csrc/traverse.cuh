@@ -50,6 +50,30 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
 
 __device__ __forceinline__ uint32_t extract_byte(uint32_t x, uint32_t i) { return (x >> (i * 8)) & 0xffu; }
 
+// Quantised plane coordinate -> float without the quarter-rate I2F of the XU pipe (ncu r01: 48 I2F per node visit,
+// XU the busiest pipe of the traversal kernels): one PRMT drops byte J of x into mantissa bits [15:8] of the
+// constant c = 1.0f, giving exactly 1 + b * 2^-15; the node's scale and offset absorb the affine map
+// (aix' = aix * 2^15, orx' = orx - aix').  Rounding orx' costs at most 2^-24 * 2^15 = 2^-9 quantisation step of
+// accuracy per plane on top of the errors proportional to t that the relative widening of the far side already
+// covers.  It is paid back by the constant: the bytes of a node's HIGH planes are converted with c = 1.0f + 2 ulp,
+// i.e. 2^-7 step further out.  For a positive direction component the high plane is the far one (t_far grows),
+// for a negative one it is the near one (t_near shrinks): either way the slab interval only widens.
+#ifndef MCRT_QUANT_PRMT
+#define MCRT_QUANT_PRMT 1
+#endif
+#define MCRT_QUANT_C_LO 0x3F800000u
+#define MCRT_QUANT_C_HI 0x3F800002u
+template <int J>
+__device__ __forceinline__ float quant_byte_to_float(uint32_t x, uint32_t c) {
+#if MCRT_QUANT_PRMT
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(c), "n"(0x7604 | (J << 4)));
+    return __uint_as_float(r);
+#else
+    return (float)extract_byte(x, J);
+#endif
+}
+
 __device__ __forceinline__ float safe_inv(float d) {
     return __fdiv_rn(1.0f, fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d));
 }
@@ -175,12 +199,22 @@ struct Traverser {
                 tgroup.x = n1.y;
                 tgroup.y = 0u;
                 uint32_t hitmask = 0u;
+#if MCRT_QUANT_PRMT
+                // scale = 2^(e + 15): the exponent byte is >= 1 for every node the builder emits, and far below 240
+                const float aix = mul_(__uint_as_float((extract_byte(n0.w, 0) + 15u) << 23), s.idx);
+                const float aiy = mul_(__uint_as_float((extract_byte(n0.w, 1) + 15u) << 23), s.idy);
+                const float aiz = mul_(__uint_as_float((extract_byte(n0.w, 2) + 15u) << 23), s.idz);
+                const float orx = sub_(mul_(sub_(__uint_as_float(n0.x), r.ox), s.idx), aix);
+                const float ory = sub_(mul_(sub_(__uint_as_float(n0.y), r.oy), s.idy), aiy);
+                const float orz = sub_(mul_(sub_(__uint_as_float(n0.z), r.oz), s.idz), aiz);
+#else
                 const float aix = mul_(__uint_as_float(extract_byte(n0.w, 0) << 23), s.idx);
                 const float aiy = mul_(__uint_as_float(extract_byte(n0.w, 1) << 23), s.idy);
                 const float aiz = mul_(__uint_as_float(extract_byte(n0.w, 2) << 23), s.idz);
                 const float orx = mul_(sub_(__uint_as_float(n0.x), r.ox), s.idx);
                 const float ory = mul_(sub_(__uint_as_float(n0.y), r.oy), s.idy);
                 const float orz = mul_(sub_(__uint_as_float(n0.z), r.oz), s.idz);
+#endif
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
                     const uint32_t meta4 = half == 0 ? n1.z : n1.w;
@@ -194,21 +228,29 @@ struct Traverser {
                     const uint32_t xmin = s.idx < 0.f ? qhx : qlx, xmax = s.idx < 0.f ? qlx : qhx;
                     const uint32_t ymin = s.idy < 0.f ? qhy : qly, ymax = s.idy < 0.f ? qly : qhy;
                     const uint32_t zmin = s.idz < 0.f ? qhz : qlz, zmax = s.idz < 0.f ? qlz : qhz;
+                    // conversion constants travel with the words: HIGH planes get the outward bias
+                    const uint32_t cxmin = s.idx < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, cxmax = cxmin ^ 2u;
+                    const uint32_t cymin = s.idy < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, cymax = cymin ^ 2u;
+                    const uint32_t czmin = s.idz < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, czmax = czmin ^ 2u;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const float tminx = __fmaf_rn((float)extract_byte(xmin, j), aix, orx);
-                        const float tminy = __fmaf_rn((float)extract_byte(ymin, j), aiy, ory);
-                        const float tminz = __fmaf_rn((float)extract_byte(zmin, j), aiz, orz);
-                        const float tmaxx = __fmaf_rn((float)extract_byte(xmax, j), aix, orx);
-                        const float tmaxy = __fmaf_rn((float)extract_byte(ymax, j), aiy, ory);
-                        const float tmaxz = __fmaf_rn((float)extract_byte(zmax, j), aiz, orz);
-                        const float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, 0.f));
-                        // 1 + 3 ulp widening keeps the quantised slab test conservative w.r.t. fp32 rounding
-                        const float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, s.closest)) * 1.0000004f;
-                        if (cmin <= cmax) {
-                            hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);
-                        }
-                    }
+#define MCRT_CHILD_TEST(j)                                                                                      \
+    {                                                                                                          \
+        const float tminx = __fmaf_rn(quant_byte_to_float<j>(xmin, cxmin), aix, orx);                          \
+        const float tminy = __fmaf_rn(quant_byte_to_float<j>(ymin, cymin), aiy, ory);                          \
+        const float tminz = __fmaf_rn(quant_byte_to_float<j>(zmin, czmin), aiz, orz);                          \
+        const float tmaxx = __fmaf_rn(quant_byte_to_float<j>(xmax, cxmax), aix, orx);                          \
+        const float tmaxy = __fmaf_rn(quant_byte_to_float<j>(ymax, cymax), aiy, ory);                          \
+        const float tmaxz = __fmaf_rn(quant_byte_to_float<j>(zmax, czmax), aiz, orz);                          \
+        const float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, 0.f));                                      \
+        /* 1 + 3 ulp widening keeps the quantised slab test conservative w.r.t. fp32 rounding */               \
+        const float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, s.closest)) * 1.0000004f;                   \
+        if (cmin <= cmax) hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);              \
+    }
+                    MCRT_CHILD_TEST(0)
+                    MCRT_CHILD_TEST(1)
+                    MCRT_CHILD_TEST(2)
+                    MCRT_CHILD_TEST(3)
+#undef MCRT_CHILD_TEST
                 }
                 ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
                 tgroup.y = hitmask & 0x00FFFFFFu;

@@ -113,12 +113,16 @@ def closest_hit(nodes, tris, ray_o, ray_d, tmax, tri_test):
                     continue
                 tmin, tmx = f32(0.0), closest
                 for a in range(3):
-                    sc = np.array([e[a] << 23], np.uint32).view(np.float32)[0]
+                    # traverse.cuh (MCRT_QUANT_PRMT): byte -> 1 + b * 2^-15 (+ 2 ulp for the HIGH planes), scale and
+                    # offset absorb the affine map
+                    sc = np.array([(e[a] + 15) << 23], np.uint32).view(np.float32)[0]
                     ai = f32(sc * inv[a])
-                    org = f32(f32(p[a] - o[a]) * inv[a])
-                    qa, qb = (q[3 + a][s], q[a][s]) if inv[a] < 0 else (q[a][s], q[3 + a][s])
-                    ta = f32(np.float64(f32(qa)) * np.float64(ai) + np.float64(org))   # fma
-                    tb = f32(np.float64(f32(qb)) * np.float64(ai) + np.float64(org))
+                    org = f32(f32(f32(p[a] - o[a]) * inv[a]) - ai)
+                    lo = np.array([0x3F800000 | (int(q[a][s]) << 8)], np.uint32).view(np.float32)[0]
+                    hi = np.array([0x3F800002 | (int(q[3 + a][s]) << 8)], np.uint32).view(np.float32)[0]
+                    qa, qb = (hi, lo) if inv[a] < 0 else (lo, hi)
+                    ta = f32(np.float64(qa) * np.float64(ai) + np.float64(org))   # fma
+                    tb = f32(np.float64(qb) * np.float64(ai) + np.float64(org))
                     tmin, tmx = max(tmin, ta), min(tmx, tb)
                 if tmin <= f32(tmx * f32(1.0000004)):
                     inner = (imask >> s) & 1
