@@ -122,6 +122,14 @@ int ptb_set_overlap(ptb_context* ctx, int halves);
  * shade kernel take the same light / lobe branches), 2 = bounce 0 as well, 0 = push order.  Per-sample results are
  * identical in all modes. */
 #define PTB_DEFAULT_COHERENCE 1
+/* Opt-in estimator switches of ptb_pt_render_sample (default 0 = the reference's estimator, PathTracing.cl:52-184,
+ * which has neither): Russian roulette from the third vertex on, and power-heuristic MIS between next-event
+ * estimation and BSDF sampling for triangle-mesh area lights.  Both keep the expectation of the reference's
+ * estimator (MIS: for light meshes whose triangles have equal areas, lights.cl:106,122) and change its variance,
+ * so they are excluded from per-sample parity; the stage-wise entry points ignore them. */
+#define PTB_EST_RUSSIAN_ROULETTE 1
+#define PTB_EST_NEE_MIS 2
+int ptb_set_estimator(ptb_context* ctx, int flags);
 int ptb_set_coherence(ptb_context* ctx, int mode);
 
 /* Per-kernel device timing of the fused wavefront (no reference counterpart; measurement only).

@@ -233,8 +233,9 @@ k_trace_mixed(PtState s, int cur, int sh) {
 #ifndef PT_SHADE_MIN_BLOCKS
 #define PT_SHADE_MIN_BLOCKS 1      // register cap = 64K / (PT_SHADE_BLOCK * PT_SHADE_MIN_BLOCKS)
 #endif
-__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
-k_shade(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
+template <bool EST>
+__device__ __forceinline__ void shade_queue(const PtState& s, int cur, int frame, int bounce, int maxDepth, int cap,
+                                            int estimator) {
     const unsigned count = s.cnt[cur];
     const Scene sc = make_scene(s);
     // CTA-uniform trip count: every thread reaches the barriers inside shade_vertex and the ballots below
@@ -249,6 +250,8 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
         in.bu = in.bv = 0.0f;
         in.rayDir = in.throughput = v3(0.0f);
         in.prevBsdfFlags = 0;
+        in.prevPdf = 0.0f;
+        in.prevOrigin = in.prevDirectWeight = v3(0.0f);
         if (i < count) {
             px = s.queue[cur][i];
             const int4 h = s.hit[px];
@@ -264,17 +267,29 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
                 const float4 tp = s.throughput[px];
                 in.throughput = v3(tp.x, tp.y, tp.z);
                 in.prevBsdfFlags = __float_as_int(tp.w);
+                if (EST) {
+                    in.prevPdf = d.w;
+                    const float4 o = s.ray_o[px];
+                    in.prevOrigin = v3(o.x, o.y, o.z);
+                    if (d.w > 0.0f) {
+                        const float4 dw = s.direct_weight[px];
+                        in.prevDirectWeight = v3(dw.x, dw.y, dw.z);
+                    }
+                }
             }
         }
-        shade_vertex<PT_SHADE_SYNC != 0>(sc, in, active, frame, s.width, s.height, bounce, maxDepth, &out);
+        shade_vertex<PT_SHADE_SYNC != 0, EST>(sc, in, active, frame, s.width, s.height, bounce, maxDepth, &out, estimator);
         if (active) {
-            if (out.hasEmission) {
+            // hasEmission: the reference's emission branch, which ends the path; with EST a weighted emission can
+            // also come with a path that goes on
+            if (out.hasEmission || (EST && (out.emitted.x != 0.0f || out.emitted.y != 0.0f || out.emitted.z != 0.0f))) {
                 float4 r = s.radiance[px];
                 r.x += out.emitted.x;
                 r.y += out.emitted.y;
                 r.z += out.emitted.z;
                 s.radiance[px] = r;
-            } else {
+            }
+            if (!out.hasEmission) {
                 // a zero contribution adds nothing whatever the visibility: no shadow ray needed
                 pushShadow = out.shadow.written &&
                              !(out.direct.x == 0.0f && out.direct.y == 0.0f && out.direct.z == 0.0f);
@@ -297,11 +312,23 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
         }
         if (pushNext) {
             s.ray_o[px] = make_float4(out.nextO.x, out.nextO.y, out.nextO.z, RT_MAX_TRACE_DISTANCE);
-            s.ray_d[px] = make_float4(out.nextD.x, out.nextD.y, out.nextD.z, 0.0f);
+            s.ray_d[px] = make_float4(out.nextD.x, out.nextD.y, out.nextD.z, EST ? out.nextPdf : 0.0f);
+            if (EST && out.nextPdf > 0.0f)
+                s.direct_weight[px] = make_float4(out.nextDirectWeight.x, out.nextDirectWeight.y, out.nextDirectWeight.z, 0.0f);
             s.throughput[px] = make_float4(out.throughput.x, out.throughput.y, out.throughput.z,
                                            __int_as_float(out.bsdfFlags));
         }
     }
+}
+
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
+k_shade(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
+    shade_queue<false>(s, cur, frame, bounce, maxDepth, cap, 0);
+}
+// the same with the opt-in estimator switches (PtState::estimator != 0)
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
+k_shade_est(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
+    shade_queue<true>(s, cur, frame, bounce, maxDepth, cap, s.estimator);
 }
 
 static int env_int(const char* name, int dflt) {
@@ -371,7 +398,10 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                     k_trace_mixed<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1);
                 }
                 if (timer) timer->mark(h, H.stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
-                k_shade<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
+                if (s.estimator)
+                    k_shade_est<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
+                else
+                    k_shade<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
                 if (timer) timer->mark(h, H.stream, StageTimer::SHADE);
                 launches += 3;
                 cur[h] = 1 - cur[h];

@@ -37,6 +37,7 @@ struct PtState {
     int4* hit;            // shape id, prim id, u bits, v bits
     float4* throughput;   // rgb, w = previous BSDF flags (int bits)
     float4* radiance;     // "RadianceBufferCL": this frame's per-pixel radiance
+    float4* direct_weight;  // opt-in MIS only (pt_shade.cuh): path weight for light found along the current ray
     uint32_t* queue[2];   // ping-pong live-path queues (pixel indices)
     float4* sh_o;         // shadow queue: xyz origin, w tmax
     float4* sh_d;         // xyz direction, w = pixel index (int bits)
@@ -44,6 +45,7 @@ struct PtState {
     unsigned int* cnt;    // [0],[1] queue counts, [3],[4] work counters, [5],[6] shadow counts by bounce parity,
                           // [8..15] coherence-bucket counts, [16..24] their prefix sums (PT_CNT_STRIDE per half frame)
     uint32_t* bucket;     // coherence staging: PT_NUM_BUCKETS regions per half frame (pt_kernels.cu)
+    int estimator;        // PT_EST_* flags of the opt-in estimator switches (pt_shade.cuh); 0 = the reference's estimator
     int coherence;        // 0 = queues in push order, 1 = bounces >= 1 bucketed by sampler decisions, 2 = bounce 0 too
     unsigned long long* stats;  // [0] closest rays, [1] shadow rays, [2] shaded vertices, [3] samples
     // reference-layout (AoS) stage buffers

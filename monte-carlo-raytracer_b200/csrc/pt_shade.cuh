@@ -7,10 +7,24 @@
 // a specular bounce, and it terminates the path; one light sample per vertex; sampler re-seeded
 // per bounce with draws in the fixed order 1D light pick, 2D light sample, 2D BSDF sample; no
 // Russian roulette, no MIS, no environment term.
+//
+// Opt-in estimator switches (EST = true, `estimator` flags; BASELINE north_star asks for them, the reference has
+// neither, so they are off by default and excluded from parity runs -- SURVEY App. B.4):
+//   PT_EST_NEE_MIS           power-heuristic MIS between light sampling and BSDF sampling for triangle-mesh
+//                            area lights (the only lights a BSDF-sampled ray can hit): the NEE term is weighted by
+//                            p_l^2 / (p_l^2 + p_b^2), and a non-specular bounce that lands on an emitter adds
+//                            throughput * Le * p_b^2 / (p_b^2 + p_l^2) where the reference adds nothing.  Same
+//                            expectation as the reference's estimator when the light pdf is exact (E10: meshes whose
+//                            triangles have equal areas), lower variance on glossy surfaces.
+//   PT_EST_RUSSIAN_ROULETTE  from the third vertex on, a path survives with probability
+//                            min(0.95, max throughput component) and is re-weighted; sixth draw of the bounce's
+//                            sampler, so the five draws of the reference's estimator are unchanged.
 #pragma once
 #include "pt_material.cuh"
 
 namespace mcrt {
+
+enum { PT_EST_RUSSIAN_ROULETTE = 1, PT_EST_NEE_MIS = 2 };   // = PTB_EST_* (include/ptb.h)
 
 struct ShadeIn {
     int pixel;            // GLOBAL buffer index (seeds the sampler)
@@ -19,6 +33,10 @@ struct ShadeIn {
     V3 rayDir;
     V3 throughput;        // ignored on bounce 0 (set to 1)
     int prevBsdfFlags;
+    // EST only: density with which the previous vertex's lobe mixture samples rayDir (0 after a delta lobe), the
+    // path weight for light found along rayDir (throughput * f * cos / that density), and the ray origin
+    float prevPdf;
+    V3 prevOrigin, prevDirectWeight;
 };
 
 struct ShadeOut {
@@ -27,6 +45,8 @@ struct ShadeOut {
     V3 direct;            // throughput * L, to be multiplied by the shadow ray's visibility
     ShadowRay shadow;     // .written = the reference's setRay() on the shadow ray ran
     bool continues;       // a next ray was spawned
+    float nextPdf;        // EST only: mixture density of nextD (0 for a delta lobe), and the weight that goes with it
+    V3 nextDirectWeight;
     V3 nextO, nextD;
     V3 throughput;
     int bsdfFlags;
@@ -40,10 +60,16 @@ HD void phase_barrier() {
     if (SYNC) __syncthreads();
 }
 
-template <bool SYNC>
+HD float power_heuristic(float a, float b) {
+    const float a2 = a * a, b2 = b * b;
+    return a2 + b2 > 0.0f ? a2 / (a2 + b2) : 0.0f;
+}
+
+template <bool SYNC, bool EST = false>
 HD void shade_vertex(const Scene& sc, const ShadeIn& in, bool active, int frame, int width, int height, int bounce,
-                     int maxDepth, ShadeOut* out) {
+                     int maxDepth, ShadeOut* out, int estimator = 0) {
     out->hasEmission = false;
+    out->nextPdf = 0.0f;
     out->emitted = v3(0.0f);
     out->direct = v3(0.0f);
     out->shadow.written = false;
@@ -74,6 +100,15 @@ HD void shade_vertex(const Scene& sc, const ShadeIn& in, bool active, int frame,
             out->emitted = throughput * Le;
             out->hasEmission = true;
             active = false;      // the path ends here (PathTracing.cl:91-101)
+        } else if (EST && isEmitter && (estimator & PT_EST_NEE_MIS) && in.prevPdf > 0.0f &&
+                   sc.lights[lightID].type == RT_TRIANGLE_MESH_AREA_LIGHT) {
+            // BSDF-sampled hit of an area light: the share of direct light that light sampling at the previous
+            // vertex did not take.  p_l as sampleLightLi computes it for this point (lights.cl:104-131).
+            const RTLight* light = sc.lights + lightID;
+            const float c = absDot(si.gn, si.wo);
+            const float pl = isNearZero(c) ? 0.0f
+                                           : light->choicePdf * (1.0f / light->area) * distanceSquared(si.p, in.prevOrigin) / c;
+            out->emitted = in.prevDirectWeight * evalLightLe(light, si.gn, si.wo) * power_heuristic(in.prevPdf, pl);
         }
     }
     phase_barrier<SYNC>();
@@ -87,9 +122,11 @@ HD void shade_vertex(const Scene& sc, const ShadeIn& in, bool active, int frame,
     // direct lighting: one light, one sample (PathTracing.cl:106-134)
     float lightPdf = 0.0f;
     V3 wiL = v3(0.0f), Li = v3(0.0f);
+    bool lightIsMesh = false;
     if (active) {
         uint32_t lightIdx = ((uint32_t)floorf(getSample1D(&sampler) * sc.numLights));
         lightIdx %= (uint32_t)sc.numLights;
+        if (EST) lightIsMesh = sc.lights[lightIdx].type == RT_TRIANGLE_MESH_AREA_LIGHT;
         V2 u = getSample2D(&sampler);
         V3 unusedN, unusedP;
         Li = sampleLightLi((int)lightIdx, sc, &si, u, &unusedP, &unusedN, &wiL, &lightPdf, &out->shadow);
@@ -102,6 +139,9 @@ HD void shade_vertex(const Scene& sc, const ShadeIn& in, bool active, int frame,
             V3 bsdf = evaluateUberBSDF(um, &si, si.wo, wiL, TRANSPORT_MODE_RADIANCE);
             bsdf *= absDot(wiL, si.sn);
             if (!isNearZero(lightPdf)) L = Li * bsdf / lightPdf;
+            // (the last vertex of a path spawns no ray, so light sampling is its only strategy: weight 1)
+            if (EST && (estimator & PT_EST_NEE_MIS) && !isNearZero(lightPdf) && lightIsMesh && bounce + 1 < maxDepth)
+                L *= power_heuristic(lightPdf, evaluateUberBSDF_Pdf(um, &si, si.wo, wiL, BSDF_ALL));
         }
         out->direct = throughput * L;
     }
@@ -126,6 +166,32 @@ HD void shade_vertex(const Scene& sc, const ShadeIn& in, bool active, int frame,
                 out->nextO = si.p + si.gn * traceErrorOffset;
                 out->nextD = wi;
                 out->continues = true;
+                if (EST) {
+                    // The reference's sampler divides by a branch-dependent "pdf" (the lobe walk of bxdfs.cl:892-1053
+                    // skips the Lambertian term when the microfacet lobe was chosen, E7), which is fine for its own
+                    // estimator but is not the density of wi.  The MIS share of direct light found along wi uses
+                    // the true mixture density and the full BSDF value instead.
+                    out->nextPdf = 0.0f;
+                    out->nextDirectWeight = v3(0.0f);
+                    if ((estimator & PT_EST_NEE_MIS) && !(sampledType & BSDF_SPECULAR)) {
+                        const float pmix = evaluateUberBSDF_Pdf(um, &si, si.wo, wi, BSDF_ALL);
+                        if (!isNearZero(pmix)) {
+                            out->nextPdf = pmix;
+                            out->nextDirectWeight = throughput *
+                                (evaluateUberBSDF(um, &si, si.wo, wi, TRANSPORT_MODE_RADIANCE) * absDot(wi, si.sn) / pmix);
+                        }
+                    }
+                    if ((estimator & PT_EST_RUSSIAN_ROULETTE) && bounce >= 2) {
+                        const V3 t = out->throughput;
+                        const float survive = fminf(0.95f, fmaxf(t.x, fmaxf(t.y, t.z)));
+                        if (!(getSample1D(&sampler) < survive)) {
+                            out->continues = false;
+                        } else {
+                            out->throughput = t / survive;
+                            out->nextDirectWeight = out->nextDirectWeight / survive;
+                        }
+                    }
+                }
             }
         }
     }

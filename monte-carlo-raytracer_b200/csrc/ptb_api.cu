@@ -232,6 +232,16 @@ int ptb_set_overlap(ptb_context* c, int halves) {
     return 0;
 }
 
+int ptb_set_estimator(ptb_context* c, int flags) {
+    if (!c || (flags & ~(PTB_EST_RUSSIAN_ROULETTE | PTB_EST_NEE_MIS)))
+        return pfail(RRB_ERROR_INVALID_ARGUMENT, "unknown estimator flag");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    c->st.estimator = flags;
+    return 0;
+}
+
 int ptb_set_coherence(ptb_context* c, int mode) {
     if (!c || mode < 0 || mode > 2) return pfail(RRB_ERROR_INVALID_ARGUMENT, "coherence mode must be 0, 1 or 2");
     int rc = set_dev(c);
@@ -361,6 +371,7 @@ int ptb_resize(ptb_context* c, int width, int height) {
         {"hit", 16, (void**)&s.hit, nullptr},
         {"throughput", 16, (void**)&s.throughput, nullptr},
         {"radiance", 16, (void**)&s.radiance, "RadianceBufferCL"},
+        {"direct_weight", 16, (void**)&s.direct_weight, nullptr},
         {"queue0", 4, (void**)&s.queue[0], nullptr},
         {"queue1", 4, (void**)&s.queue[1], nullptr},
         {"bucket", 4 * mcrt::PT_NUM_BUCKETS, (void**)&s.bucket, nullptr},

@@ -67,7 +67,7 @@ def _lib():
             "ptb_denoise": [vp, ctypes.c_char_p, i, ctypes.c_float, ctypes.c_float],
             "ptb_tonemap": [vp, ctypes.c_char_p, ctypes.c_float],
             "ptb_profile_enable": [vp, ctypes.c_int], "ptb_set_overlap": [vp, ctypes.c_int],
-            "ptb_set_coherence": [vp, ctypes.c_int],
+            "ptb_set_coherence": [vp, ctypes.c_int], "ptb_set_estimator": [vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
         }
@@ -287,6 +287,10 @@ class RenderPipeline:
         """Queue order of the fused wavefront: 0 push order, 1 bounces >= 1 bucketed by the sampler's light / lobe
         decisions, 2 bounce 0 too (include/ptb.h)."""
         _check(_lib().ptb_set_coherence(self.scene._h, int(mode)))
+
+    def set_estimator(self, russian_roulette=False, nee_mis=False):
+        """Opt-in estimator switches (include/ptb.h PTB_EST_*); both off = the reference's estimator."""
+        _check(_lib().ptb_set_estimator(self.scene._h, (1 if russian_roulette else 0) | (2 if nee_mis else 0)))
 
     def set_partition(self, part, num_parts):
         _check(_lib().ptb_set_partition(self.scene._h, int(part), int(num_parts)))
