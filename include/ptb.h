@@ -119,9 +119,10 @@ int ptb_set_overlap(ptb_context* ctx, int halves);
 /* Order of the live-path queues of ptb_pt_render_sample.  The reference's sampler is a pure function of (pixel, frame,
  * bounce) (samplers.cl:75-84), so which light a vertex will sample and which half of the lobe-selection variate it
  * will draw are known before its ray is traced: 1 = queues of bounces >= 1 are bucketed by that key (warps of the
- * shade kernel take the same light / lobe branches), 2 = bounce 0 as well, 0 = push order.  Per-sample results are
- * identical in all modes. */
-#define PTB_DEFAULT_COHERENCE 1
+ * shade kernel take the same light / lobe branches), 2 = bounce 0 as well, 3 = bucketed inside each thread block's
+ * chunk of the queue only (keeps neighbouring pixels together: texture / geometry locality), 0 = push order.
+ * Per-sample results are identical in all modes. */
+#define PTB_DEFAULT_COHERENCE 3
 /* Opt-in estimator switches of ptb_pt_render_sample (default 0 = the reference's estimator, PathTracing.cl:52-184,
  * which has neither): Russian roulette from the third vertex on, and power-heuristic MIS between next-event
  * estimation and BSDF sampling for triangle-mesh area lights.  Both keep the expectation of the reference's

@@ -34,7 +34,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
 ] + FP_MODES[FP_MODE] + [
     "-Xcompiler", "-fPIC,-O3,-ffp-contract=off,-fno-fast-math", "-Xptxas", "-v",
-] + os.environ.get("MCRT_NVCC_DEFS", "").split()
+] + os.environ.get("MCRT_NVCC_DEFS", "").replace(",", " ").split()
 
 
 def _nvcc():

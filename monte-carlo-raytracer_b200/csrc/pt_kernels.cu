@@ -97,7 +97,7 @@ k_raygen(PtState s, const uint32_t* __restrict__ pixels, int first, int n, int f
         s.ray_d[px] = make_float4(d.x, d.y, d.z, 0.0f);
         s.radiance[px] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    if (s.coherence >= 2 && s.numLights > 0) {   // without lights no bounce runs (launch_pt_sample)
+    if (s.coherence == 2 && s.numLights > 0) {   // without lights no bounce runs (launch_pt_sample)
         const unsigned key = live ? coherence_key(s, px, frame, 0) : 0u;
         const unsigned slot = warp_push_keyed(live, key, s.cnt + 8);
         if (live) s.bucket[(size_t)key * (size_t)n + slot] = px;
@@ -302,7 +302,27 @@ __device__ __forceinline__ void shade_queue(const PtState& s, int cur, int frame
             s.sh_d[si] = make_float4(out.shadow.d.x, out.shadow.d.y, out.shadow.d.z, __int_as_float((int)px));
             s.sh_L[si] = make_float4(out.direct.x, out.direct.y, out.direct.z, 0.0f);
         }
-        if (s.coherence >= 1) {   // next bounce's queue goes to the staging regions, by coherence key
+        if (s.coherence == 3) {
+            // CTA-local bucketing: the survivors of this CTA's chunk of the queue go to ONE contiguous chunk of the
+            // next queue, ordered by coherence key inside it.  Neighbouring pixels stay neighbours (texture and
+            // geometry locality of the next bounce), warps of the next shade launch still see runs of equal keys.
+            __shared__ unsigned s_cnt[PT_NUM_BUCKETS], s_pre[PT_NUM_BUCKETS], s_base;
+            if (threadIdx.x < PT_NUM_BUCKETS) s_cnt[threadIdx.x] = 0;
+            __syncthreads();
+            const unsigned key = pushNext ? coherence_key(s, px, frame, bounce + 1) : 0u;
+            const unsigned rank = warp_push_keyed(pushNext, key, s_cnt);      // shared-memory atomics
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                unsigned sum = 0;
+                for (int k = 0; k < PT_NUM_BUCKETS; ++k) {
+                    s_pre[k] = sum;
+                    sum += s_cnt[k];
+                }
+                s_base = sum ? atomicAdd(s.cnt + (1 - cur), sum) : 0u;
+            }
+            __syncthreads();
+            if (pushNext) s.queue[1 - cur][s_base + s_pre[key] + rank] = px;
+        } else if (s.coherence >= 1) {   // next bounce's queue goes to the staging regions, by coherence key
             const unsigned key = pushNext ? coherence_key(s, px, frame, bounce + 1) : 0u;
             const unsigned slot = warp_push_keyed(pushNext, key, s.cnt + 8);
             if (pushNext) s.bucket[(size_t)key * (size_t)cap + slot] = px;
@@ -382,7 +402,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         for (int b = 0; b < max_depth; ++b) {
             for (int h = 0; h < nh; ++h) {
                 const Half& H = half[h];
-                const bool bucketed = s.coherence >= 2 || (s.coherence == 1 && b >= 1);
+                const bool bucketed = s.coherence == 2 || (s.coherence == 1 && b >= 1);
                 k_bounce_ctl<<<1, 32, 0, H.stream>>>(H.s.cnt, H.s.stats, cur[h], b, H.n, bucketed ? 1 : 0);
                 if (bucketed) {
                     k_queue_gather<<<min(sms * 4, (H.n + 255) / 256), 256, 0, H.stream>>>(H.s, cur[h], H.n);

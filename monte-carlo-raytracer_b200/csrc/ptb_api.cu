@@ -214,7 +214,7 @@ int ptb_create(rrb_api* api, ptb_context** out) {
     c->st.camera = p;
     if (const char* v = getenv("MCRT_OVERLAP_HALVES")) c->halves = atoi(v) == 1 ? 1 : 2;   // profiling aid
     c->st.coherence = PTB_DEFAULT_COHERENCE;
-    if (const char* v = getenv("MCRT_COHERENCE")) c->st.coherence = std::max(0, std::min(2, atoi(v)));   // variant runs
+    if (const char* v = getenv("MCRT_COHERENCE")) c->st.coherence = std::max(0, std::min(3, atoi(v)));   // variant runs
     PTB_CUDA(cudaStreamCreateWithFlags(&c->overlap.stream, cudaStreamNonBlocking));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.fork, cudaEventDisableTiming));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.join, cudaEventDisableTiming));
@@ -243,7 +243,7 @@ int ptb_set_estimator(ptb_context* c, int flags) {
 }
 
 int ptb_set_coherence(ptb_context* c, int mode) {
-    if (!c || mode < 0 || mode > 2) return pfail(RRB_ERROR_INVALID_ARGUMENT, "coherence mode must be 0, 1 or 2");
+    if (!c || mode < 0 || mode > 3) return pfail(RRB_ERROR_INVALID_ARGUMENT, "coherence mode must be 0 .. 3");
     int rc = set_dev(c);
     if (rc) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
