@@ -123,6 +123,11 @@ typedef struct rrb_stats {
     int64_t launches;           /* traversal kernels launched since creation */
     int64_t refits;             /* commits served by the device refit (option "bvh.refit") since creation */
     int64_t last_commit_refit;  /* 1 when the last rrb_commit was a refit, 0 when it was a full build */
+    int64_t last_build_on_device; /* 1 when the last full build ran on the device (acc.type = "hlbvh" or
+                                     bvh.builder = "lbvh": Morton codes, radix sort, radix tree, wide collapse as CUDA
+                                     kernels -- Radeon Rays' own GPU builder sits behind the same option,
+                                     intersector_hlbvh.cpp); 0 for the multi-threaded host SAH builder */
+    int64_t num_levels;         /* breadth-first levels of the tree when known (device build or "bvh.refit"), else 0 */
 } rrb_stats;
 int rrb_get_stats(rrb_api* api, rrb_stats* out);
 /* Instrumented query: per-ray visited-node and tested-triangle counts into int32[2*numrays]. */

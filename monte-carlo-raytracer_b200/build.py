@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libmcrt_b200.so")
 STAMP_PATH = os.path.join(_HERE, ".libmcrt_b200.stamp")
 
 CUDA_SOURCES = ["rrb_api.cu", "rrb_kernels.cu", "ptb_api.cu", "pt_kernels.cu", "pt_stage_kernels.cu", "bdpt_kernels.cu",
-                "postfx_kernels.cu", "refit_kernels.cu"]
+                "postfx_kernels.cu", "refit_kernels.cu", "lbvh_build.cu"]
 CXX_SOURCES = ["bvh8_build.cpp"]
 
 # fp32 modes of the SHADING arithmetic.  The traversal, the triangle test and the hit

@@ -18,6 +18,7 @@
 
 #include "../../include/rrb.h"
 #include "bvh8.h"
+#include "lbvh_build.h"
 #include "rrb_kernels.h"
 
 namespace {
@@ -96,6 +97,8 @@ struct rrb_api {
     mcrt::RefitMesh* d_refit_meshes = nullptr;
     int64_t refits = 0;
     bool last_commit_was_refit = false;
+    bool last_build_on_device = false;                 // acc.type = hlbvh / bvh.builder = lbvh (lbvh_build.cu)
+    std::string device_build_fallback_reason;
     unsigned int* d_counter = nullptr;
     std::vector<rrb_event*> event_pool;
     // staging for the host-buffer entry points
@@ -432,26 +435,18 @@ int rrb_commit(rrb_api* api) {
     mcrt::BuildOptions opt;
     auto b = api->str_options.find("bvh.builder");
     opt.use_sah = !(b != api->str_options.end() && b->second == "median");
-    mcrt::Bvh8 bvh;
-    try {
-        mcrt::build_bvh8(meshes, opt, bvh);
-    } catch (const std::exception& ex) {
-        bool empty = std::string(ex.what()) == "Scene is empty.";
-        return fail(empty ? RRB_ERROR_EMPTY_SCENE : RRB_ERROR_INVALID_ARGUMENT, ex.what());
-    }
+    // acc.type = "hlbvh" is Radeon Rays' GPU-built hierarchy (intersector_hlbvh.cpp); here it selects the device
+    // builder of the 8-wide tree (lbvh_build.cu).  bvh.builder = "lbvh" does the same.
+    auto acc = api->str_options.find("acc.type");
+    const bool want_device_build = (acc != api->str_options.end() && acc->second == "hlbvh") ||
+                                   (b != api->str_options.end() && b->second == "lbvh");
+    api->last_build_on_device = false;
     RRB_CUDA(cudaStreamSynchronize(api->stream));
     free_bvh(api);
-    RRB_CUDA(cudaMalloc(&api->d_nodes, bvh.nodes.size() * sizeof(uint32_t)));
-    RRB_CUDA(cudaMalloc(&api->d_tris, bvh.triangles.size() * sizeof(float)));
-    RRB_CUDA(cudaMemcpyAsync(api->d_nodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(uint32_t),
-                             cudaMemcpyHostToDevice, api->stream));
-    RRB_CUDA(cudaMemcpyAsync(api->d_tris, bvh.triangles.data(), bvh.triangles.size() * sizeof(float),
-                             cudaMemcpyHostToDevice, api->stream));
-    RRB_CUDA(cudaStreamSynchronize(api->stream));
-    api->num_nodes = bvh.num_nodes;
-    api->num_tris = bvh.num_tris;
-    if (refit_enabled(api)) {
-        // pooled object-space geometry + per-triangle mesh index + per-node exact boxes for later refits
+
+    // pooled object-space geometry on the device: input of the device builder and of later refits
+    std::vector<int> face_prefix(1, 0);
+    if (want_device_build || refit_enabled(api)) {
         std::vector<float> pv;
         std::vector<int> pi;
         api->refit_meshes.clear();
@@ -464,21 +459,72 @@ int rrb_commit(rrb_api* api) {
             rm.vertex_base = (int)(pv.size() / 3);
             rm.index_base = (int)pi.size();
             fill_refit_transform(rm, s);
+            for (int id : g->indices)
+                if (id < 0 || (size_t)id >= g->vertices.size() / 3)
+                    return fail(RRB_ERROR_INVALID_ARGUMENT, "vertex index out of range");
             pv.insert(pv.end(), g->vertices.begin(), g->vertices.end());
             pi.insert(pi.end(), g->indices.begin(), g->indices.end());
+            face_prefix.push_back(face_prefix.back() + (int)(g->indices.size() / 3));
             api->refit_meshes.push_back(rm);
         }
+        if (api->refit_meshes.empty()) return fail(RRB_ERROR_EMPTY_SCENE, "Scene is empty.");
         RRB_CUDA(cudaMalloc((void**)&api->d_ref_vertices, pv.size() * sizeof(float)));
         RRB_CUDA(cudaMalloc((void**)&api->d_ref_indices, pi.size() * sizeof(int)));
-        RRB_CUDA(cudaMalloc((void**)&api->d_tri_mesh, bvh.tri_mesh.size() * sizeof(int)));
-        RRB_CUDA(cudaMalloc((void**)&api->d_boxes, (size_t)bvh.num_nodes * 6 * sizeof(float)));
         RRB_CUDA(cudaMalloc((void**)&api->d_refit_meshes, api->refit_meshes.size() * sizeof(mcrt::RefitMesh)));
         RRB_CUDA(cudaMemcpyAsync(api->d_ref_vertices, pv.data(), pv.size() * sizeof(float), cudaMemcpyHostToDevice, api->stream));
         RRB_CUDA(cudaMemcpyAsync(api->d_ref_indices, pi.data(), pi.size() * sizeof(int), cudaMemcpyHostToDevice, api->stream));
-        RRB_CUDA(cudaMemcpyAsync(api->d_tri_mesh, bvh.tri_mesh.data(), bvh.tri_mesh.size() * sizeof(int),
-                                 cudaMemcpyHostToDevice, api->stream));
+        RRB_CUDA(cudaMemcpyAsync(api->d_refit_meshes, api->refit_meshes.data(),
+                                 api->refit_meshes.size() * sizeof(mcrt::RefitMesh), cudaMemcpyHostToDevice, api->stream));
         RRB_CUDA(cudaStreamSynchronize(api->stream));
-        api->level_offsets = bvh.level_offsets;
+    }
+
+    bool built = false;
+    if (want_device_build) {
+        mcrt::DeviceBvh8 dev;
+        std::string why;
+        if (mcrt::build_bvh8_device(api->d_ref_vertices, api->d_ref_indices, api->d_refit_meshes, face_prefix, &dev,
+                                    api->stream, &why)) {
+            api->d_nodes = dev.nodes;
+            api->d_tris = dev.tris;
+            api->d_tri_mesh = dev.tri_mesh;
+            api->d_boxes = dev.boxes;
+            api->num_nodes = dev.num_nodes;
+            api->num_tris = dev.num_tris;
+            api->level_offsets.assign(dev.level_offsets.begin(), dev.level_offsets.end());
+            api->launches += dev.launches;
+            api->last_build_on_device = true;
+            built = true;
+        } else {
+            api->device_build_fallback_reason = why;    // e.g. fewer than 4 triangles: the host builder takes over
+        }
+    }
+    if (!built) {
+        mcrt::Bvh8 bvh;
+        try {
+            mcrt::build_bvh8(meshes, opt, bvh);
+        } catch (const std::exception& ex) {
+            bool empty = std::string(ex.what()) == "Scene is empty.";
+            return fail(empty ? RRB_ERROR_EMPTY_SCENE : RRB_ERROR_INVALID_ARGUMENT, ex.what());
+        }
+        RRB_CUDA(cudaMalloc(&api->d_nodes, bvh.nodes.size() * sizeof(uint32_t)));
+        RRB_CUDA(cudaMalloc(&api->d_tris, bvh.triangles.size() * sizeof(float)));
+        RRB_CUDA(cudaMemcpyAsync(api->d_nodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(uint32_t),
+                                 cudaMemcpyHostToDevice, api->stream));
+        RRB_CUDA(cudaMemcpyAsync(api->d_tris, bvh.triangles.data(), bvh.triangles.size() * sizeof(float),
+                                 cudaMemcpyHostToDevice, api->stream));
+        api->num_nodes = bvh.num_nodes;
+        api->num_tris = bvh.num_tris;
+        if (api->d_ref_vertices) {
+            // per-triangle mesh index + per-node exact boxes for later refits
+            RRB_CUDA(cudaMalloc((void**)&api->d_tri_mesh, bvh.tri_mesh.size() * sizeof(int)));
+            RRB_CUDA(cudaMalloc((void**)&api->d_boxes, (size_t)bvh.num_nodes * 6 * sizeof(float)));
+            RRB_CUDA(cudaMemcpyAsync(api->d_tri_mesh, bvh.tri_mesh.data(), bvh.tri_mesh.size() * sizeof(int),
+                                     cudaMemcpyHostToDevice, api->stream));
+            api->level_offsets = bvh.level_offsets;
+        }
+        RRB_CUDA(cudaStreamSynchronize(api->stream));
+    }
+    if (api->d_ref_vertices) {
         api->built_world = api->world;
         api->built_mesh_of_shape = mesh_of_shape;
     }
@@ -735,6 +781,8 @@ int rrb_get_stats(rrb_api* api, rrb_stats* out) {
     out->launches = api->launches;
     out->refits = api->refits;
     out->last_commit_refit = api->last_commit_was_refit ? 1 : 0;
+    out->last_build_on_device = api->last_build_on_device ? 1 : 0;
+    out->num_levels = api->level_offsets.empty() ? 0 : (int64_t)api->level_offsets.size() - 1;
     return RRB_OK;
 }
 

@@ -28,7 +28,8 @@ class RadeonRaysError(RuntimeError):
 class RrbStats(ctypes.Structure):
     _fields_ = [("num_triangles", ctypes.c_int64), ("num_nodes", ctypes.c_int64), ("node_bytes", ctypes.c_int64),
                 ("triangle_bytes", ctypes.c_int64), ("build_seconds", ctypes.c_double), ("launches", ctypes.c_int64),
-                ("refits", ctypes.c_int64), ("last_commit_refit", ctypes.c_int64)]
+                ("refits", ctypes.c_int64), ("last_commit_refit", ctypes.c_int64),
+                ("last_build_on_device", ctypes.c_int64), ("num_levels", ctypes.c_int64)]
 
 
 def lib_path() -> str:

@@ -370,6 +370,78 @@ def test_golden_intersections(api, cornell):
     assert np.array_equal(api.QueryOcclusionHost(rays), g["occluded"])
 
 
+@pytest.mark.parametrize("how", ["acc.type=hlbvh", "bvh.builder=lbvh"])
+def test_device_built_tree_cornell(api, cornell, how):
+    """acc.type = "hlbvh" (Radeon Rays' GPU-built hierarchy, intersector_hlbvh.cpp) selects the device builder
+    (lbvh_build.cu).  Hit results do not depend on the tree: ids, t and barycentrics equal the brute-force oracle's
+    bit for bit, any-hit booleans are equal, also for directions with zero components."""
+    rr.attach_scene(api, cornell)
+    k, v = how.split("=")
+    api.SetOption(k, v)
+    api.Commit()
+    st = api.GetStats()
+    assert st["last_build_on_device"] == 1 and st["num_triangles"] == 36 and 1 <= st["num_levels"] <= 19
+    tris = port.scene_triangles(cornell)
+    lo, hi = cornell.world_bounds()
+    rays = random_rays(10000, lo - 1.0, hi + 1.0, seed=1234)
+    rays["d"][::7, 1] = np.float32(-0.0)
+    res = port.compare_hits(api.QueryIntersectionHost(rays), port.intersect(tris, rays), tris, rays)
+    assert res["bad"] == 0 and res["tie_ok"] == 0, res
+    assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
+    cam, _ = camera_rays(cornell, 128, 128)
+    res = port.compare_hits(api.QueryIntersectionHost(cam), port.intersect(tris, cam), tris, cam)
+    assert res["bad"] == 0 and res["tie_ok"] == 0, res
+
+
+def test_device_built_tree_large_soup_and_duplicates(api):
+    """Device build of a 200k-triangle soup in two meshes (one transformed, one instance-free duplicate of a block of
+    triangles, so equal Morton codes occur): closest hit and any hit against brute force; then the same tree is
+    refitted after a transform change (the device build leaves the refit inputs in place) and checked again."""
+    rng = np.random.RandomState(11)
+    n = 120000
+    c = rng.rand(n, 1, 3) * 20.0
+    v = (c + (rng.rand(n, 3, 3) - 0.5) * 0.5).reshape(-1, 3).astype(np.float32)
+    idx = np.arange(3 * n, dtype=np.int32).reshape(n, 3)
+    dup = 4000                                         # exact duplicates: identical boxes and Morton codes
+    v2 = np.concatenate([v[:3 * dup], (rng.rand(3 * (80000 - dup), 3) * 20.0).astype(np.float32)])
+    n2 = v2.shape[0] // 3
+    idx2 = np.arange(3 * n2, dtype=np.int32).reshape(n2, 3)
+    a, b = api.CreateMesh(v, 3 * n, 12, idx, 12, None, n), api.CreateMesh(v2, 3 * n2, 12, idx2, 12, None, n2)
+    a.SetId(3)
+    b.SetId(5)
+    m = _rot_y(20.0, (0.5, -0.25, 1.0))
+    b.SetTransform(m, np.linalg.inv(m))
+    api.AttachShape(a)
+    api.AttachShape(b)
+    api.SetOption("acc.type", "hlbvh")
+    api.SetOption("bvh.refit", 1.0)
+    api.Commit()
+    st = api.GetStats()
+    assert st["last_build_on_device"] == 1 and st["num_triangles"] == n + n2 and st["num_levels"] <= 19
+    rays = random_rays(20000, np.zeros(3), np.full(3, 20.0), 99, maxt=8.0)
+    tris = port.mesh_triangles([(v, idx, 3, None), (v2, idx2, 5, m)])
+    res = port.compare_hits(api.QueryIntersectionHost(rays), port.intersect(tris, rays), tris, rays)
+    assert res["bad"] == 0, res          # duplicated triangles tie with different ids: smallest id wins in both
+    assert res["tie_ok"] == 0, res
+    assert np.array_equal(api.QueryOcclusionHost(rays), port.occluded(tris, rays))
+    m2 = _rot_y(-35.0, (1.0, 0.5, -2.0))
+    b.SetTransform(m2, np.linalg.inv(m2))
+    api.Commit()
+    st = api.GetStats()
+    assert st["last_commit_refit"] == 1
+    tris = port.mesh_triangles([(v, idx, 3, None), (v2, idx2, 5, m2)])
+    res = port.compare_hits(api.QueryIntersectionHost(rays), port.intersect(tris, rays), tris, rays)
+    assert res["bad"] == 0 and res["tie_ok"] == 0, res
+
+
+def test_device_build_falls_back_below_four_triangles(api):
+    api.SetOption("acc.type", "hlbvh")
+    single_triangle(api)                 # commits: the device builder declines, the host builder takes over
+    assert api.GetStats()["last_build_on_device"] == 0
+    h = api.QueryIntersectionHost(one_ray((0.0, 0.0, -10.0), (0.0, 0.0, 1.0)))
+    assert h["shapeid"][0] != -1
+
+
 def test_axis_aligned_and_negative_zero_directions(api, cornell):
     """Directions with exact +0.0 / -0.0 components (directional-light shadow rays are like this):
     the sign used for the slab order must be the one used for the inverse direction."""
