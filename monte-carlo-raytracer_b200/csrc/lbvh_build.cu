@@ -20,6 +20,8 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include <cfloat>
+#include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -338,16 +340,32 @@ k_emit_triangles(const unsigned* __restrict__ emit_src, const unsigned* __restri
     tris[3 * (size_t)j + 1].w = phi[t].w;     // face index: what k_refit_triangles reads
 }
 
+// one device allocation carved into the builder's temporaries
 struct Scratch {
-    std::vector<void*> ptrs;
+    struct Req {
+        void** p;
+        size_t bytes;
+    };
+    std::vector<Req> reqs;
+    void* base = nullptr;
     ~Scratch() {
-        for (void* p : ptrs) cudaFree(p);
+        if (base) cudaFree(base);
     }
     template <typename T>
-    cudaError_t alloc(T** p, size_t count) {
-        cudaError_t e = cudaMalloc((void**)p, (count ? count : 1) * sizeof(T));
-        if (e == cudaSuccess) ptrs.push_back(*p);
-        return e;
+    void want(T** p, size_t count) {
+        reqs.push_back({(void**)p, ((count ? count : 1) * sizeof(T) + 255) & ~(size_t)255});
+    }
+    cudaError_t commit() {
+        size_t total = 0;
+        for (const Req& r : reqs) total += r.bytes;
+        cudaError_t e = cudaMalloc(&base, total);
+        if (e != cudaSuccess) return e;
+        size_t off = 0;
+        for (const Req& r : reqs) {
+            *r.p = (char*)base + off;
+            off += r.bytes;
+        }
+        return cudaSuccess;
     }
 };
 
@@ -375,38 +393,51 @@ bool build_bvh8_device(const float* d_vertices, const int* d_indices, const Refi
         return false;
     }
     const int n = (int)total;
+    const bool trace = getenv("MCRT_BUILD_TRACE") != nullptr;
+    cudaEvent_t ev[6];
+    if (trace) for (cudaEvent_t& e : ev) cudaEventCreate(&e);
     Scratch sc;
     int* d_prefix;
     float4 *plo, *phi, *ilo, *ihi;
     unsigned *bounds, *vals, *vals2, *flags, *emit_src, *counters;
     unsigned long long *keys, *keys2;
     int *left, *right, *first, *size, *parent, *leaf_parent, *q0, *q1;
-    LB_CUDA(sc.alloc(&d_prefix, face_prefix.size()));
-    LB_CUDA(sc.alloc(&plo, n));
-    LB_CUDA(sc.alloc(&phi, n));
-    LB_CUDA(sc.alloc(&ilo, n));
-    LB_CUDA(sc.alloc(&ihi, n));
-    LB_CUDA(sc.alloc(&bounds, 8));
-    LB_CUDA(sc.alloc(&keys, n));
-    LB_CUDA(sc.alloc(&keys2, n));
-    LB_CUDA(sc.alloc(&vals, n));
-    LB_CUDA(sc.alloc(&vals2, n));
-    LB_CUDA(sc.alloc(&flags, n));
-    LB_CUDA(sc.alloc(&emit_src, n));
-    LB_CUDA(sc.alloc(&counters, 4));
-    LB_CUDA(sc.alloc(&left, n));
-    LB_CUDA(sc.alloc(&right, n));
-    LB_CUDA(sc.alloc(&first, n));
-    LB_CUDA(sc.alloc(&size, n));
-    LB_CUDA(sc.alloc(&parent, n));
-    LB_CUDA(sc.alloc(&leaf_parent, n));
     // every wide node but the root stands for a subtree of >= 4 triangles, disjoint per level and halving upwards
     const int node_cap = n / 2 + 64;
-    LB_CUDA(sc.alloc(&q0, node_cap));
-    LB_CUDA(sc.alloc(&q1, node_cap));
     uint4* nodes_tmp;
-    LB_CUDA(sc.alloc(&nodes_tmp, 5 * (size_t)node_cap));
+    unsigned char* sort_temp;
+    size_t sort_temp_bytes = 0;
+    {
+        cub::DoubleBuffer<unsigned long long> dk(nullptr, nullptr);
+        cub::DoubleBuffer<unsigned> dv(nullptr, nullptr);
+        LB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_temp_bytes, dk, dv, n, 0, 63, stream));
+    }
+    sc.want(&d_prefix, face_prefix.size());
+    sc.want(&plo, n);
+    sc.want(&phi, n);
+    sc.want(&ilo, n);
+    sc.want(&ihi, n);
+    sc.want(&bounds, 8);
+    sc.want(&keys, n);
+    sc.want(&keys2, n);
+    sc.want(&vals, n);
+    sc.want(&vals2, n);
+    sc.want(&flags, n);
+    sc.want(&emit_src, n);
+    sc.want(&counters, 4);
+    sc.want(&left, n);
+    sc.want(&right, n);
+    sc.want(&first, n);
+    sc.want(&size, n);
+    sc.want(&parent, n);
+    sc.want(&leaf_parent, n);
+    sc.want(&q0, node_cap);
+    sc.want(&q1, node_cap);
+    sc.want(&nodes_tmp, 5 * (size_t)node_cap);
+    sc.want(&sort_temp, sort_temp_bytes);
+    LB_CUDA(sc.commit());
 
+    if (trace) cudaEventRecord(ev[0], stream);
     LB_CUDA(cudaMemcpyAsync(d_prefix, face_prefix.data(), face_prefix.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
     const unsigned init_bounds[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
     LB_CUDA(cudaMemcpyAsync(bounds, init_bounds, sizeof(init_bounds), cudaMemcpyHostToDevice, stream));
@@ -414,20 +445,19 @@ bool build_bvh8_device(const float* d_vertices, const int* d_indices, const Refi
     const int blocks = (n + 255) / 256;
     k_prim_bounds<<<blocks, 256, 0, stream>>>(d_vertices, d_indices, d_meshes, d_prefix, num_meshes, n, plo, phi, bounds);
     k_morton<<<blocks, 256, 0, stream>>>(plo, phi, bounds, n, keys, vals);
+    if (trace) cudaEventRecord(ev[1], stream);
     {
         cub::DoubleBuffer<unsigned long long> dk(keys, keys2);
         cub::DoubleBuffer<unsigned> dv(vals, vals2);
-        size_t temp_bytes = 0;
-        LB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, dk, dv, n, 0, 63, stream));
-        unsigned char* temp;
-        LB_CUDA(sc.alloc(&temp, temp_bytes));
-        LB_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, dk, dv, n, 0, 63, stream));
+        LB_CUDA(cub::DeviceRadixSort::SortPairs(sort_temp, sort_temp_bytes, dk, dv, n, 0, 63, stream));
         keys = dk.Current();
         vals = dv.Current();
     }
+    if (trace) cudaEventRecord(ev[2], stream);
     k_radix_tree<<<(n - 1 + 255) / 256, 256, 0, stream>>>(keys, n, left, right, first, size, parent, leaf_parent);
     k_fit_binary<<<blocks, 256, 0, stream>>>(vals, plo, phi, left, right, parent, leaf_parent, n, ilo, ihi, flags);
     LB_CUDA(cudaGetLastError());
+    if (trace) cudaEventRecord(ev[3], stream);
 
     // collapse, breadth-first; the level sizes come back to the host (the refit launches need them anyway)
     const unsigned zero4[4] = {0u, 0u, 0u, 0u};
@@ -480,6 +510,7 @@ bool build_bvh8_device(const float* d_vertices, const int* d_indices, const Refi
         }
     }
     const int num_nodes = level_first;
+    if (trace) cudaEventRecord(ev[4], stream);
 
     // results: exact-size node array, triangle records, per-triangle mesh index, per-node boxes
     void *nodes = nullptr, *tris = nullptr;
@@ -509,7 +540,17 @@ bool build_bvh8_device(const float* d_vertices, const int* d_indices, const Refi
     LB_CUDA2(cudaGetLastError());
     LB_CUDA2(refit_bvh8(nodes, tris, boxes, tri_mesh, d_meshes, d_vertices, d_indices, n, level_offsets.data(),
                         (int)level_offsets.size() - 1, stream));
+    if (trace) cudaEventRecord(ev[5], stream);
     LB_CUDA2(cudaStreamSynchronize(stream));
+    if (trace) {
+        const char* names[5] = {"bounds + morton", "radix sort", "radix tree + fit", "wide collapse", "emit + quantise"};
+        for (int k = 0; k < 5; ++k) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, ev[k], ev[k + 1]);
+            fprintf(stderr, "[lbvh] %-18s %8.3f ms\n", names[k], ms);
+        }
+        for (cudaEvent_t& e : ev) cudaEventDestroy(e);
+    }
 #undef LB_CUDA2
     out->nodes = nodes;
     out->tris = tris;

@@ -99,6 +99,7 @@ struct rrb_api {
     bool last_commit_was_refit = false;
     bool last_build_on_device = false;                 // acc.type = hlbvh / bvh.builder = lbvh (lbvh_build.cu)
     std::string device_build_fallback_reason;
+    std::vector<int> pool_face_prefix;                 // faces before each pooled mesh, total last
     unsigned int* d_counter = nullptr;
     std::vector<rrb_event*> event_pool;
     // staging for the host-buffer entry points
@@ -146,21 +147,30 @@ int wait_on(rrb_api* api, const rrb_event* wait) {
     return RRB_OK;
 }
 
-void free_refit(rrb_api* api) {
+// the pooled object-space geometry (meshes are immutable after CreateMesh: it stays valid while the world holds
+// the same shapes in the same order)
+void free_geometry_pool(rrb_api* api) {
     if (api->d_ref_vertices) cudaFree(api->d_ref_vertices);
     if (api->d_ref_indices) cudaFree(api->d_ref_indices);
-    if (api->d_tri_mesh) cudaFree(api->d_tri_mesh);
-    if (api->d_boxes) cudaFree(api->d_boxes);
     if (api->d_refit_meshes) cudaFree(api->d_refit_meshes);
     api->d_ref_vertices = nullptr;
     api->d_ref_indices = nullptr;
-    api->d_tri_mesh = nullptr;
-    api->d_boxes = nullptr;
     api->d_refit_meshes = nullptr;
     api->built_world.clear();
     api->built_mesh_of_shape.clear();
     api->refit_meshes.clear();
+    api->pool_face_prefix.clear();
+}
+void free_tree_refit_state(rrb_api* api) {
+    if (api->d_tri_mesh) cudaFree(api->d_tri_mesh);
+    if (api->d_boxes) cudaFree(api->d_boxes);
+    api->d_tri_mesh = nullptr;
+    api->d_boxes = nullptr;
     api->level_offsets.clear();
+}
+void free_refit(rrb_api* api) {
+    free_geometry_pool(api);
+    free_tree_refit_state(api);
 }
 
 void free_bvh(rrb_api* api) {
@@ -442,11 +452,38 @@ int rrb_commit(rrb_api* api) {
                                    (b != api->str_options.end() && b->second == "lbvh");
     api->last_build_on_device = false;
     RRB_CUDA(cudaStreamSynchronize(api->stream));
-    free_bvh(api);
+    // a rebuild over the same shapes (moved, re-numbered) keeps the pooled geometry on the device
+    const bool keep_pool = api->d_ref_vertices && !api->world_changed && api->built_world == api->world &&
+                           api->built_mesh_of_shape == mesh_of_shape;
+    if (keep_pool) {
+        if (api->d_nodes) cudaFree(api->d_nodes);
+        if (api->d_tris) cudaFree(api->d_tris);
+        api->d_nodes = api->d_tris = nullptr;
+        api->num_nodes = api->num_tris = 0;
+        free_tree_refit_state(api);
+    } else {
+        free_bvh(api);
+    }
 
+    const bool trace = getenv("MCRT_BUILD_TRACE") != nullptr;
+    auto lap = [&](const char* what) {
+        if (trace) fprintf(stderr, "[rrb_commit] %-22s %8.2f ms\n", what,
+                           std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() * 1e3);
+    };
+    lap("gathered meshes");
     // pooled object-space geometry on the device: input of the device builder and of later refits
     std::vector<int> face_prefix(1, 0);
-    if (want_device_build || refit_enabled(api)) {
+    if (keep_pool) {
+        size_t w = 0;
+        for (const rrb_shape* s : api->world) {
+            const int mi = mesh_of_shape[w++];
+            if (mi >= 0) fill_refit_transform(api->refit_meshes[(size_t)mi], s);
+        }
+        RRB_CUDA(cudaMemcpyAsync(api->d_refit_meshes, api->refit_meshes.data(),
+                                 api->refit_meshes.size() * sizeof(mcrt::RefitMesh), cudaMemcpyHostToDevice, api->stream));
+        face_prefix = api->pool_face_prefix;
+        lap("kept geometry pool");
+    } else if (want_device_build || refit_enabled(api)) {
         std::vector<float> pv;
         std::vector<int> pi;
         api->refit_meshes.clear();
@@ -476,6 +513,8 @@ int rrb_commit(rrb_api* api) {
         RRB_CUDA(cudaMemcpyAsync(api->d_refit_meshes, api->refit_meshes.data(),
                                  api->refit_meshes.size() * sizeof(mcrt::RefitMesh), cudaMemcpyHostToDevice, api->stream));
         RRB_CUDA(cudaStreamSynchronize(api->stream));
+        api->pool_face_prefix = face_prefix;
+        lap("pooled + uploaded");
     }
 
     bool built = false;
@@ -494,6 +533,7 @@ int rrb_commit(rrb_api* api) {
             api->launches += dev.launches;
             api->last_build_on_device = true;
             built = true;
+            lap("device build");
         } else {
             api->device_build_fallback_reason = why;    // e.g. fewer than 4 triangles: the host builder takes over
         }

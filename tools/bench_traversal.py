@@ -61,14 +61,25 @@ def main():
     ap.add_argument("--res", type=int, default=2048)
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--refit", action="store_true", help="also time a device refit against a full rebuild")
+    ap.add_argument("--builder", default="sah", choices=["sah", "median", "lbvh"],
+                    help="lbvh = the device builder (what acc.type = hlbvh selects)")
     a = ap.parse_args()
     scene = scene_library.traversal_bench_scene(a.quads)
     api = rr.IntersectionApi.Create(0)
-    rr.attach_scene(api, scene)
+    shapes = rr.attach_scene(api, scene)
+    api.SetOption("bvh.builder", a.builder)
     t0 = time.time()
     api.Commit()
     st = api.GetStats()
-    print(json.dumps({"tris": st["num_triangles"], "nodes": st["num_nodes"], "build_s": st["build_seconds"],
+    rebuilds = []
+    for k in range(3):           # warm rebuilds (the first device build also pays CUDA module load)
+        shapes[0].SetTransform(np.eye(4, dtype=np.float32))
+        t1 = time.perf_counter()
+        api.Commit()
+        rebuilds.append(round(time.perf_counter() - t1, 4))
+    print(json.dumps({"builder": a.builder, "on_device": st["last_build_on_device"], "levels": st["num_levels"],
+                      "tris": st["num_triangles"], "nodes": st["num_nodes"], "build_s": st["build_seconds"],
+                      "rebuild_s": rebuilds,
                       "node_MB": st["node_bytes"] / 1e6, "tri_MB": st["triangle_bytes"] / 1e6}))
     prim, _ = camera_rays(scene, a.res, a.res)
     hits = api.QueryIntersectionHost(prim)
