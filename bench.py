@@ -231,8 +231,9 @@ def own_arm(args):
     W, H, depth, P = args.width, args.height, args.depth, args.width * args.height
     stream = torch.cuda.Stream(device=dev)
     api = rr.IntersectionApi.Create(local, cuda_stream=stream.cuda_stream)
+    acc_type = os.environ.get("MCRT_ACC_TYPE", "fatbvh")      # hlbvh = the device builder (lbvh_build.cu)
     t0 = time.perf_counter()
-    pl = pt.make_pt_pipeline(api, scene, W, H, depth)          # attaches shapes, Commit() builds the BVH, uploads
+    pl = pt.make_pt_pipeline(api, scene, W, H, depth, acc_type=acc_type)          # attaches shapes, Commit() builds the BVH, uploads
     setup_s = time.perf_counter() - t0
     stats = api.GetStats()
     pl.ensure_size()
@@ -427,7 +428,9 @@ def own_arm(args):
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / K, "h2d_bytes_per_step": 176,
                         "d2h_bytes_per_step": int(host_np.nbytes), "image_mean": img_mean},
                 "gpu_launches": launches_total, "clocks": clocks,
-                "bvh": {"build_and_upload_s": setup_s, "nodes": int(stats.get("num_nodes", 0)) if isinstance(stats, dict) else None}}
+                "bvh": {"build_and_upload_s": setup_s, "nodes": int(stats.get("num_nodes", 0)) if isinstance(stats, dict) else None,
+                        "acc_type": acc_type, "on_device": int(stats.get("last_build_on_device", 0)) if isinstance(stats, dict) else None,
+                        "commit_s": float(stats.get("build_seconds", 0.0)) if isinstance(stats, dict) else None}}
         emit(line)
     pl.scene.destroy()
     rr.IntersectionApi.Delete(api)

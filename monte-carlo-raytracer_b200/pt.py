@@ -132,15 +132,16 @@ class RTScene:
     """Device scene + Radeon Rays world: RTScene's constructor, attachMesh and commit
     (scene/RTScene.cpp:28-56,199-267,564-678) for a headless host scene."""
 
-    def __init__(self, api: rr.IntersectionApi, scene, refit=False):
+    def __init__(self, api: rr.IntersectionApi, scene, refit=False, acc_type="fatbvh", builder="sah"):
         self.api = api
         self.host = scene
         self.shapes = rr.attach_scene(api, scene)
         if refit:       # extension: transform-only commits refit the tree on the device (include/rrb.h)
             api.SetOption("bvh.refit", 1.0)
         # RTScene::commit: acc.type / bvh.builder from the GUI defaults (PathTracingSettings.h:241-249)
-        api.SetOption("acc.type", "fatbvh")
-        api.SetOption("bvh.builder", "sah")
+        # (acc.type = "hlbvh", Radeon Rays' GPU-built hierarchy, selects the device builder here too)
+        api.SetOption("acc.type", acc_type)
+        api.SetOption("bvh.builder", builder)
         api.SetOption("bvh.sah.traversal_cost", 10.0)
         api.SetOption("bvh.sah.num_bins", 64.0)
         api.Commit()
@@ -436,9 +437,9 @@ def write_pfm(path, image, width, height):
         f.write(np.ascontiguousarray(rgb, "<f4").tobytes())
 
 
-def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=True, refit=False):
+def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=True, refit=False, acc_type="fatbvh"):
     """PathTracingApp::startPathTracing's PT pipeline (:248-255) without denoise / tonemap / display."""
-    rts = RTScene(api, scene, refit=refit)
+    rts = RTScene(api, scene, refit=refit, acc_type=acc_type)
     gi = GISettings()
     gi.imageResolution = (width, height)
     gi.maxDepth = max_depth
@@ -469,9 +470,9 @@ def smoke_check(api, scene, width=64, height=64, depth=3):
     return out[0]
 
 
-def make_bdpt_pipeline(api, scene, width, height, max_depth, use_taa=True):
+def make_bdpt_pipeline(api, scene, width, height, max_depth, use_taa=True, acc_type="fatbvh"):
     """PathTracingApp::startPathTracing's BDPT pipeline (:256-263): RTBDPTPass + RTReconstructionPass."""
-    rts = RTScene(api, scene)
+    rts = RTScene(api, scene, acc_type=acc_type)
     gi = GISettings()
     gi.imageResolution = (width, height)
     gi.maxDepth = max_depth

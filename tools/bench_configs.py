@@ -29,9 +29,10 @@ from mcrt_b200 import camera, pt, rr, scene_library  # noqa: E402
 def run(name, scene, w, h, depth, steps, bdpt=False, tiles=None):
     stream = torch.cuda.Stream()
     api = rr.IntersectionApi.Create(0, cuda_stream=stream.cuda_stream)
+    acc_type = os.environ.get("MCRT_ACC_TYPE", "fatbvh")      # hlbvh = the device builder (lbvh_build.cu)
     t0 = time.perf_counter()
     make = pt.make_bdpt_pipeline if bdpt else pt.make_pt_pipeline
-    pl = make(api, scene, w, h, depth)
+    pl = make(api, scene, w, h, depth, acc_type=acc_type)
     setup = time.perf_counter() - t0
     pl.ensure_size()
     if tiles:
