@@ -47,6 +47,20 @@ struct BVertex {
     V3 beta;
 };
 
+// The two vertex evaluators inline the whole uber material (texture-modulated properties + BSDF value or density)
+// and have four call sites each: inlined, k_bdpt_prepare / k_bdpt_connect are 250 / 200 KB of SASS and stall on
+// instruction fetch (ncu r01: no_instructions 35 % / 59 % of the samples).  Out of line they shrink to 156 / 73 KB
+// (connect: 123 -> 67 registers), but the vertex then travels through local memory: C4 9.91 ms per frame against
+// 9.67 ms inlined (same run), so inlining stays the default.
+#ifndef BDPT_NOINLINE_EVAL
+#define BDPT_NOINLINE_EVAL 0
+#endif
+#if BDPT_NOINLINE_EVAL
+#define BD_EVAL static __device__ __noinline__
+#else
+#define BD_EVAL HD
+#endif
+
 HD bool vOnSurface(const BVertex& v) {     // BDPT.cl:39-42 isVertexOnSurface
     return isNotNearZero(v.si.gn.x) || isNotNearZero(v.si.gn.y) || isNotNearZero(v.si.gn.z);
 }
@@ -171,7 +185,7 @@ HD float evalVertexPdfLight(const Scene& sc, const BVertex& thisV, const BVertex
 }
 
 // thisV must carry LEVEL >= 1 fields when it is a surface vertex
-HD float evalVertexPdf(const Scene& sc, const BVertex& thisV, const BVertex* prevV, const BVertex& nextV) {
+BD_EVAL float evalVertexPdf(const Scene& sc, const BVertex& thisV, const BVertex* prevV, const BVertex& nextV) {
     if (thisV.type == RT_BDPT_LIGHT_VERTEX) return evalVertexPdfLight(sc, thisV, nextV);
     V3 wn = nextV.si.p - thisV.si.p;
     float lenSq = dot(wn, wn);
@@ -207,7 +221,7 @@ HD float evalVertexPdfLightOrigin(const Scene& sc, const BVertex& thisV, V3 next
 }
 
 // thisV: surface vertex with LEVEL >= 2 fields
-HD V3 evalVertex_f(const Scene& sc, const BVertex& thisV, V3 nextP, int mode) {
+BD_EVAL V3 evalVertex_f(const Scene& sc, const BVertex& thisV, V3 nextP, int mode) {
     V3 wi = nextP - thisV.si.p;
     float lenSq = dot(wi, wi);
     if (isNearZero(lenSq)) return v3(0.0f);
