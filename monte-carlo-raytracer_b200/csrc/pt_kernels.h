@@ -26,6 +26,7 @@ struct PtState {
     const void* materials;
     const void* camera;
     const uint32_t* sobol;   // Sobol generator matrices when that sampler is selected, else NULL
+    const float2* material_alpha;   // roughnessToAlpha of every material (launch_material_alpha), may be NULL
     int numLights;
     int width, height;
     // acceleration structure
@@ -114,6 +115,9 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
 cudaError_t launch_generate_primary_rays(const PtState& s, cudaStream_t stream);
 cudaError_t launch_pt_shade_aos(const PtState& s, int frame, int max_depth, int bounce, cudaStream_t stream);
 cudaError_t launch_pt_shadow_resolve_aos(const PtState& s, int bounce, cudaStream_t stream);
+
+// alpha[i] = (roughnessToAlpha(materials[i].roughness.x), roughnessToAlpha(materials[i].roughness.y))
+cudaError_t launch_material_alpha(const void* materials, float2* alpha, int num_materials, cudaStream_t stream);
 
 struct FilterProps {
     int filter_type;

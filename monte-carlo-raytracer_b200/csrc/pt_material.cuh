@@ -38,14 +38,19 @@ HD void getUberMaterialProperties(const Scene& sc, int materialIdx, const RTInte
     t = v3(1.0f);
     if (m->opacityTexId != RT_INVALID_ID) t = v3(readTexture2Df(sc, m->opacityTexId, si->uv));
     p->opacity = t * v3(m->opacity) * Kd_opacity.w;
-    V2 r = v2(m->roughness.x, m->roughness.y);
-    if (m->roughnessTexId != RT_INVALID_ID) {
-        float4 q = readTexture2Df(sc, m->roughnessTexId, si->uv);
-        r = v2(q.x, q.y);
-    }
     p->eta = m->eta;
     if (m->iorTexId != RT_INVALID_ID) p->eta = readTexture2Df(sc, m->iorTexId, si->uv).x;
-    p->roughness = v2(roughnessToAlpha(r.x), roughnessToAlpha(r.y));
+    if (m->roughnessTexId == RT_INVALID_ID && sc.materialAlpha) {
+        const float2 a = __ldg(sc.materialAlpha + materialIdx);     // = the two roughnessToAlpha() below, precomputed
+        p->roughness = v2(a.x, a.y);
+    } else {
+        V2 r = v2(m->roughness.x, m->roughness.y);
+        if (m->roughnessTexId != RT_INVALID_ID) {
+            float4 q = readTexture2Df(sc, m->roughnessTexId, si->uv);
+            r = v2(q.x, q.y);
+        }
+        p->roughness = v2(roughnessToAlpha(r.x), roughnessToAlpha(r.y));
+    }
 }
 
 // bxdfs.cl:804-827 evaluateUberBSDF

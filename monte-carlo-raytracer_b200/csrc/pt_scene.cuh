@@ -66,6 +66,10 @@ struct Scene {              // kernel_data.h:353-370 (device pointers)
     const RTMaterial* __restrict__ materials;
     const RTPinholeCamera* __restrict__ camera;
     const uint32_t* __restrict__ sobolMatrices;   // NULL = random sampler
+    // roughnessToAlpha(material.roughness) of every material, computed once on the device by the same function
+    // (k_material_alpha); read instead of re-evaluating two logf polynomials per material lookup when the
+    // material has no roughness texture.  NULL = always evaluate.
+    const float2* __restrict__ materialAlpha;
     int numLights;
 };
 

@@ -41,6 +41,7 @@ __device__ __forceinline__ Scene make_scene2(const PtState& s) {
     sc.materials = (const RTMaterial*)s.materials;
     sc.camera = (const RTPinholeCamera*)s.camera;
     sc.sobolMatrices = s.sobol;
+    sc.materialAlpha = nullptr;   // the stage-wise kernels evaluate roughnessToAlpha per lookup, like the reference
     sc.numLights = s.numLights;
     return sc;
 }
@@ -221,6 +222,17 @@ cudaError_t launch_accumulate(const PtState& s, const FilterProps& f, int frame,
                               cudaStream_t stream) {
     if (n_pixels <= 0) return cudaSuccess;
     k_accumulate<<<(n_pixels + 255) / 256, 256, 0, stream>>>(s, f, frame, pixels, n_pixels);
+    return cudaGetLastError();
+}
+
+__global__ void k_material_alpha(const RTMaterial* __restrict__ materials, float2* __restrict__ alpha, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    alpha[i] = make_float2(roughnessToAlpha(materials[i].roughness.x), roughnessToAlpha(materials[i].roughness.y));
+}
+cudaError_t launch_material_alpha(const void* materials, float2* alpha, int num_materials, cudaStream_t stream) {
+    if (num_materials <= 0) return cudaSuccess;
+    k_material_alpha<<<(num_materials + 127) / 128, 128, 0, stream>>>((const RTMaterial*)materials, alpha, num_materials);
     return cudaGetLastError();
 }
 

@@ -21,6 +21,7 @@ __device__ __forceinline__ Scene make_scene(const PtState& s) {
     sc.materials = (const RTMaterial*)s.materials;
     sc.camera = (const RTPinholeCamera*)s.camera;
     sc.sobolMatrices = s.sobol;
+    sc.materialAlpha = s.material_alpha;
     sc.numLights = s.numLights;
     return sc;
 }

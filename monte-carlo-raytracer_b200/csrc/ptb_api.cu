@@ -68,6 +68,7 @@ struct ptb_context {
     size_t snapshot_bytes = 0;
     bool copy_pending = false;
     int halves = 2;
+    int num_materials = 0;
     ptb_context() {
         std::memset(&st, 0, sizeof(st));
         std::memset(&bd, 0, sizeof(bd));
@@ -308,6 +309,15 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
     c->st.lights = p;
     if ((rc = upload(c, "materials", d->materials, (size_t)d->num_materials * 128, &p))) return rc;
     c->st.materials = p;
+    {
+        void* a = nullptr;
+        if ((rc = alloc_into(c->scene_bufs, "material_alpha", (size_t)std::max(d->num_materials, 1) * sizeof(float2), true,
+                             c->stream, &a)))
+            return rc;
+        c->st.material_alpha = (const float2*)a;
+        c->num_materials = d->num_materials;
+        PTB_CUDA(mcrt::launch_material_alpha(c->st.materials, (float2*)a, d->num_materials, c->stream));
+    }
     c->st.numLights = d->num_lights;
     if (d->sobol && (rc = set_sobol_table(c, d->sobol, 1024))) return rc;   // the engine's table (scene/RTScene.cpp:55)
     PTB_CUDA(cudaStreamSynchronize(c->stream));
@@ -327,6 +337,8 @@ int ptb_update_scene_array(ptb_context* c, const char* array, const void* data, 
     int rc = set_dev(c);
     if (rc) return rc;
     PTB_CUDA(cudaMemcpyAsync(it->second.p, data, bytes, cudaMemcpyHostToDevice, c->stream));
+    if (name == "materials")
+        PTB_CUDA(mcrt::launch_material_alpha(c->st.materials, (float2*)c->st.material_alpha, c->num_materials, c->stream));
     return 0;
 }
 
