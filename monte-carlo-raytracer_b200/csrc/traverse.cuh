@@ -31,6 +31,15 @@ namespace mcrt {
 #define MCRT_POSTPONE_PERCENT 35      // profiles/r01_traversal_variants.md
 #endif
 
+// Latency hints (experiment knob, off).  Bit 0: while a triangle is tested, the next one of the group is prefetched.
+// Bit 1: as soon as a node's hit mask is known, the child that will be visited first is prefetched.  Measured
+// (profiles/r01_c5_tiles.md): neither shortens the tail of a launch, and the node prefetch costs 20 % of the mixed
+// trace on C3 (issue slots), so both stay off.
+#ifndef MCRT_TRAV_PREFETCH
+#define MCRT_TRAV_PREFETCH 0
+#endif
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 struct Ray {
     float ox, oy, oz, tmax;
     float dx, dy, dz;
@@ -254,6 +263,14 @@ struct Traverser {
                 }
                 ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
                 tgroup.y = hitmask & 0x00FFFFFFu;
+#if MCRT_TRAV_PREFETCH & 2
+                if (ngroup.y > 0x00FFFFFFu) {      // the child the next iteration will pop
+                    const uint32_t nslot = ((31u - __clz(ngroup.y)) - 24u) ^ octinv;
+                    const uint4* nn = nodes + 5 * (size_t)(ngroup.x + __popc(ngroup.y & ~(0xFFFFFFFFu << nslot)));
+                    prefetch_l1(nn);
+                    prefetch_l1(nn + 4);           // an 80-byte node can straddle two 128-byte lines
+                }
+#endif
             } else {
                 tgroup = ngroup;
                 ngroup = make_uint2(0u, 0u);
@@ -269,6 +286,13 @@ struct Traverser {
                 const uint32_t ti = 31u - __clz(tgroup.y);
                 tgroup.y &= ~(1u << ti);
                 const size_t ta = (size_t)tgroup.x + ti;
+#if MCRT_TRAV_PREFETCH & 1
+                if (tgroup.y != 0u) {
+                    const float4* nt = tris + 3 * ((size_t)tgroup.x + (31u - __clz(tgroup.y)));
+                    prefetch_l1(nt);
+                    prefetch_l1(nt + 2);
+                }
+#endif
                 const float4 v0 = __ldg(tris + 3 * ta + 0);
                 const float4 v1 = __ldg(tris + 3 * ta + 1);
                 const float4 v2 = __ldg(tris + 3 * ta + 2);
