@@ -116,6 +116,14 @@ int ptb_bdpt_render_sample(ptb_context* ctx, int frame, int max_depth);
  * on two streams, so that each kernel's drain-out tail is filled by the other half's kernels;
  * 1 = one wavefront on the context's stream.  Per-sample results are identical. */
 int ptb_set_overlap(ptb_context* ctx, int halves);
+/* Frames in flight: with depth D > 1 (at most 4; default 1) consecutive ptb_pt_render_sample calls are issued on D
+ * side streams, each with its own wavefront state and camera copy, so that the latency chain of one frame -- every
+ * traversal launch ends with the few rays that graze the mesh -- is filled by the work of the following frames.
+ * ptb_accumulate consumes the frames in the order they were rendered, on the context's stream; every other entry
+ * point first waits for the frames in flight, so the call sequence of the render passes and every per-sample value
+ * are unchanged.  "RadianceBufferCL" names the buffer of the frame rendered last.  Costs 184 B per pixel of device
+ * memory per extra frame. */
+int ptb_set_frames_in_flight(ptb_context* ctx, int depth);
 /* Order of the live-path queues of ptb_pt_render_sample.  The reference's sampler is a pure function of (pixel, frame,
  * bounce) (samplers.cl:75-84), so which light a vertex will sample and which half of the lobe-selection variate it
  * will draw are known before its ray is traced: 1 = queues of bounces >= 1 are bucketed by that key (warps of the

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
 #include <map>
 #include <memory>
 #include <string>
@@ -69,6 +70,24 @@ struct ptb_context {
     bool copy_pending = false;
     int halves = 2;
     int num_materials = 0;
+    // Frames in flight (ptb_set_frames_in_flight): with D > 1 consecutive ptb_pt_render_sample calls run on D side
+    // streams with their own wavefront state, so that the latency chain of one frame (the few long rays that keep
+    // every traversal launch alive, profiles/r01_c5_tiles.md) is filled by the next frames' work.  ptb_accumulate
+    // consumes the frames in the order they were rendered, on the context's stream.
+    struct FrameSlot {
+        cudaStream_t stream = nullptr;
+        cudaEvent_t render_done = nullptr, slot_free = nullptr;
+        bool done_recorded = false, free_recorded = false;
+        mcrt::PtOverlap overlap{nullptr, nullptr, nullptr, nullptr};
+        mcrt::PtState st;     // per-slot pointers filled in by alloc_slots(); scene / options copied at launch
+        void* camera = nullptr;
+        uint64_t camera_version = 0;
+    };
+    unsigned char camera_host[176] = {0};   // last ptb_set_camera argument: each slot takes its copy when it renders
+    uint64_t camera_version = 0;
+    std::vector<FrameSlot> slots;     // empty = one frame at a time on the context's stream
+    int next_slot = 0;
+    std::deque<int> rendered;         // slots holding a frame that has not been accumulated yet
     ptb_context() {
         std::memset(&st, 0, sizeof(st));
         std::memset(&bd, 0, sizeof(bd));
@@ -155,6 +174,124 @@ int ready(ptb_context* c) {
     return refresh_bvh(c);
 }
 
+// ---- frames in flight
+bool pipelined(const ptb_context* c) { return c->slots.size() > 1 && !c->profiling; }
+
+// the context's stream waits (on the device) for every frame rendered on a side stream
+int join_frames(ptb_context* c) {
+    for (ptb_context::FrameSlot& s : c->slots)
+        if (s.done_recorded) PTB_CUDA(cudaStreamWaitEvent(c->stream, s.render_done, 0));
+    return 0;
+}
+// ... and forgets them: whatever follows works on the context's own state
+int join_and_drop_frames(ptb_context* c) {
+    int rc = join_frames(c);
+    if (rc) return rc;
+    c->rendered.clear();
+    auto it = c->named.find("RadianceBufferCL");
+    if (it != c->named.end()) it->second.p = c->st.radiance;
+    return 0;
+}
+
+void destroy_slots(ptb_context* c) {
+    for (ptb_context::FrameSlot& s : c->slots) {
+        if (s.stream) {
+            cudaStreamSynchronize(s.stream);
+            cudaStreamDestroy(s.stream);
+        }
+        if (s.render_done) cudaEventDestroy(s.render_done);
+        if (s.slot_free) cudaEventDestroy(s.slot_free);
+        if (s.overlap.stream) {
+            cudaStreamSynchronize(s.overlap.stream);
+            cudaStreamDestroy(s.overlap.stream);
+            cudaEventDestroy(s.overlap.fork);
+            cudaEventDestroy(s.overlap.join);
+            cudaEventDestroy(s.overlap.stagger);
+        }
+    }
+    c->slots.clear();
+    c->rendered.clear();
+    c->next_slot = 0;
+    for (auto it = c->pixel_bufs.begin(); it != c->pixel_bufs.end();) {
+        if (it->first.rfind("slot", 0) == 0) {
+            if (it->second.p) cudaFree(it->second.p);
+            it = c->pixel_bufs.erase(it);
+        } else {
+            ++it;
+        }
+    }
+}
+
+// per-slot wavefront state (slot 0 reuses the context's own arrays)
+int alloc_slots(ptb_context* c, int depth) {
+    destroy_slots(c);
+    if (depth <= 1) return 0;
+    c->slots.resize((size_t)depth);
+    const size_t P = (size_t)c->width * c->height;
+    for (int k = 0; k < depth; ++k) {
+        ptb_context::FrameSlot& s = c->slots[(size_t)k];
+        PTB_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        PTB_CUDA(cudaEventCreateWithFlags(&s.render_done, cudaEventDisableTiming));
+        PTB_CUDA(cudaEventCreateWithFlags(&s.slot_free, cudaEventDisableTiming));
+        PTB_CUDA(cudaStreamCreateWithFlags(&s.overlap.stream, cudaStreamNonBlocking));
+        PTB_CUDA(cudaEventCreateWithFlags(&s.overlap.fork, cudaEventDisableTiming));
+        PTB_CUDA(cudaEventCreateWithFlags(&s.overlap.join, cudaEventDisableTiming));
+        PTB_CUDA(cudaEventCreateWithFlags(&s.overlap.stagger, cudaEventDisableTiming));
+        s.st = c->st;
+        const std::string pre = "slot" + std::to_string(k) + "_";
+        void* p = nullptr;
+        int rc;
+        if ((rc = alloc_into(c->pixel_bufs, pre + "camera", 176, true, c->stream, &p))) return rc;
+        s.camera = p;
+        if ((rc = alloc_into(c->pixel_bufs, pre + "cnt", 2 * mcrt::PT_CNT_STRIDE * sizeof(unsigned int), true, c->stream, &p)))
+            return rc;
+        s.st.cnt = (unsigned int*)p;
+        if (k == 0 || P == 0) continue;
+        struct {
+            const char* name;
+            size_t elem;
+            void** dst;
+        } specs[] = {
+            {"ray_o", 16, (void**)&s.st.ray_o},   {"ray_d", 16, (void**)&s.st.ray_d},
+            {"hit", 16, (void**)&s.st.hit},       {"throughput", 16, (void**)&s.st.throughput},
+            {"radiance", 16, (void**)&s.st.radiance}, {"direct_weight", 16, (void**)&s.st.direct_weight},
+            {"queue0", 4, (void**)&s.st.queue[0]}, {"queue1", 4, (void**)&s.st.queue[1]},
+            {"bucket", 4 * mcrt::PT_NUM_BUCKETS, (void**)&s.st.bucket},
+            {"sh_o", 16, (void**)&s.st.sh_o},     {"sh_d", 16, (void**)&s.st.sh_d},
+            {"sh_L", 16, (void**)&s.st.sh_L},
+        };
+        for (auto& sp : specs) {
+            if ((rc = alloc_into(c->pixel_bufs, pre + sp.name, P * sp.elem, true, c->stream, &p))) return rc;
+            *sp.dst = p;
+        }
+    }
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// the PtState a slot renders with: the context's scene / options, the slot's wavefront arrays
+mcrt::PtState slot_state(const ptb_context* c, int k) {
+    const ptb_context::FrameSlot& s = c->slots[(size_t)k];
+    mcrt::PtState st = c->st;
+    st.camera = s.camera;
+    st.cnt = s.st.cnt;
+    if (k > 0) {
+        st.ray_o = s.st.ray_o;
+        st.ray_d = s.st.ray_d;
+        st.hit = s.st.hit;
+        st.throughput = s.st.throughput;
+        st.radiance = s.st.radiance;
+        st.direct_weight = s.st.direct_weight;
+        st.queue[0] = s.st.queue[0];
+        st.queue[1] = s.st.queue[1];
+        st.bucket = s.st.bucket;
+        st.sh_o = s.st.sh_o;
+        st.sh_d = s.st.sh_d;
+        st.sh_L = s.st.sh_L;
+    }
+    return st;
+}
+
 // 64x64 tiles dealt round-robin in row-major tile order (partition A)
 void partition_pixels(int width, int height, int part, int num_parts, std::vector<uint32_t>& px) {
     const int tw = (width + 63) / 64, th = (height + 63) / 64;
@@ -228,6 +365,7 @@ int ptb_set_overlap(ptb_context* c, int halves) {
     if (!c || (halves != 1 && halves != 2)) return pfail(RRB_ERROR_INVALID_ARGUMENT, "halves must be 1 or 2");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->halves = halves;
     return 0;
@@ -238,6 +376,7 @@ int ptb_set_estimator(ptb_context* c, int flags) {
         return pfail(RRB_ERROR_INVALID_ARGUMENT, "unknown estimator flag");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->st.estimator = flags;
     return 0;
@@ -247,6 +386,7 @@ int ptb_set_coherence(ptb_context* c, int mode) {
     if (!c || mode < 0 || mode > 3) return pfail(RRB_ERROR_INVALID_ARGUMENT, "coherence mode must be 0 .. 3");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->st.coherence = mode;
     return 0;
@@ -256,6 +396,7 @@ int ptb_destroy(ptb_context* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    destroy_slots(c);
     free_map(c->scene_bufs);
     free_map(c->pixel_bufs);
     for (const char* k : {"__cnt", "__stats", "__camera"}) {
@@ -287,6 +428,7 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
     if (!c || !d) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     free_map(c->scene_bufs);
     c->scene_loaded = false;
@@ -336,9 +478,11 @@ int ptb_update_scene_array(ptb_context* c, const char* array, const void* data, 
         return pfail(RRB_ERROR_INVALID_ARGUMENT, "size of '" + name + "' differs from the uploaded array");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaMemcpyAsync(it->second.p, data, bytes, cudaMemcpyHostToDevice, c->stream));
     if (name == "materials")
         PTB_CUDA(mcrt::launch_material_alpha(c->st.materials, (float2*)c->st.material_alpha, c->num_materials, c->stream));
+    if (!c->slots.empty()) PTB_CUDA(cudaStreamSynchronize(c->stream));   // frames on side streams must see the update
     return 0;
 }
 
@@ -346,6 +490,7 @@ int ptb_set_sampler(ptb_context* c, int kind, const uint32_t* matrices, int num_
     if (!c || (kind != 0 && kind != 1)) return pfail(RRB_ERROR_INVALID_ARGUMENT, "sampler kind must be 0 (Sobol) or 1 (random)");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     if (matrices) {
         if (num_dimensions < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "num_dimensions must be >= 1");
@@ -361,7 +506,10 @@ int ptb_resize(ptb_context* c, int width, int height) {
     if (!c || width <= 0 || height <= 0) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad size");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
+    const int frames_in_flight = (int)c->slots.size();
+    destroy_slots(c);
     free_map(c->pixel_bufs);
     c->bdpt_depth = -1;
     std::memset(&c->bd, 0, sizeof(c->bd));
@@ -416,8 +564,18 @@ int ptb_resize(ptb_context* c, int width, int height) {
     }
     rc = build_partition(c);
     if (rc) return rc;
+    if ((rc = alloc_slots(c, frames_in_flight))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
+}
+
+int ptb_set_frames_in_flight(ptb_context* c, int depth) {
+    if (!c || depth < 1 || depth > 4) return pfail(RRB_ERROR_INVALID_ARGUMENT, "frames in flight must be 1 .. 4");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    return alloc_slots(c, depth);
 }
 
 int ptb_set_camera(ptb_context* c, const void* cam) {
@@ -426,6 +584,10 @@ int ptb_set_camera(ptb_context* c, const void* cam) {
     if (rc) return rc;
     // pageable source: the copy is staged before the call returns, so the caller may reuse `cam`
     PTB_CUDA(cudaMemcpyAsync((void*)c->st.camera, cam, 176, cudaMemcpyHostToDevice, c->stream));
+    // frames in flight take their own copy on their own stream when they are rendered: it must not queue up behind
+    // the accumulation of the previous frame on the context's stream
+    std::memcpy(c->camera_host, cam, 176);
+    c->camera_version += 1;
     return 0;
 }
 
@@ -449,6 +611,7 @@ int ptb_set_partition(ptb_context* c, int part, int num_parts) {
     if (c->width > 0) {
         int rc = set_dev(c);
         if (rc) return rc;
+        if ((rc = join_and_drop_frames(c))) return rc;
         PTB_CUDA(cudaStreamSynchronize(c->stream));
         return build_partition(c);
     }
@@ -465,6 +628,7 @@ extern "C" {
 int ptb_generate_primary_rays(ptb_context* c) {
     int rc = ready(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(mcrt::launch_generate_primary_rays(c->st, c->stream));
     c->launches += 1;
     return 0;
@@ -473,6 +637,7 @@ int ptb_generate_primary_rays(ptb_context* c) {
 int ptb_pt_shade(ptb_context* c, int frame, int max_depth, int bounce) {
     int rc = ready(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(mcrt::launch_pt_shade_aos(c->st, frame, max_depth, bounce, c->stream));
     c->launches += 1;
     return 0;
@@ -481,6 +646,7 @@ int ptb_pt_shade(ptb_context* c, int frame, int max_depth, int bounce) {
 int ptb_pt_shadow_resolve(ptb_context* c, int bounce) {
     int rc = ready(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(mcrt::launch_pt_shadow_resolve_aos(c->st, bounce, c->stream));
     c->launches += 1;
     return 0;
@@ -491,6 +657,29 @@ int ptb_pt_render_sample(ptb_context* c, int frame, int max_depth) {
     if (rc) return rc;
     if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
     cudaError_t e = cudaSuccess;
+    if (pipelined(c)) {
+        const int k = c->next_slot;
+        ptb_context::FrameSlot& s = c->slots[(size_t)k];
+        // a slot whose frame was never accumulated is simply rendered over, as the one radiance buffer would be
+        for (auto it = c->rendered.begin(); it != c->rendered.end();)
+            it = (*it == k) ? c->rendered.erase(it) : it + 1;
+        if (s.free_recorded) PTB_CUDA(cudaStreamWaitEvent(s.stream, s.slot_free, 0));
+        if (s.camera_version != c->camera_version) {
+            PTB_CUDA(cudaMemcpyAsync(s.camera, c->camera_host, 176, cudaMemcpyHostToDevice, s.stream));
+            s.camera_version = c->camera_version;
+        }
+        const mcrt::PtState st = slot_state(c, k);
+        c->launches += mcrt::launch_pt_sample(st, c->d_pixels, c->n_pixels, frame, max_depth, s.stream, &e, nullptr,
+                                              c->halves == 2 ? &s.overlap : nullptr);
+        if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("path tracer launch: ") + cudaGetErrorString(e));
+        PTB_CUDA(cudaEventRecord(s.render_done, s.stream));
+        s.done_recorded = true;
+        c->rendered.push_back(k);
+        c->named["RadianceBufferCL"].p = st.radiance;
+        c->next_slot = (k + 1) % (int)c->slots.size();
+        return 0;
+    }
+    if ((rc = join_and_drop_frames(c))) return rc;
     c->launches += mcrt::launch_pt_sample(c->st, c->d_pixels, c->n_pixels, frame, max_depth, c->stream, &e,
                                           c->profiling ? &c->timer : nullptr, c->halves == 2 ? &c->overlap : nullptr);
     if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("path tracer launch: ") + cudaGetErrorString(e));
@@ -501,6 +690,7 @@ int ptb_profile_enable(ptb_context* c, int on) {
     if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->profiling = on != 0;
     c->timer.reset();
@@ -511,6 +701,7 @@ int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
     if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     double acc[mcrt::StageTimer::NUM_STAGES] = {0.0, 0.0, 0.0, 0.0};
     int64_t n[mcrt::StageTimer::NUM_STAGES] = {0, 0, 0, 0};
@@ -534,6 +725,7 @@ int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
 int ptb_bdpt_render_sample(ptb_context* c, int frame, int max_depth) {
     int rc = ready(c);
     if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
     if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
     if (c->bdpt_depth != max_depth) {
         // RTBDPTPass::createBuffers (RTBDPTPass.cpp:451-478): sized by maxDepth, zero-filled (E12)
@@ -576,7 +768,18 @@ int ptb_accumulate(ptb_context* c, int frame, const ptb_filter_props* f) {
     fp.gaussian_exp_y = f->gaussian_exp_y;
     fp.pixel_offset[0] = f->pixel_offset[0];
     fp.pixel_offset[1] = f->pixel_offset[1];
-    PTB_CUDA(mcrt::launch_accumulate(c->st, fp, frame, c->d_pixels, c->n_pixels, c->stream));
+    if (!c->rendered.empty()) {
+        // the oldest frame still waiting on a side stream: accumulation keeps the order of the render calls
+        const int k = c->rendered.front();
+        c->rendered.pop_front();
+        ptb_context::FrameSlot& s = c->slots[(size_t)k];
+        PTB_CUDA(cudaStreamWaitEvent(c->stream, s.render_done, 0));
+        PTB_CUDA(mcrt::launch_accumulate(slot_state(c, k), fp, frame, c->d_pixels, c->n_pixels, c->stream));
+        PTB_CUDA(cudaEventRecord(s.slot_free, c->stream));
+        s.free_recorded = true;
+    } else {
+        PTB_CUDA(mcrt::launch_accumulate(c->st, fp, frame, c->d_pixels, c->n_pixels, c->stream));
+    }
     c->launches += 1;
     return 0;
 }
@@ -595,6 +798,7 @@ int named_image(ptb_context* c, const char* name, float4** out) {
 int ptb_denoise(ptb_context* c, const char* src_name, int radius, float sigma_spatial, float sigma_range) {
     int rc = ready(c);
     if (rc) return rc;
+    if ((rc = join_frames(c))) return rc;
     float4* src = nullptr;
     if ((rc = named_image(c, src_name, &src))) return rc;
     if (src == c->denoised) return pfail(RRB_ERROR_INVALID_ARGUMENT, "denoise cannot run in place");
@@ -609,6 +813,7 @@ int ptb_denoise(ptb_context* c, const char* src_name, int radius, float sigma_sp
 int ptb_tonemap(ptb_context* c, const char* src_name, float lwhite) {
     int rc = ready(c);
     if (rc) return rc;
+    if ((rc = join_frames(c))) return rc;
     float4* src = nullptr;
     if ((rc = named_image(c, src_name, &src))) return rc;
     cudaError_t e = mcrt::launch_reinhard_tonemap(c->width, c->height, lwhite, src, c->tonemapped, c->stream);
@@ -620,6 +825,7 @@ int ptb_tonemap(ptb_context* c, const char* src_name, float lwhite) {
 int ptb_reset_accumulation(ptb_context* c) {
     int rc = ready(c);
     if (rc) return rc;
+    if ((rc = join_frames(c))) return rc;
     const size_t P = (size_t)c->width * c->height;
     PTB_CUDA(cudaMemsetAsync(c->st.weighted_radiance, 0, P * 16, c->stream));
     PTB_CUDA(cudaMemsetAsync(c->st.filter_weights, 0, P * 4, c->stream));
@@ -643,6 +849,7 @@ int ptb_read_buffer(ptb_context* c, const char* name, void* host_dst, size_t byt
     if (rc) return rc;
     if (!host_dst || bytes > n) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad destination or size");
     if ((rc = set_dev(c))) return rc;
+    if ((rc = join_frames(c))) return rc;
     PTB_CUDA(cudaMemcpyAsync(host_dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
@@ -665,6 +872,7 @@ int ptb_read_buffer_async(ptb_context* c, const char* name, void* host_dst, size
     if (rc) return rc;
     if (!host_dst || bytes > n) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad destination or size");
     if ((rc = set_dev(c))) return rc;
+    if ((rc = join_frames(c))) return rc;
     if (!c->copy_stream) {
         PTB_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
         PTB_CUDA(cudaEventCreateWithFlags(&c->snap_ready, cudaEventDisableTiming));
@@ -692,6 +900,7 @@ int ptb_synchronize(ptb_context* c) {
     if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -700,6 +909,7 @@ int ptb_get_counters(ptb_context* c, ptb_counters* out) {
     if (!c || !out) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_frames(c))) return rc;
     unsigned long long h[8];
     PTB_CUDA(cudaMemcpyAsync(h, c->st.stats, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
     PTB_CUDA(cudaStreamSynchronize(c->stream));
@@ -715,6 +925,7 @@ int ptb_reset_counters(ptb_context* c) {
     if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
     int rc = set_dev(c);
     if (rc) return rc;
+    if ((rc = join_frames(c))) return rc;
     PTB_CUDA(cudaMemsetAsync(c->st.stats, 0, 64, c->stream));
     c->launches = 0;
     return 0;

@@ -68,6 +68,7 @@ def _lib():
             "ptb_tonemap": [vp, ctypes.c_char_p, ctypes.c_float],
             "ptb_profile_enable": [vp, ctypes.c_int], "ptb_set_overlap": [vp, ctypes.c_int],
             "ptb_set_coherence": [vp, ctypes.c_int], "ptb_set_estimator": [vp, ctypes.c_int],
+            "ptb_set_frames_in_flight": [vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
         }
@@ -283,6 +284,10 @@ class RenderPipeline:
 
     def set_overlap(self, halves):
         _check(_lib().ptb_set_overlap(self.scene._h, int(halves)))
+
+    def set_frames_in_flight(self, depth):
+        """Render up to `depth` consecutive frames concurrently on side streams (include/ptb.h); results unchanged."""
+        _check(_lib().ptb_set_frames_in_flight(self.scene._h, int(depth)))
 
     def set_coherence(self, mode):
         """Queue order of the fused wavefront: 0 push order, 1 bounces >= 1 bucketed by the sampler's light / lobe

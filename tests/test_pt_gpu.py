@@ -448,6 +448,56 @@ def test_coherence_bucketed_queues_equal_push_order_bitwise(api, halves):
             assert res[0][2][k] == res[mode][2][k], (mode, k)
 
 
+@pytest.mark.parametrize("depth_in_flight", [2, 4])
+def test_frames_in_flight_equal_one_at_a_time_bitwise(api, depth_in_flight):
+    """ptb_set_frames_in_flight: consecutive frames rendered concurrently on side streams (own wavefront state and
+    camera copy each, accumulation in render order) give bit for bit the images and counters of frames rendered one
+    at a time -- with reads in between (which join the frames) and without, with a tile partition, after a hot material
+    update, and when the frames-in-flight depth changes in the middle of a run."""
+    w, h, depth, frames = 512, 320, 5, 7
+
+    def run(d, partition=None, read_each=False):
+        scene = scene_library.sponza_class(64)      # fresh: the hot update below replaces the host scene's materials
+        a = rr.IntersectionApi.Create(0)
+        try:
+            pl = pt.make_pt_pipeline(a, scene, w, h, depth)
+            pl.ensure_size()
+            if partition:
+                pl.set_partition(*partition)
+            pl.set_frames_in_flight(d)
+            per_frame = []
+            for f in range(frames):
+                if f == 3:      # hot update in the middle: later frames must see it, earlier ones must not
+                    mats = scene.materials.copy()
+                    mats["uber_kd"][:, :3] *= 0.5
+                    pl.scene.updateDynamicEntities(materials=mats)
+                if f == 5 and d > 1:
+                    pl.set_frames_in_flight(d - 1)
+                pl.update()
+                if read_each:
+                    per_frame.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+            img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+            wr = pl.read_buffer("WeightedRadianceBuffer").reshape(-1, 4).copy()
+            cnt = pl.counters()
+            pl.scene.destroy()
+        finally:
+            rr.IntersectionApi.Delete(a)
+        return per_frame, img, wr, cnt
+
+    for partition in (None, (1, 3)):
+        base = run(1, partition, read_each=True)
+        for read_each in (True, False):
+            got = run(depth_in_flight, partition, read_each)
+            if read_each:
+                for f in range(frames):
+                    assert np.array_equal(base[0][f].view(np.uint32), got[0][f].view(np.uint32)), (partition, f)
+            assert np.array_equal(base[2].view(np.uint32), got[2].view(np.uint32)), (partition, read_each)
+            assert np.array_equal(base[1].view(np.uint32), got[1].view(np.uint32), equal_nan=False) or \
+                np.array_equal(np.nan_to_num(base[1]).view(np.uint32), np.nan_to_num(got[1]).view(np.uint32))
+            for k in ("samples", "closest_rays", "shadow_rays", "shaded_vertices"):
+                assert base[3][k] == got[3][k], (partition, read_each, k)
+
+
 def _mean_radiance(scene, w, h, depth, frames, **estimator):
     a = rr.IntersectionApi.Create(0)
     try:
