@@ -53,6 +53,11 @@ def parse_args():
     ap.add_argument("--tex", type=int, default=1024, help="texture edge length (1024 = the named workload)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--frames-in-flight", type=int, default=1,
+                    help="consecutive samples rendered concurrently on side streams (ptb_set_frames_in_flight). "
+                         "Measured on this workload (profiles/r01_frames_in_flight.md): 3 in flight gives +1.4 %% "
+                         "device-resident and -7 %% end to end, so the default is one frame at a time; the option pays "
+                         "where a frame is small or tail-heavy (tile partitions, the 4K knot)")
     return ap.parse_args()
 
 
@@ -60,6 +65,7 @@ def config_of(args, n_gpus):
     return {"workload": WORKLOAD, "triangles": 262144, "width": args.width, "height": args.height,
             "max_depth": args.depth, "spp_per_step": 1, "textures": "74 x %d^2 RGBA8" % args.tex,
             "lights": "point+directional+area", "partition": "sample-index x%d, 1 all-reduce/step (overlapped with the next step)" % n_gpus if n_gpus > 1 else "none",
+            "frames_in_flight": args.frames_in_flight,
             "l2": "no flush: per-step working set (pixel state + textures) exceeds the 126 MB L2"}
 
 
@@ -237,6 +243,7 @@ def own_arm(args):
     setup_s = time.perf_counter() - t0
     stats = api.GetStats()
     pl.ensure_size()
+    pl.set_frames_in_flight(max(1, min(4, args.frames_in_flight)))
     pt_pass = pl.passes[0]
     lib, h = pt._lib(), pl.scene._h
     fprops = pl.GI.filter_props()
@@ -412,7 +419,7 @@ def own_arm(args):
                     "launches": nb, "avg_launch_ms": top_ms / nb, "algorithmic_bytes_per_launch": top_bytes / nb,
                     "stage_ms_per_step": {k: v[0] / K for k, v in stages.items()},
                     "stage_share_of_step": {k: v[0] / max(ms_single, 1e-9) for k, v in stages.items()},
-                    "stage_timing": "separate %d-step loop, one wavefront per frame (%.3f ms/step); the timed region "
+                    "stage_timing": "separate %d-step loop, one frame at a time, one wavefront per frame (%.3f ms/step); the timed region "
                                     "overlaps two half-frame wavefronts on two streams" % (K, ms_single / K),
                     "trace_rays_per_s": (cnt["closest_rays"] + cnt["shadow_rays"]) /
                                         max((t_closest + t_mixed + t_shadow) * 1e-3, 1e-12)}

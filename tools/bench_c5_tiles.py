@@ -43,6 +43,7 @@ def main():
     ap.add_argument("--reduce-every", type=int, default=0)
     ap.add_argument("--acc-type", default="hlbvh", help="hlbvh = device builder (fast set-up); fatbvh = host SAH")
     ap.add_argument("--verify", action="store_true")
+    ap.add_argument("--frames-in-flight", type=int, default=3, help="ptb_set_frames_in_flight (1 = off)")
     ap.add_argument("--partition", default="tiles", choices=["tiles", "samples"],
                     help="tiles: every rank renders its 64x64 tiles of every sample (strong scaling, BASELINE configs[4]); "
                          "samples: rank r renders whole frames r, r+N, ... (weak scaling, like bench.py)")
@@ -65,6 +66,7 @@ def main():
     by_tiles = a.partition == "tiles"
     if by_tiles:
         pl.set_partition(rank, world)
+    pl.set_frames_in_flight(a.frames_in_flight)
     lib, h = pt._lib(), pl.scene._h
     fprops = pl.GI.filter_props()
     views = {k: pl.device_buffer(k) for k in ("WeightedRadianceBuffer", "FilterWeightsBuffer", "NextFrameImageCL")}
@@ -139,7 +141,7 @@ def main():
             "n_gpus": world, "partition": a.partition, "scaling": "strong" if by_tiles else "weak", "steps": K, "warmup": Wm, "ms_per_step": ms / K,
             "paths_per_s": float(tot[0].item()) / (ms * 1e-3), "mrays_per_s": float(tot[1].item()) / (ms * 1e-3) / 1e6,
             "reduce": "every %d step(s)" % a.reduce_every if a.reduce_every else "once per run",
-            "allreduce_bytes": 20 * P, "acc_type": a.acc_type, "bvh_on_device": st["last_build_on_device"],
+            "frames_in_flight": a.frames_in_flight, "allreduce_bytes": 20 * P, "acc_type": a.acc_type, "bvh_on_device": st["last_build_on_device"],
             "setup_s": setup_s, "commit_s": st["build_seconds"], "image_mean": float(img[:, :3].mean()),
             "finite": bool(np.isfinite(img).all()), "bit_identical_to_one_gpu": verified}), flush=True)
     if world > 1:
