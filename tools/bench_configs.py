@@ -35,6 +35,9 @@ def run(name, scene, w, h, depth, steps, bdpt=False, tiles=None):
     pl = make(api, scene, w, h, depth, acc_type=acc_type)
     setup = time.perf_counter() - t0
     pl.ensure_size()
+    fif = int(os.environ.get("MCRT_FRAMES_IN_FLIGHT", "1"))
+    if fif > 1 and not bdpt:
+        pl.set_frames_in_flight(fif)
     if tiles:
         pl.set_partition(tiles[0], tiles[1])
     lib, hnd = pt._lib(), pl.scene._h
@@ -68,7 +71,7 @@ def run(name, scene, w, h, depth, steps, bdpt=False, tiles=None):
     st = api.GetStats()
     img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4)
     line = {"config": name, "integrator": "bdpt" if bdpt else "pt", "triangles": int(st["num_triangles"]),
-            "width": w, "height": h, "max_depth": depth, "steps": steps, "tiles": tiles,
+            "width": w, "height": h, "max_depth": depth, "steps": steps, "tiles": tiles, "frames_in_flight": fif,
             "ms_per_step": ms / steps, "paths_per_s": cnt["samples"] / (ms * 1e-3),
             "mrays_per_s": (cnt["closest_rays"] + cnt["shadow_rays"]) / (ms * 1e-3) / 1e6,
             "rays_per_path": (cnt["closest_rays"] + cnt["shadow_rays"]) / max(cnt["samples"], 1),
