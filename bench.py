@@ -53,11 +53,10 @@ def parse_args():
     ap.add_argument("--tex", type=int, default=1024, help="texture edge length (1024 = the named workload)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--frames-in-flight", type=int, default=1,
-                    help="consecutive samples rendered concurrently on side streams (ptb_set_frames_in_flight). "
-                         "Measured on this workload (profiles/r01_frames_in_flight.md): 3 in flight gives +1.4 %% "
-                         "device-resident and -7 %% end to end, so the default is one frame at a time; the option pays "
-                         "where a frame is small or tail-heavy (tile partitions, the 4K knot)")
+    ap.add_argument("--frames-in-flight", type=int, default=2,
+                    help="consecutive samples rendered concurrently on side streams (ptb_set_frames_in_flight); results "
+                         "are bit-identical.  Measured on this workload (profiles/r01_c5_tiles.md): 1 -> 3.87 ms per step "
+                         "device-resident / 3.90 end to end, 2 -> 3.65 / 3.69, 3 -> 3.66 / 3.83")
     return ap.parse_args()
 
 
@@ -243,7 +242,12 @@ def own_arm(args):
     setup_s = time.perf_counter() - t0
     stats = api.GetStats()
     pl.ensure_size()
-    pl.set_frames_in_flight(max(1, min(4, args.frames_in_flight)))
+    fif = max(1, min(4, args.frames_in_flight))
+    pl.set_frames_in_flight(fif)
+    # with frames in flight a frame is issued as ONE wavefront: whole frames overlap each other, and that fills the
+    # kernel tails better than two half-frame wavefronts of the same frame do (profiles/r01_frames_in_flight.md)
+    timed_halves = 1 if fif > 1 else 2
+    pl.set_overlap(timed_halves)
     pt_pass = pl.passes[0]
     lib, h = pt._lib(), pl.scene._h
     fprops = pl.GI.filter_props()
@@ -351,7 +355,7 @@ def own_arm(args):
         ms_single = max_over_ranks(ev0.elapsed_time(ev1))
         prof = pl.profile_collect()
         pl.profile_enable(False)
-        pl.set_overlap(2)
+        pl.set_overlap(timed_halves)
 
         # ---------------- end to end through the pipeline mirror, image read back every step
         pt._check(lib.ptb_reset_accumulation(h))
@@ -419,8 +423,9 @@ def own_arm(args):
                     "launches": nb, "avg_launch_ms": top_ms / nb, "algorithmic_bytes_per_launch": top_bytes / nb,
                     "stage_ms_per_step": {k: v[0] / K for k, v in stages.items()},
                     "stage_share_of_step": {k: v[0] / max(ms_single, 1e-9) for k, v in stages.items()},
-                    "stage_timing": "separate %d-step loop, one frame at a time, one wavefront per frame (%.3f ms/step); the timed region "
-                                    "overlaps two half-frame wavefronts on two streams" % (K, ms_single / K),
+                    "stage_timing": "separate %d-step loop, one frame at a time, one wavefront per frame (%.3f ms/step); the timed region %s"
+                                    % (K, ms_single / K, ("keeps %d frames in flight on side streams" % fif) if fif > 1 else
+                                       "overlaps two half-frame wavefronts on two streams"),
                     "trace_rays_per_s": (cnt["closest_rays"] + cnt["shadow_rays"]) /
                                         max((t_closest + t_mixed + t_shadow) * 1e-3, 1e-12)}
         cpu = None

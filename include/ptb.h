@@ -173,8 +173,9 @@ int ptb_get_buffer(ptb_context* ctx, const char* name, void** device_ptr, size_t
 int ptb_read_buffer(ptb_context* ctx, const char* name, void* host_dst, size_t bytes);
 /* Pipelined read-back for a consumer that wants the image every frame (the role of RTDisplayPass): snapshots the
  * buffer on the context's stream (device-to-device), then copies the snapshot to `host_dst` (pinned memory) on a
- * copy stream while the next frame renders.  `host_dst` is valid after ptb_read_wait, or after the next
- * ptb_read_buffer_async (which waits for the previous copy first).  One copy in flight per context. */
+ * copy stream while the next frames render.  Two copies may be in flight per context: `host_dst` is valid after
+ * ptb_read_wait, or after the second ptb_read_buffer_async that follows (which waits for the copy issued two calls
+ * before it), so a consumer rotates three host buffers -- or two, if it only looks at an image after the wait. */
 int ptb_read_buffer_async(ptb_context* ctx, const char* name, void* host_dst, size_t bytes);
 int ptb_read_wait(ptb_context* ctx);
 int ptb_synchronize(ptb_context* ctx);

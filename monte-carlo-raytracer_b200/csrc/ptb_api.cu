@@ -63,11 +63,14 @@ struct ptb_context {
     mcrt::StageTimer timer;
     mcrt::PtOverlap overlap{nullptr, nullptr, nullptr, nullptr};   // second stream of a frame (ptb_set_overlap)
     // asynchronous read-back (ptb_read_buffer_async): device snapshot + copy stream
+    // (two snapshots in rotation: the host waits for the copy issued two calls ago, not for the previous one, so it
+    // can keep enqueuing frames while an image is still crossing PCIe)
     cudaStream_t copy_stream = nullptr;
-    cudaEvent_t snap_ready = nullptr, copy_done = nullptr;
-    void* snapshot = nullptr;
-    size_t snapshot_bytes = 0;
-    bool copy_pending = false;
+    cudaEvent_t snap_ready[2] = {nullptr, nullptr}, copy_done[2] = {nullptr, nullptr};
+    void* snapshot[2] = {nullptr, nullptr};
+    size_t snapshot_bytes[2] = {0, 0};
+    bool copy_pending[2] = {false, false};
+    int snap_next = 0;
     int halves = 2;
     int num_materials = 0;
     // Frames in flight (ptb_set_frames_in_flight): with D > 1 consecutive ptb_pt_render_sample calls run on D side
@@ -409,9 +412,11 @@ int ptb_destroy(ptb_context* c) {
     if (c->copy_stream) {
         cudaStreamSynchronize(c->copy_stream);
         cudaStreamDestroy(c->copy_stream);
-        cudaEventDestroy(c->snap_ready);
-        cudaEventDestroy(c->copy_done);
-        if (c->snapshot) cudaFree(c->snapshot);
+        for (int k = 0; k < 2; ++k) {
+            cudaEventDestroy(c->snap_ready[k]);
+            cudaEventDestroy(c->copy_done[k]);
+            if (c->snapshot[k]) cudaFree(c->snapshot[k]);
+        }
     }
     if (c->overlap.stream) {
         cudaStreamSynchronize(c->overlap.stream);
@@ -857,11 +862,14 @@ int ptb_read_buffer(ptb_context* c, const char* name, void* host_dst, size_t byt
 
 int ptb_read_wait(ptb_context* c) {
     if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
-    if (!c->copy_pending) return 0;
+    if (!c->copy_pending[0] && !c->copy_pending[1]) return 0;
     int rc = set_dev(c);
     if (rc) return rc;
-    PTB_CUDA(cudaEventSynchronize(c->copy_done));
-    c->copy_pending = false;
+    for (int k = 0; k < 2; ++k)
+        if (c->copy_pending[k]) {
+            PTB_CUDA(cudaEventSynchronize(c->copy_done[k]));
+            c->copy_pending[k] = false;
+        }
     return 0;
 }
 
@@ -875,24 +883,31 @@ int ptb_read_buffer_async(ptb_context* c, const char* name, void* host_dst, size
     if ((rc = join_frames(c))) return rc;
     if (!c->copy_stream) {
         PTB_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-        PTB_CUDA(cudaEventCreateWithFlags(&c->snap_ready, cudaEventDisableTiming));
-        PTB_CUDA(cudaEventCreateWithFlags(&c->copy_done, cudaEventDisableTiming));
+        for (int k = 0; k < 2; ++k) {
+            PTB_CUDA(cudaEventCreateWithFlags(&c->snap_ready[k], cudaEventDisableTiming));
+            PTB_CUDA(cudaEventCreateWithFlags(&c->copy_done[k], cudaEventDisableTiming));
+        }
     }
-    if ((rc = ptb_read_wait(c))) return rc;            // the one snapshot is free again
-    if (c->snapshot_bytes < bytes) {
-        if (c->snapshot) cudaFree(c->snapshot);
-        c->snapshot = nullptr;
-        c->snapshot_bytes = 0;
-        cudaError_t e = cudaMalloc(&c->snapshot, bytes);
+    const int k = c->snap_next;
+    c->snap_next ^= 1;
+    if (c->copy_pending[k]) {                        // the copy issued two calls ago: this snapshot is free again
+        PTB_CUDA(cudaEventSynchronize(c->copy_done[k]));
+        c->copy_pending[k] = false;
+    }
+    if (c->snapshot_bytes[k] < bytes) {
+        if (c->snapshot[k]) cudaFree(c->snapshot[k]);
+        c->snapshot[k] = nullptr;
+        c->snapshot_bytes[k] = 0;
+        cudaError_t e = cudaMalloc(&c->snapshot[k], bytes);
         if (e != cudaSuccess) return pfail(RRB_ERROR_OUT_OF_MEMORY, std::string("cudaMalloc(snapshot): ") + cudaGetErrorString(e));
-        c->snapshot_bytes = bytes;
+        c->snapshot_bytes[k] = bytes;
     }
-    PTB_CUDA(cudaMemcpyAsync(c->snapshot, p, bytes, cudaMemcpyDeviceToDevice, c->stream));
-    PTB_CUDA(cudaEventRecord(c->snap_ready, c->stream));
-    PTB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->snap_ready, 0));
-    PTB_CUDA(cudaMemcpyAsync(host_dst, c->snapshot, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
-    PTB_CUDA(cudaEventRecord(c->copy_done, c->copy_stream));
-    c->copy_pending = true;
+    PTB_CUDA(cudaMemcpyAsync(c->snapshot[k], p, bytes, cudaMemcpyDeviceToDevice, c->stream));
+    PTB_CUDA(cudaEventRecord(c->snap_ready[k], c->stream));
+    PTB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->snap_ready[k], 0));
+    PTB_CUDA(cudaMemcpyAsync(host_dst, c->snapshot[k], bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    PTB_CUDA(cudaEventRecord(c->copy_done[k], c->copy_stream));
+    c->copy_pending[k] = true;
     return 0;
 }
 

@@ -563,15 +563,16 @@ def test_pipelined_readback_equals_blocking_read(api, cornell):
     import torch
     w = h = 128
     pl = pt.make_pt_pipeline(api, cornell, w, h, 3)
-    host = [torch.empty(4 * w * h, dtype=torch.float32, pin_memory=True).numpy() for _ in range(2)]
+    host = [torch.empty(4 * w * h, dtype=torch.float32, pin_memory=True).numpy() for _ in range(3)]
     want = []
-    for f in range(3):
+    for f in range(6):
         pl.update()
-        pl.read_buffer_async("NextFrameImageCL", host[f & 1])
+        pl.read_buffer_async("NextFrameImageCL", host[f % 3])
         want.append(pl.read_buffer("NextFrameImageCL").copy())      # blocking read of the same frame
-        if f >= 1:
-            # slot (f - 1) & 1 was waited for by the async call above and holds frame f - 1
-            assert np.array_equal(host[(f - 1) & 1].view(np.uint32), want[f - 1].view(np.uint32))
+        if f >= 2:
+            # two copies may be in flight: the call above waited for the one issued two calls ago (frame f - 2)
+            assert np.array_equal(host[(f - 2) % 3].view(np.uint32), want[f - 2].view(np.uint32))
     pl.read_wait()
-    assert np.array_equal(host[0].view(np.uint32), want[2].view(np.uint32))
+    for f in (4, 5):
+        assert np.array_equal(host[f % 3].view(np.uint32), want[f].view(np.uint32))
     pl.scene.destroy()
