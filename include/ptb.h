@@ -168,6 +168,10 @@ int ptb_reset_accumulation(ptb_context* ctx);
 int ptb_denoise(ptb_context* ctx, const char* src_name, int radius, float sigma_spatial, float sigma_range);
 int ptb_tonemap(ptb_context* ctx, const char* src_name, float lwhite);
 
+/* Self-test (no reference counterpart): the shading code's division helper -- IEEE division with a branch-free
+ * shortcut for zero numerators, pt_math.cuh:fdiv -- and the plain hardware division, element-wise over host arrays. */
+int ptb_selftest_fdiv(ptb_context* ctx, const float* a, const float* b, float* out_shortcut, float* out_plain, int n);
+
 int ptb_get_buffer(ptb_context* ctx, const char* name, void** device_ptr, size_t* bytes);
 /* Blocking device->host read of a named buffer (the step's result for the end-to-end leg). */
 int ptb_read_buffer(ptb_context* ctx, const char* name, void* host_dst, size_t bytes);

@@ -119,6 +119,8 @@ cudaError_t launch_pt_shadow_resolve_aos(const PtState& s, int bounce, cudaStrea
 // alpha[i] = (roughnessToAlpha(materials[i].roughness.x), roughnessToAlpha(materials[i].roughness.y))
 cudaError_t launch_material_alpha(const void* materials, float2* alpha, int num_materials, cudaStream_t stream);
 
+cudaError_t launch_selftest_fdiv(const float* a, const float* b, float* shortcut, float* plain, int n, cudaStream_t stream);
+
 struct FilterProps {
     int filter_type;
     float radius[2];

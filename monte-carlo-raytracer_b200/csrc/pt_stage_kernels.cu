@@ -236,4 +236,18 @@ cudaError_t launch_material_alpha(const void* materials, float2* alpha, int num_
     return cudaGetLastError();
 }
 
+// self-test of pt_math.cuh:fdiv against the plain IEEE division (ptb_selftest_fdiv)
+__global__ void k_selftest_fdiv(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ shortcut,
+                                float* __restrict__ plain, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    shortcut[i] = fdiv(a[i], b[i]);
+    plain[i] = __fdiv_rn(a[i], b[i]);
+}
+cudaError_t launch_selftest_fdiv(const float* a, const float* b, float* shortcut, float* plain, int n, cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    k_selftest_fdiv<<<(n + 255) / 256, 256, 0, stream>>>(a, b, shortcut, plain, n);
+    return cudaGetLastError();
+}
+
 }  // namespace mcrt

@@ -920,6 +920,25 @@ int ptb_synchronize(ptb_context* c) {
     return 0;
 }
 
+int ptb_selftest_fdiv(ptb_context* c, const float* a, const float* b, float* out_shortcut, float* out_plain, int n) {
+    if (!c || !a || !b || !out_shortcut || !out_plain || n < 0) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad argument");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    if (n == 0) return 0;
+    float* d = nullptr;
+    const size_t bytes = (size_t)n * sizeof(float);
+    PTB_CUDA(cudaMalloc((void**)&d, 4 * bytes));
+    cudaError_t e = cudaMemcpyAsync(d, a, bytes, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d + n, b, bytes, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = mcrt::launch_selftest_fdiv(d, d + n, d + 2 * (size_t)n, d + 3 * (size_t)n, n, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_shortcut, d + 2 * (size_t)n, bytes, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_plain, d + 3 * (size_t)n, bytes, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("fdiv self-test: ") + cudaGetErrorString(e));
+    return 0;
+}
+
 int ptb_get_counters(ptb_context* c, ptb_counters* out) {
     if (!c || !out) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
     int rc = set_dev(c);

@@ -69,6 +69,7 @@ def _lib():
             "ptb_profile_enable": [vp, ctypes.c_int], "ptb_set_overlap": [vp, ctypes.c_int],
             "ptb_set_coherence": [vp, ctypes.c_int], "ptb_set_estimator": [vp, ctypes.c_int],
             "ptb_set_frames_in_flight": [vp, ctypes.c_int],
+            "ptb_selftest_fdiv": [vp, vp, vp, vp, vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
         }

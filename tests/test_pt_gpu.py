@@ -498,6 +498,29 @@ def test_frames_in_flight_equal_one_at_a_time_bitwise(api, depth_in_flight):
                 assert base[3][k] == got[3][k], (partition, read_each, k)
 
 
+def test_division_shortcut_is_ieee_division(api, cornell):
+    """pt_math.cuh:fdiv (zero numerators answered without the hardware sequence's slow path) returns, bit for bit,
+    what IEEE division returns -- for signed zeros, infinities, NaNs, denormals and 4 M random bit patterns."""
+    pl = pt.make_pt_pipeline(api, cornell, 64, 64, 2)
+    rng = np.random.RandomState(5)
+    special = np.array([0.0, -0.0, 1.0, -1.0, np.inf, -np.inf, np.nan, 1e-45, -1e-45, 1e-39, 3e38, -3e38, 1.17549435e-38,
+                        2.0 ** -40, 2.0 ** -100, 2.0 ** 100, 0.1, -7.5], np.float32)
+    a = np.concatenate([np.repeat(special, special.size), rng.randint(0, 2 ** 32, 1 << 22, dtype=np.uint64).astype(np.uint32).view(np.float32),
+                        np.zeros(1 << 16, np.float32), -np.zeros(1 << 16, np.float32)])
+    b = np.concatenate([np.tile(special, special.size), rng.randint(0, 2 ** 32, 1 << 22, dtype=np.uint64).astype(np.uint32).view(np.float32),
+                        rng.randint(0, 2 ** 32, 1 << 17, dtype=np.uint64).astype(np.uint32).view(np.float32)])
+    a, b = np.ascontiguousarray(a, np.float32), np.ascontiguousarray(b, np.float32)
+    got, want = np.empty_like(a), np.empty_like(a)
+    pt._check(pt._lib().ptb_selftest_fdiv(pl.scene._h, a.ctypes.data, b.ctypes.data, got.ctypes.data, want.ctypes.data, a.size))
+    nan = np.isnan(want)
+    assert np.array_equal(np.isnan(got), nan)
+    assert np.array_equal(got[~nan].view(np.uint32), want[~nan].view(np.uint32))
+    with np.errstate(all="ignore"):
+        host = a / b                       # the host agrees with the device on everything but NaN payloads
+    assert np.array_equal(host[~nan].view(np.uint32), want[~nan].view(np.uint32))
+    pl.scene.destroy()
+
+
 def _mean_radiance(scene, w, h, depth, frames, **estimator):
     a = rr.IntersectionApi.Create(0)
     try:
