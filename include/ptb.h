@@ -21,6 +21,9 @@
  *   "RadianceBufferCL"             float4[P]                RTPathTracingPass.cpp:106 / RTBDPTPass.cpp:120
  *   "NextFrameImageCL"             float4[P] (was a GL-interop image2d_t, RTReconstructionPass.cpp:67)
  *   "WeightedRadianceBuffer", "FilterWeightsBuffer"  float4[P], float[P]  RTReconstructionPass.cpp:212-213
+ *   "AccumulationBuffer"           the two above as the one allocation they are: float[4P] || float[P]
+ *   "BDPTSampledLightBuffer"       BDPT state that persists across frames (exists after the first BDPT frame)
+ *   "PathTraceBuffer"              diagnostic, see ptb_set_path_trace
  */
 #ifndef PTB_H
 #define PTB_H
@@ -112,6 +115,9 @@ int ptb_pt_shadow_resolve(ptb_context* ctx, int bounce);                        
 int ptb_pt_render_sample(ptb_context* ctx, int frame, int max_depth);
 /* Same for RTBDPTPass::update. */
 int ptb_bdpt_render_sample(ptb_context* ctx, int frame, int max_depth);
+/* RTBDPTPass::createBuffers (RTBDPTPass.cpp:451-478) alone: allocates the zero-filled BDPT buffers for `max_depth`
+ * (ptb_bdpt_render_sample does it on first use), so that a checkpoint can be restored before the first frame. */
+int ptb_bdpt_reserve(ptb_context* ctx, int max_depth);
 /* How ptb_pt_render_sample issues a frame: 2 (default) = the pixel set is split in two halves whose wavefronts run
  * on two streams, so that each kernel's drain-out tail is filled by the other half's kernels;
  * 1 = one wavefront on the context's stream.  Per-sample results are identical. */
@@ -140,6 +146,14 @@ int ptb_set_frames_in_flight(ptb_context* ctx, int depth);
 #define PTB_EST_NEE_MIS 2
 int ptb_set_estimator(ptb_context* ctx, int flags);
 int ptb_set_coherence(ptb_context* ctx, int mode);
+
+/* Diagnostic record of ptb_pt_render_sample (no reference counterpart; parity evidence only).  With max_depth > 0 a
+ * buffer "PathTraceBuffer" of int4[max_depth][P] is kept: entry [bounce * P + pixel] = {shape id, prim id, flags,
+ * shadow ray occluded} of the vertex the pixel's path shaded at that bounce in the frame rendered last (all zero
+ * = the path was not alive).  flags: bit 0 a hit was shaded, bit 1 a shadow ray was traced, bit 2 the path ended
+ * on an emitter, bit 3 a next ray was spawned, bits 8.. the sampled BSDF flags (bxdfs.cl BSDF_*).  While it is on,
+ * frames are rendered one at a time.  0 switches it off and frees the buffer; ptb_resize drops it. */
+int ptb_set_path_trace(ptb_context* ctx, int max_depth);
 
 /* Per-kernel device timing of the fused wavefront (no reference counterpart; measurement only).
  * While enabled, CUDA events are recorded on the context's stream around every traversal and shade launch;
@@ -172,7 +186,33 @@ int ptb_tonemap(ptb_context* ctx, const char* src_name, float lwhite);
  * shortcut for zero numerators, pt_math.cuh:fdiv -- and the plain hardware division, element-wise over host arrays. */
 int ptb_selftest_fdiv(ptb_context* ctx, const float* a, const float* b, float* out_shortcut, float* out_plain, int n);
 
+/* ---- multi-GPU merge (no reference counterpart: the reference is single-device).  One process per GPU,
+ * scene and BVH replicated, every rank renders its share of the samples (ptb_set_partition for image tiles, or
+ * different frame indices for a sample-index split) into its own accumulation buffers; the ONE collective of the
+ * path sums  sum(w L) (float4[P]) || sum(w) (float[P])  -- a single 20 B/pixel allocation, "AccumulationBuffer" --
+ * over the ranks with NCCL (NVLink / NVSwitch) on the context's stream, and the division of ReconstructionPass
+ * (reconstruction.cl:50-58) follows in one kernel:
+ *   root >= 0  ncclReduce to `root`, in place.  The root's buffers then hold the sums over all ranks and all frames
+ *              so far and "NextFrameImageCL" on the root is the merged image; every other rank's buffers are zeroed
+ *              (its samples have been handed over), so rendering simply goes on and the next merge adds the new
+ *              samples.  Call it every frame for a progressive display or once at the end of a batch.
+ *   root < 0   ncclAllReduce into a side buffer; every rank gets the merged image, rank-local sums are kept.
+ * `nccl_comm` is an ncclComm_t whose ranks all make this call (NULL = single rank: only the division runs).  Under
+ * a sample-index split only the rank that renders frame 0 restarts its sums by itself (ptb_accumulate); a host that
+ * restarts the image calls ptb_reset_accumulation on every rank.
+ * The ptb_nccl_* helpers wrap ncclGetUniqueId / ncclCommInitRank / ncclCommDestroy for hosts that do not link
+ * NCCL themselves: rank 0 makes the id, the host's launcher carries its 128 bytes to the other ranks. */
+#define PTB_NCCL_UNIQUE_ID_BYTES 128
+int ptb_nccl_unique_id(void* id_out);
+int ptb_nccl_comm_create(ptb_context* ctx, const void* id_in, int rank, int num_ranks, void** nccl_comm_out);
+int ptb_nccl_comm_destroy(void* nccl_comm);
+int ptb_merge_accumulation(ptb_context* ctx, void* nccl_comm, int root);
+
 int ptb_get_buffer(ptb_context* ctx, const char* name, void** device_ptr, size_t* bytes);
+/* Blocking host->device write of a whole named buffer: restores a checkpoint of the accumulation state
+ * ("AccumulationBuffer" = sum(w L) || sum(w), RTReconstructionPass.cpp:212-213; for BDPT also "BDPTSampledLightBuffer",
+ * whose records are read before they are rewritten) so that a render resumes bit for bit. */
+int ptb_write_buffer(ptb_context* ctx, const char* name, const void* host_src, size_t bytes);
 /* Blocking device->host read of a named buffer (the step's result for the end-to-end leg). */
 int ptb_read_buffer(ptb_context* ctx, const char* name, void* host_dst, size_t bytes);
 /* Pipelined read-back for a consumer that wants the image every frame (the role of RTDisplayPass): snapshots the

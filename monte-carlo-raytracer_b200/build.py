@@ -37,6 +37,19 @@ NVCC_FLAGS = [
 ] + os.environ.get("MCRT_NVCC_DEFS", "").replace(",", " ").split()
 
 
+def _nccl():
+    """(include dir, lib dir) of NCCL: the copy PyTorch ships (the one a torch.distributed process has already
+    loaded), else the system's.  The library is linked by soname with an rpath, so whichever process loads
+    libmcrt_b200.so first -- torch or a plain ctypes host -- resolves to the same libnccl.so.2."""
+    import importlib.util
+    spec = importlib.util.find_spec("nvidia.nccl")
+    if spec and spec.submodule_search_locations:
+        base = list(spec.submodule_search_locations)[0]
+        if os.path.exists(os.path.join(base, "lib", "libnccl.so.2")):
+            return os.path.join(base, "include"), os.path.join(base, "lib")
+    return "/usr/include", "/usr/lib/x86_64-linux-gnu"
+
+
 def _nvcc():
     return shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 
@@ -75,7 +88,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     objs, procs = [], []
     for src in _sources():
         obj = os.path.join(build_dir, os.path.basename(src) + ".o")
-        cmd = [_nvcc()] + NVCC_FLAGS + ["-I", INCLUDE, "-I", CSRC, "-c", src, "-o", obj]
+        cmd = [_nvcc()] + NVCC_FLAGS + ["-I", INCLUDE, "-I", CSRC, "-I", _nccl()[0], "-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     log = []
@@ -90,7 +103,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
         print("\n".join(log))
     if failed:
         raise RuntimeError("nvcc failed; see %s" % os.path.join(build_dir, "build.log"))
-    link = [_nvcc(), "-shared", "-o", LIB_PATH] + objs + ["-lcudart", "-lpthread"]
+    nccl_lib = _nccl()[1]
+    link = [_nvcc(), "-shared", "-o", LIB_PATH] + objs + ["-lcudart", "-lpthread", "-L" + nccl_lib, "-l:libnccl.so.2",
+                                                           "-Xlinker", "-rpath=" + nccl_lib]
     subprocess.check_call(link)
     with open(STAMP_PATH, "w") as f:
         f.write(_fingerprint())

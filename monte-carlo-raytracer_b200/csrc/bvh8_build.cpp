@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <climits>
 #include <cmath>
 #include <cstring>
 #include <future>
@@ -62,6 +63,10 @@ struct Builder {
     std::atomic<int> next_node{0};
     std::atomic<int> live_threads{1};
     int max_threads = 1;
+    // Binary depth from which splits are forced to equal counts (balanced, so the remaining subtree collapses three
+    // binary levels per wide level).  INT_MAX = SAH everywhere; build_bvh8 lowers it only for a tree whose wide
+    // depth would overflow the traversal stack (kMaxWideLevels).
+    int sah_depth_cap = std::numeric_limits<int>::max();
 
     explicit Builder(const BuildOptions& o) : opt(o) {}
 
@@ -86,7 +91,14 @@ struct Builder {
         int best_axis = -1, best_bin = -1;
         float best_cost = std::numeric_limits<float>::infinity();
         const int NB = std::max(4, std::min(opt.num_bins, 64));
-        if (opt.use_sah) {
+        const bool forced = depth >= sah_depth_cap;
+        if (forced) {
+            if (count <= 3) {
+                n.first = first;
+                n.count = count;
+                return;
+            }
+        } else if (opt.use_sah) {
             for (int axis = 0; axis < 3; ++axis) {
                 float cmin = cb.lo[axis], cext = cb.hi[axis] - cb.lo[axis];
                 if (!(cext > 0.f)) continue;
@@ -145,7 +157,17 @@ struct Builder {
         }
 
         int mid;
-        if (best_axis >= 0) {
+        if (forced) {
+            int axis = 0;
+            float ext[3] = {cb.hi[0] - cb.lo[0], cb.hi[1] - cb.lo[1], cb.hi[2] - cb.lo[2]};
+            if (ext[1] > ext[axis]) axis = 1;
+            if (ext[2] > ext[axis]) axis = 2;
+            int* beg = prim.data() + first;
+            mid = count / 2;
+            std::nth_element(beg, beg + mid, beg + count, [&](int a, int b) {
+                return pcent[3 * (size_t)a + axis] < pcent[3 * (size_t)b + axis];
+            });
+        } else if (best_axis >= 0) {
             float cmin = cb.lo[best_axis], cext = cb.hi[best_axis] - cb.lo[best_axis];
             float scale = (float)NB / cext;
             int* beg = prim.data() + first;
@@ -242,6 +264,8 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
                 o[4 * k + 0] = transform_coord(m.m + 0, v[0], v[1], v[2]);
                 o[4 * k + 1] = transform_coord(m.m + 4, v[0], v[1], v[2]);
                 o[4 * k + 2] = transform_coord(m.m + 8, v[0], v[1], v[2]);
+                if (!std::isfinite(o[4 * k + 0]) || !std::isfinite(o[4 * k + 1]) || !std::isfinite(o[4 * k + 2]))
+                    throw std::runtime_error("non-finite vertex position");
                 b.grow(o + 4 * k);
             }
             int sid = m.shape_id, pid = f, zero = 0;
@@ -255,8 +279,19 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
         }
     }
 
+    // The traversal keeps at most two stack entries per wide level (a node group and a postponed triangle group) on a
+    // 40-entry stack (traverse.cuh), so a tree may have at most kMaxWideLevels levels -- the bound the device builder
+    // enforces too (lbvh_build.h).  A SAH tree over strongly non-uniform input can be deeper: it is then rebuilt with
+    // equal-count splits below a binary depth that is lowered until the wide tree fits (0 = balanced everywhere, which
+    // always fits: ceil(log2(2^30 / 2) / 3) + 1 = 11 levels).
+    enum { kMaxWideLevels = 19 };
+    static const int caps[] = {std::numeric_limits<int>::max(), 40, 24, 12, 0};
+    for (int attempt = 0;; ++attempt) {
+    B.sah_depth_cap = caps[attempt];
+    B.next_node.store(0);
+    for (size_t i = 0; i < N; ++i) B.prim[i] = (int)i;
     // ---- 2. binary build
-    B.nodes.resize(2 * N);
+    B.nodes.assign(2 * N, Node2());
     B.max_threads = opt.num_threads > 0 ? opt.num_threads : (int)std::max(1u, std::thread::hardware_concurrency());
     int root = B.alloc_node();
     B.build_range(root, 0, (int)N, 0);
@@ -336,6 +371,12 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
                         bs = s;
                     }
                 }
+            }
+            if (bi < 0) {      // NaN scores (non-finite boxes): first free child into the first free slot
+                for (int i = 0; i < nch && bi < 0; ++i)
+                    if (slot_of[i] < 0) bi = i;
+                for (int s = 0; s < 8 && bs < 0; ++s)
+                    if (child_in_slot[s] < 0) bs = s;
             }
             slot_of[bi] = bs;
             child_in_slot[bs] = bi;
@@ -423,6 +464,9 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
         out.scene_max[a] = n2[(size_t)root].box.hi[a];
     }
     if (out.num_tris != (int64_t)N) throw std::runtime_error("internal error: triangle count mismatch");
+    if ((int)out.level_offsets.size() - 1 <= kMaxWideLevels) break;
+    if (caps[attempt] == 0) throw std::runtime_error("internal error: balanced tree deeper than the traversal stack");
+    }
 }
 
 }  // namespace mcrt

@@ -153,9 +153,10 @@ __device__ __forceinline__ void fetch_shadow_ray(const PtState& s, unsigned idx,
     r.dx = d.x; r.dy = d.y; r.dz = d.z;
     r.mask = -1;
 }
-__device__ __forceinline__ void resolve_shadow(const PtState& s, unsigned idx, const TravState& st) {
+__device__ __forceinline__ void resolve_shadow(const PtState& s, unsigned idx, const TravState& st, int bounce) {
     const uint32_t px = (uint32_t)__float_as_int(s.sh_d[idx].w);
     const float V = st.best_tri >= 0 ? 0.0f : 1.0f;
+    if (s.path_trace) s.path_trace[(size_t)bounce * ((size_t)s.width * s.height) + px].w = st.best_tri >= 0 ? 1 : 0;
     const float4 L = s.sh_L[idx];
     float4 r = s.radiance[px];
     r.x += L.x * V;
@@ -179,7 +180,7 @@ k_trace_closest(PtState s, int cur) {
 
 // any-hit traversal fused with the reference's ShadowPass; shadow rays of bounce parity `sh`
 __global__ void __launch_bounds__(128, 8)
-k_trace_shadow(PtState s, int sh) {
+k_trace_shadow(PtState s, int sh, int bounce) {
     const unsigned count = s.cnt[5 + sh];
     persistent_trace<true>(
         s.nodes, s.tris, count, s.cnt + 4,
@@ -187,14 +188,14 @@ k_trace_shadow(PtState s, int sh) {
             fetch_shadow_ray(s, idx, r);
             return true;
         },
-        [&](unsigned idx, const Ray&, const TravState& st) { resolve_shadow(s, idx, st); });
+        [&](unsigned idx, const Ray&, const TravState& st) { resolve_shadow(s, idx, st, bounce); });
 }
 
 // One launch for the two ray sets that are ready after a shade stage: the closest-hit rays of the next bounce
 // (queue `cur`) and the shadow rays of the bounce just shaded (parity `sh`).  They are independent of each other, so
 // sharing the persistent warps removes one drain-out tail and one launch per bounce.  Long rays first.
 __global__ void __launch_bounds__(128, 8)
-k_trace_mixed(PtState s, int cur, int sh) {
+k_trace_mixed(PtState s, int cur, int sh, int sh_bounce) {
     const unsigned n_closest = s.cnt[cur], n_shadow = s.cnt[5 + sh];
     const uint32_t* __restrict__ queue = s.queue[cur];
     persistent_trace<false, true>(
@@ -209,7 +210,7 @@ k_trace_mixed(PtState s, int cur, int sh) {
         },
         [&](unsigned idx, const Ray& r, const TravState& st) {
             if (idx < n_closest) store_closest_hit(s, queue, idx, r, st);
-            else resolve_shadow(s, idx - n_closest, st);
+            else resolve_shadow(s, idx - n_closest, st, sh_bounce);
         });
 }
 
@@ -295,6 +296,12 @@ __device__ __forceinline__ void shade_queue(const PtState& s, int cur, int frame
                              !(out.direct.x == 0.0f && out.direct.y == 0.0f && out.direct.z == 0.0f);
                 pushNext = out.continues;
             }
+        }
+        if (s.path_trace && i < count) {
+            const int4 h = s.hit[px];
+            const int flags = (active ? 1 : 0) | (pushShadow ? 2 : 0) | (active && out.hasEmission ? 4 : 0) |
+                              (pushNext ? 8 : 0) | (active ? (out.bsdfFlags << 8) : 0);
+            s.path_trace[(size_t)bounce * ((size_t)s.width * s.height) + px] = make_int4(h.x, h.y, flags, 0);
         }
         const unsigned si = warp_push(pushShadow, s.cnt + 5 + (bounce & 1));
         if (pushShadow) {
@@ -415,7 +422,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                     k_trace_closest<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h]);
                     if (h == 0 && nh == 2 && stagger) cudaEventRecord(overlap->stagger, H.stream);
                 } else {
-                    k_trace_mixed<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1);
+                    k_trace_mixed<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1, b - 1);
                 }
                 if (timer) timer->mark(h, H.stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
                 if (s.estimator)
@@ -431,7 +438,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
             const Half& H = half[h];
             k_sample_end<<<1, 32, 0, H.stream>>>(H.s.cnt, H.s.stats, max_depth - 1);
             if (timer) timer->mark(h, H.stream);
-            k_trace_shadow<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1);
+            k_trace_shadow<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1, max_depth - 1);
             if (timer) timer->mark(h, H.stream, StageTimer::TRACE_SHADOW);
             launches += 2;
         }

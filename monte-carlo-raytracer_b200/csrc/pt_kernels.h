@@ -49,6 +49,12 @@ struct PtState {
     int estimator;        // PT_EST_* flags of the opt-in estimator switches (pt_shade.cuh); 0 = the reference's estimator
     int coherence;        // 0 = queues in push order, 1 = bounces >= 1 bucketed by sampler decisions, 2 = bounce 0 too
     unsigned long long* stats;  // [0] closest rays, [1] shadow rays, [2] shaded vertices, [3] samples
+    // Diagnostic record of the fused wavefront (ptb_set_path_trace; NULL = off): one int4 per (bounce, pixel) at
+    // [bounce * P + pixel] = {shape id, prim id, flags, shadow ray occluded}.  flags: bit 0 the vertex was shaded,
+    // bit 1 a shadow ray was traced for it, bit 2 the path ended on an emitter, bit 3 a next ray was spawned,
+    // bits 8.. the sampled BSDF flags.  The parity tests use it to show WHERE a pixel that leaves the tolerance
+    // diverged from the oracle (tests/parity_util.py).
+    int4* path_trace;
     // reference-layout (AoS) stage buffers
     void* aos_rays;        // RTRay[P]
     void* aos_isect;       // Intersection[P]
@@ -129,6 +135,13 @@ struct FilterProps {
 };
 cudaError_t launch_accumulate(const PtState& s, const FilterProps& f, int frame, const uint32_t* pixels, int n_pixels,
                               cudaStream_t stream);
+
+// the same for a BDPT frame of tile partition `part` of `num_parts`: radiance is accumulated over the whole frame
+// (splats land anywhere), the filter weight only on the pixels the partition owns
+cudaError_t launch_accumulate_splat(const PtState& s, const FilterProps& f, int frame, int part, int num_parts,
+                                    cudaStream_t stream);
+// image = weighted / weights over n pixels (the merge step of the multi-GPU path, ptb_merge_accumulation)
+cudaError_t launch_divide_accumulation(const float4* weighted, const float* weights, float4* image, int n, cudaStream_t stream);
 
 // post-processing (postfx_kernels.cu)
 cudaError_t launch_bilateral_denoise(int width, int height, int radius, float sigmaSpatial, float sigmaRange,

@@ -203,6 +203,52 @@ k_accumulate(PtState s, FilterProps f, int frame, const uint32_t* __restrict__ p
     s.image[px] = make_float4(acc.x / wsum, acc.y / wsum, acc.z / wsum, acc.w / wsum);
 }
 
+// ReconstructionPass for a BDPT frame rendered under the tile partition (ptb_set_partition): the rank's light-tracing
+// (t = 1) strategies splat into pixels of ANY tile (BDPT.cl:888-899), so sum(w L) is taken over the whole frame,
+// while sum(w) counts the sample only on the rank that owns the pixel -- summed over the ranks that gives, per
+// pixel, sum over all ranks' contributions / one weight per sample, which is what a single device accumulates.
+// (The clamp of reconstruction.cl:17-20 applies to each rank's share, a single device clamps their sum: they differ
+// only for a radiance above RT_MAX_ALLOWED_RADIANCE.)
+__global__ void __launch_bounds__(256)
+k_accumulate_splat(PtState s, FilterProps f, int frame, int part, int num_parts) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = s.width * s.height;
+    if (i >= n) return;
+    const int tw = (s.width + 63) / 64;
+    const int tile = ((i / s.width) / 64) * tw + (i % s.width) / 64;
+    const bool own = tile % num_parts == part;
+    float4 r = s.radiance[i];
+    r.x = clampf(r.x, 0.0f, RT_MAX_ALLOWED_RADIANCE);
+    r.y = clampf(r.y, 0.0f, RT_MAX_ALLOWED_RADIANCE);
+    r.z = clampf(r.z, 0.0f, RT_MAX_ALLOWED_RADIANCE);
+    r.w = clampf(r.w, 0.0f, RT_MAX_ALLOWED_RADIANCE);
+    const float w = filter_weight(f);
+    const float wo = own ? w : 0.0f;
+    float4 acc;
+    float wsum;
+    if (frame == 0) {
+        acc = make_float4(r.x * w, r.y * w, r.z * w, r.w * w);
+        wsum = wo;
+    } else {
+        acc = s.weighted_radiance[i];
+        acc.x += r.x * w;
+        acc.y += r.y * w;
+        acc.z += r.z * w;
+        acc.w += r.w * w;
+        wsum = s.filter_weights[i] + wo;
+    }
+    s.weighted_radiance[i] = acc;
+    s.filter_weights[i] = wsum;
+    if (own) s.image[i] = make_float4(acc.x / wsum, acc.y / wsum, acc.z / wsum, acc.w / wsum);   // partial until merged
+}
+cudaError_t launch_accumulate_splat(const PtState& s, const FilterProps& f, int frame, int part, int num_parts,
+                                    cudaStream_t stream) {
+    const int n = s.width * s.height;
+    if (n <= 0) return cudaSuccess;
+    k_accumulate_splat<<<(n + 255) / 256, 256, 0, stream>>>(s, f, frame, part, num_parts);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_generate_primary_rays(const PtState& s, cudaStream_t stream) {
     const int n = s.width * s.height;
     k_generate_rays_aos<<<(n + 255) / 256, 256, 0, stream>>>(s);
@@ -222,6 +268,22 @@ cudaError_t launch_accumulate(const PtState& s, const FilterProps& f, int frame,
                               cudaStream_t stream) {
     if (n_pixels <= 0) return cudaSuccess;
     k_accumulate<<<(n_pixels + 255) / 256, 256, 0, stream>>>(s, f, frame, pixels, n_pixels);
+    return cudaGetLastError();
+}
+
+// The division ReconstructionPass ends with (reconstruction.cl:50-58), alone: after the ranks' accumulation buffers
+// have been summed (ptb_merge_accumulation) the image is sum(w L) / sum(w) over the whole frame.
+__global__ void __launch_bounds__(256)
+k_divide_accumulation(const float4* __restrict__ weighted, const float* __restrict__ weights, float4* __restrict__ image, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 acc = weighted[i];
+    const float wsum = weights[i];
+    image[i] = make_float4(acc.x / wsum, acc.y / wsum, acc.z / wsum, acc.w / wsum);
+}
+cudaError_t launch_divide_accumulation(const float4* weighted, const float* weights, float4* image, int n, cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    k_divide_accumulation<<<(n + 255) / 256, 256, 0, stream>>>(weighted, weights, image, n);
     return cudaGetLastError();
 }
 

@@ -5,6 +5,7 @@
 // RTBufferManager (system/RTBufferManager.h:59-71) and of the kernel-launch halves of
 // RTPrimaryRaysPass / RTPathTracingPass / RTReconstructionPass.  No CPU fallback.
 #include <cuda_runtime.h>
+#include <nccl.h>
 
 #include <algorithm>
 #include <cstdlib>
@@ -53,6 +54,9 @@ struct ptb_context {
     uint32_t* d_pixels = nullptr;                 // partition pixel list (NULL = identity)
     int n_pixels = 0;
     int bdpt_depth = -1;
+    bool last_frame_bdpt = false;                 // the frame in "RadianceBufferCL" came from ptb_bdpt_render_sample
+    float* merged = nullptr;                      // ptb_merge_accumulation(root < 0): all-reduce result, 20 B/pixel, lazy
+    int path_trace_depth = 0;                     // ptb_set_path_trace: bounces recorded (0 = off)
     int64_t launches = 0;
     float4* denoised = nullptr;                   // RTDenoisePass / RTToneMappingPass outputs
     float4* tonemapped = nullptr;
@@ -178,7 +182,7 @@ int ready(ptb_context* c) {
 }
 
 // ---- frames in flight
-bool pipelined(const ptb_context* c) { return c->slots.size() > 1 && !c->profiling; }
+bool pipelined(const ptb_context* c) { return c->slots.size() > 1 && !c->profiling && !c->st.path_trace; }
 
 // the context's stream waits (on the device) for every frame rendered on a side stream
 int join_frames(ptb_context* c) {
@@ -516,6 +520,10 @@ int ptb_resize(ptb_context* c, int width, int height) {
     const int frames_in_flight = (int)c->slots.size();
     destroy_slots(c);
     free_map(c->pixel_bufs);
+    c->st.path_trace = nullptr;
+    c->path_trace_depth = 0;
+    c->named.erase("PathTraceBuffer");
+    c->named.erase("BDPTSampledLightBuffer");
     c->bdpt_depth = -1;
     std::memset(&c->bd, 0, sizeof(c->bd));
     c->width = width;
@@ -549,8 +557,6 @@ int ptb_resize(ptb_context* c, int width, int height) {
         {"aos_occlusion", 4, (void**)&s.aos_occlusion, "ShadowRayOcclusionBuffer"},
         {"aos_temp_radiance", 16, (void**)&s.aos_temp_radiance, "TempRadianceBuffer"},
         {"aos_throughput", 32, &s.aos_throughput, "ThroughputBuffer"},
-        {"weighted_radiance", 16, (void**)&s.weighted_radiance, "WeightedRadianceBuffer"},
-        {"filter_weights", 4, (void**)&s.filter_weights, "FilterWeightsBuffer"},
         {"image", 16, (void**)&s.image, "NextFrameImageCL"},
         {"denoised", 16, (void**)&c->denoised, "DenoisedImageCL"},
         {"tonemapped", 16, (void**)&c->tonemapped, "TonemappedImageCL"},
@@ -566,6 +572,25 @@ int ptb_resize(ptb_context* c, int width, int height) {
             v.bytes = P * sp.elem;
             c->named[sp.public_name] = v;
         }
+    }
+    {
+        // sum(w L) (float4[P]) and sum(w) (float[P]) are ONE 20 B/pixel allocation: the multi-GPU merge reduces it
+        // with a single NCCL call and no staging copy (ptb_merge_accumulation)
+        void* p = nullptr;
+        if ((rc = alloc_into(c->pixel_bufs, "accumulation", P * 20, true, c->stream, &p))) return rc;
+        s.weighted_radiance = (float4*)p;
+        s.filter_weights = (float*)((char*)p + P * 16);
+        DevBuf v;
+        v.p = p;
+        v.bytes = P * 16;
+        c->named["WeightedRadianceBuffer"] = v;
+        v.p = s.filter_weights;
+        v.bytes = P * 4;
+        c->named["FilterWeightsBuffer"] = v;
+        v.p = p;
+        v.bytes = P * 20;
+        c->named["AccumulationBuffer"] = v;
+        c->merged = nullptr;
     }
     rc = build_partition(c);
     if (rc) return rc;
@@ -660,6 +685,7 @@ int ptb_pt_shadow_resolve(ptb_context* c, int bounce) {
 int ptb_pt_render_sample(ptb_context* c, int frame, int max_depth) {
     int rc = ready(c);
     if (rc) return rc;
+    c->last_frame_bdpt = false;
     if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
     cudaError_t e = cudaSuccess;
     if (pipelined(c)) {
@@ -685,9 +711,41 @@ int ptb_pt_render_sample(ptb_context* c, int frame, int max_depth) {
         return 0;
     }
     if ((rc = join_and_drop_frames(c))) return rc;
+    if (c->st.path_trace) {
+        if (max_depth > c->path_trace_depth) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth exceeds the depth given to ptb_set_path_trace");
+        PTB_CUDA(cudaMemsetAsync(c->st.path_trace, 0, (size_t)c->path_trace_depth * c->width * c->height * sizeof(int4), c->stream));
+    }
     c->launches += mcrt::launch_pt_sample(c->st, c->d_pixels, c->n_pixels, frame, max_depth, c->stream, &e,
                                           c->profiling ? &c->timer : nullptr, c->halves == 2 ? &c->overlap : nullptr);
     if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("path tracer launch: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+int ptb_set_path_trace(ptb_context* c, int max_depth) {
+    if (!c || max_depth < 0 || max_depth > 64) return pfail(RRB_ERROR_INVALID_ARGUMENT, "path trace depth must be 0 .. 64");
+    if (c->width <= 0) return pfail(RRB_ERROR_INVALID_ARGUMENT, "ptb_resize has not been called");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    auto it = c->pixel_bufs.find("path_trace");
+    if (it != c->pixel_bufs.end()) {
+        if (it->second.p) cudaFree(it->second.p);
+        c->pixel_bufs.erase(it);
+    }
+    c->named.erase("PathTraceBuffer");
+    c->st.path_trace = nullptr;
+    c->path_trace_depth = 0;
+    if (max_depth == 0) return 0;
+    void* p = nullptr;
+    const size_t bytes = (size_t)max_depth * c->width * c->height * sizeof(int4);
+    if ((rc = alloc_into(c->pixel_bufs, "path_trace", bytes, true, c->stream, &p))) return rc;
+    c->st.path_trace = (int4*)p;
+    c->path_trace_depth = max_depth;
+    DevBuf v;
+    v.p = p;
+    v.bytes = bytes;
+    c->named["PathTraceBuffer"] = v;
     return 0;
 }
 
@@ -727,33 +785,45 @@ int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
     return 0;
 }
 
-int ptb_bdpt_render_sample(ptb_context* c, int frame, int max_depth) {
+int ptb_bdpt_reserve(ptb_context* c, int max_depth) {
     int rc = ready(c);
     if (rc) return rc;
     if ((rc = join_and_drop_frames(c))) return rc;
     if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
-    if (c->bdpt_depth != max_depth) {
-        // RTBDPTPass::createBuffers (RTBDPTPass.cpp:451-478): sized by maxDepth, zero-filled (E12)
-        PTB_CUDA(cudaStreamSynchronize(c->stream));
-        for (const char* k : mcrt::bdpt_buffer_names()) {
-            auto it = c->pixel_bufs.find(k);
-            if (it != c->pixel_bufs.end()) {
-                if (it->second.p) cudaFree(it->second.p);
-                c->pixel_bufs.erase(it);
-            }
+    if (c->bdpt_depth == max_depth) return 0;
+    // RTBDPTPass::createBuffers (RTBDPTPass.cpp:451-478): sized by maxDepth, zero-filled (E12)
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    for (const char* k : mcrt::bdpt_buffer_names()) {
+        auto it = c->pixel_bufs.find(k);
+        if (it != c->pixel_bufs.end()) {
+            if (it->second.p) cudaFree(it->second.p);
+            c->pixel_bufs.erase(it);
         }
-        const size_t P = (size_t)c->width * c->height;
-        for (const mcrt::BdptBufferSpec& sp : mcrt::bdpt_buffer_specs(c->bd, max_depth)) {
-            void* p = nullptr;
-            const size_t bytes = sp.bytes_per_pixel ? P * sp.bytes_per_pixel : 64;
-            if ((rc = alloc_into(c->pixel_bufs, sp.name, bytes, true, c->stream, &p))) return rc;
-            *sp.dst = p;
-        }
-        c->bdpt_depth = max_depth;
     }
+    const size_t P = (size_t)c->width * c->height;
+    for (const mcrt::BdptBufferSpec& sp : mcrt::bdpt_buffer_specs(c->bd, max_depth)) {
+        void* p = nullptr;
+        const size_t bytes = sp.bytes_per_pixel ? P * sp.bytes_per_pixel : 64;
+        if ((rc = alloc_into(c->pixel_bufs, sp.name, bytes, true, c->stream, &p))) return rc;
+        *sp.dst = p;
+        if (std::string(sp.name) == "bdpt_sampled_light") {     // the one BDPT buffer whose old contents are read (E12)
+            DevBuf v;
+            v.p = p;
+            v.bytes = bytes;
+            c->named["BDPTSampledLightBuffer"] = v;
+        }
+    }
+    c->bdpt_depth = max_depth;
+    return 0;
+}
+
+int ptb_bdpt_render_sample(ptb_context* c, int frame, int max_depth) {
+    int rc = ptb_bdpt_reserve(c, max_depth);
+    if (rc) return rc;
     cudaError_t e = cudaSuccess;
     c->launches += mcrt::launch_bdpt_sample(c->st, c->bd, c->d_pixels, c->n_pixels, frame, max_depth, c->stream, &e);
     if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("bdpt launch: ") + cudaGetErrorString(e));
+    c->last_frame_bdpt = true;
     return 0;
 }
 
@@ -782,6 +852,8 @@ int ptb_accumulate(ptb_context* c, int frame, const ptb_filter_props* f) {
         PTB_CUDA(mcrt::launch_accumulate(slot_state(c, k), fp, frame, c->d_pixels, c->n_pixels, c->stream));
         PTB_CUDA(cudaEventRecord(s.slot_free, c->stream));
         s.free_recorded = true;
+    } else if (c->last_frame_bdpt && c->num_parts > 1) {
+        PTB_CUDA(mcrt::launch_accumulate_splat(c->st, fp, frame, c->part, c->num_parts, c->stream));
     } else {
         PTB_CUDA(mcrt::launch_accumulate(c->st, fp, frame, c->d_pixels, c->n_pixels, c->stream));
     }
@@ -832,8 +904,7 @@ int ptb_reset_accumulation(ptb_context* c) {
     if (rc) return rc;
     if ((rc = join_frames(c))) return rc;
     const size_t P = (size_t)c->width * c->height;
-    PTB_CUDA(cudaMemsetAsync(c->st.weighted_radiance, 0, P * 16, c->stream));
-    PTB_CUDA(cudaMemsetAsync(c->st.filter_weights, 0, P * 4, c->stream));
+    PTB_CUDA(cudaMemsetAsync(c->st.weighted_radiance, 0, P * 20, c->stream));    // sum(w L) and sum(w): one allocation
     PTB_CUDA(cudaMemsetAsync(c->st.image, 0, P * 16, c->stream));
     return 0;
 }
@@ -856,6 +927,19 @@ int ptb_read_buffer(ptb_context* c, const char* name, void* host_dst, size_t byt
     if ((rc = set_dev(c))) return rc;
     if ((rc = join_frames(c))) return rc;
     PTB_CUDA(cudaMemcpyAsync(host_dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int ptb_write_buffer(ptb_context* c, const char* name, const void* host_src, size_t bytes) {
+    void* p = nullptr;
+    size_t n = 0;
+    int rc = ptb_get_buffer(c, name, &p, &n);
+    if (rc) return rc;
+    if (!host_src || bytes != n) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad source or size (a named buffer is written whole)");
+    if ((rc = set_dev(c))) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
+    PTB_CUDA(cudaMemcpyAsync(p, host_src, bytes, cudaMemcpyHostToDevice, c->stream));
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -962,6 +1046,90 @@ int ptb_reset_counters(ptb_context* c) {
     if ((rc = join_frames(c))) return rc;
     PTB_CUDA(cudaMemsetAsync(c->st.stats, 0, 64, c->stream));
     c->launches = 0;
+    return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// multi-GPU merge: the one collective of the path -- NCCL over NVLink / NVSwitch
+// ------------------------------------------------------------------------------------------------
+static_assert(sizeof(ncclUniqueId) == PTB_NCCL_UNIQUE_ID_BYTES, "ncclUniqueId size");
+#define PTB_NCCL(call)                                                                                  \
+    do {                                                                                                \
+        ncclResult_t r__ = (call);                                                                      \
+        if (r__ != ncclSuccess) return pfail(RRB_ERROR_CUDA, std::string(#call) + ": " + ncclGetErrorString(r__)); \
+    } while (0)
+
+extern "C" {
+
+int ptb_nccl_unique_id(void* id_out) {
+    if (!id_out) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null argument");
+    ncclUniqueId id;
+    PTB_NCCL(ncclGetUniqueId(&id));
+    std::memcpy(id_out, &id, sizeof(id));
+    return 0;
+}
+
+int ptb_nccl_comm_create(ptb_context* c, const void* id_in, int rank, int num_ranks, void** comm_out) {
+    if (!c || !id_in || !comm_out || num_ranks < 1 || rank < 0 || rank >= num_ranks)
+        return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad communicator arguments");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    ncclUniqueId id;
+    std::memcpy(&id, id_in, sizeof(id));
+    ncclComm_t comm = nullptr;
+    PTB_NCCL(ncclCommInitRank(&comm, num_ranks, id, rank));
+    *comm_out = comm;
+    return 0;
+}
+
+int ptb_nccl_comm_destroy(void* comm) {
+    if (!comm) return 0;
+    PTB_NCCL(ncclCommDestroy((ncclComm_t)comm));
+    return 0;
+}
+
+int ptb_merge_accumulation(ptb_context* c, void* nccl_comm, int root) {
+    int rc = ready(c);
+    if (rc) return rc;
+    if ((rc = join_frames(c))) return rc;
+    const size_t P = (size_t)c->width * c->height;
+    float* acc = (float*)c->st.weighted_radiance;      // [4P | P], one allocation (ptb_resize)
+    int rank = 0, nranks = 1;
+    ncclComm_t comm = (ncclComm_t)nccl_comm;
+    if (comm) {
+        PTB_NCCL(ncclCommUserRank(comm, &rank));
+        PTB_NCCL(ncclCommCount(comm, &nranks));
+        if (root >= nranks) return pfail(RRB_ERROR_INVALID_ARGUMENT, "root is not a rank of the communicator");
+    } else if (root > 0) {
+        return pfail(RRB_ERROR_INVALID_ARGUMENT, "root > 0 needs a communicator");
+    }
+    if (root < 0) {
+        // every rank gets the merged image; the rank-local sums stay as they are and keep accumulating
+        const float* src = acc;
+        if (comm && nranks > 1) {
+            if (!c->merged) {
+                void* p = nullptr;
+                if ((rc = alloc_into(c->pixel_bufs, "merged_accumulation", P * 20, true, c->stream, &p))) return rc;
+                c->merged = (float*)p;
+            }
+            PTB_NCCL(ncclAllReduce(acc, c->merged, 5 * P, ncclFloat32, ncclSum, comm, c->stream));
+            src = c->merged;
+        }
+        PTB_CUDA(mcrt::launch_divide_accumulation((const float4*)src, src + 4 * P, c->st.image, (int)P, c->stream));
+        c->launches += 1;
+        return 0;
+    }
+    // root >= 0: the ranks HAND their sums to the root (in place there), and start again from zero; the root's
+    // buffers then hold the sums over every rank and every frame so far
+    if (comm && nranks > 1) PTB_NCCL(ncclReduce(acc, acc, 5 * P, ncclFloat32, ncclSum, root, comm, c->stream));
+    if (rank == root) {
+        PTB_CUDA(mcrt::launch_divide_accumulation(c->st.weighted_radiance, c->st.filter_weights, c->st.image, (int)P, c->stream));
+        c->launches += 1;
+    } else {
+        PTB_CUDA(cudaMemsetAsync(acc, 0, P * 20, c->stream));
+    }
     return 0;
 }
 

@@ -21,7 +21,8 @@ __global__ void __launch_bounds__(128, 8)
 query_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const ApiRay* __restrict__ rays,
              const int* __restrict__ numrays_ptr, int numrays_max, void* __restrict__ out,
              unsigned int* __restrict__ work_counter, int* __restrict__ counts) {
-    const int numrays = numrays_ptr ? min(*numrays_ptr, numrays_max) : numrays_max;
+    // a negative device-side count means no rays, as the reference's `index < *num_rays` does
+    const int numrays = numrays_ptr ? max(0, min(*numrays_ptr, numrays_max)) : numrays_max;
     const unsigned lane = threadIdx.x & 31u;
     Traverser<ANY_HIT, COUNT> trav{nodes, tris};
     uint2 stack[MCRT_STACK_SIZE];
