@@ -9,7 +9,8 @@ directional + area light, regular PT 1920x1080, depth 5), one step = one sample 
 Own arm, per rank: the scene is resident in HBM; a step is raygen -> (closest-hit trace -> shade/NEE
 -> shadow trace + radiance add) x depth -> accumulation, launched through the C ABI (include/ptb.h).
 N > 1 partitions by SAMPLE INDEX (rank r renders sample step*N + r of every pixel; weak scaling) and
-merges with one NCCL all-reduce of the float4 accumulation buffers per step.
+merges with one NCCL reduce of the float4 accumulation buffers to rank 0 per step, behind the C ABI
+(ptb_merge_accumulation).
 `value` is timed with CUDA events on the launching stream (max over ranks); `e2e` drives the same
 frame through the RenderPipeline mirror (camera built and uploaded on the host every step) and reads
 the merged image back into pinned host memory every step.
@@ -63,7 +64,7 @@ def parse_args():
 def config_of(args, n_gpus):
     return {"workload": WORKLOAD, "triangles": 262144, "width": args.width, "height": args.height,
             "max_depth": args.depth, "spp_per_step": 1, "textures": "74 x %d^2 RGBA8" % args.tex,
-            "lights": "point+directional+area", "partition": "sample-index x%d, 1 all-reduce/step (overlapped with the next step)" % n_gpus if n_gpus > 1 else "none",
+            "lights": "point+directional+area", "partition": "sample-index x%d, 1 ncclReduce to rank 0 per step (ptb_merge_accumulation)" % n_gpus if n_gpus > 1 else "none",
             "frames_in_flight": args.frames_in_flight,
             "l2": "no flush: per-step working set (pixel state + textures) exceeds the 126 MB L2"}
 
@@ -128,8 +129,9 @@ def host_threads():
 
 
 def cpu_sample_size(args):
-    """Bounded sample: every third pixel of the 1080p frame in x and y (same camera, scene, depth)."""
-    return max(16, args.width // 3), max(9, args.height // 3)
+    """The host arm renders the frame `config` states, whole (r01 sub-sampled it 3 x 3; a ninth of the pixels is
+    friendlier to the CPU's caches than the workload the line names)."""
+    return args.width, args.height
 
 
 class HostReference:
@@ -145,6 +147,8 @@ class HostReference:
         self.scene, self.depth = scene, args.depth
         self.w, self.h = cpu_sample_size(args)
         self.oracle = ref.RefOracle(self.fast)
+        # every core this process may run on, set explicitly: torchrun exports OMP_NUM_THREADS=1 to its ranks
+        self.threads = self.oracle.set_threads(host_threads())
         t = time.perf_counter()
         self.nodes = self.oracle.build_scene_bvh(scene)
         self.build_s = time.perf_counter() - t
@@ -160,8 +164,9 @@ class HostReference:
         return self.tracer.rays_traced + self.tracer.shadow_rays_traced
 
     def describe(self):
-        return ("%dx%d sub-sampling of the 1080p frame (1/9 of the pixels, same camera/scene/depth), 1 spp per step, "
-                "reference .cl kernels + RR BVH2 compiled %s, OpenMP" % (self.w, self.h, "-O3 AVX2" if self.fast else "-O2 strict fp32"))
+        return ("the whole %dx%d frame, 1 spp per step, reference .cl kernels + RR BVH2 compiled %s, OpenMP on %d threads "
+                "(counted inside a parallel region)" % (self.w, self.h, "-O3 AVX2" if self.fast else "-O2 strict fp32",
+                                                        self.threads))
 
 
 def run_cpu_baseline(scene, args, seconds):
@@ -175,7 +180,7 @@ def run_cpu_baseline(scene, args, seconds):
             break
     dt = time.perf_counter() - t0
     paths = frames * hr.w * hr.h
-    return {"value": paths / dt, "unit": UNIT, "cores": host_threads(), "kind": "reference",
+    return {"value": paths / dt, "unit": UNIT, "cores": hr.threads, "kind": "reference",
             "sample": hr.describe() + ", %d steps in %.1f s" % (frames, dt),
             "mrays_per_s": (hr.rays() - r0) / dt / 1e6, "bvh_build_s": hr.build_s}
 
@@ -184,6 +189,7 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0                                # the host cores are one pool: rank 0 alone measures
+    os.environ["OMP_NUM_THREADS"] = str(host_threads())     # before libgomp loads; ref_set_threads repeats it
     import mcrt_b200  # noqa: F401
     from mcrt_b200 import scene_library
     scene = scene_library.sponza_class(args.tex)
@@ -199,7 +205,7 @@ def reference_arm(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": config_of(args, args.gpus), "mrays_per_s": (hr.rays() - r0) / dt / 1e6,
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": host_threads(), "kind": "reference",
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": hr.threads, "kind": "reference",
                              "sample": hr.describe(), "bvh_build_s": hr.build_s},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -252,14 +258,9 @@ def own_arm(args):
     lib, h = pt._lib(), pl.scene._h
     fprops = pl.GI.filter_props()
 
-    # merged-image plumbing for N > 1: [weighted radiance (4P) | filter weights (P)] staged and all-reduced
-    wr_ptr, wr_bytes = pl.device_buffer("WeightedRadianceBuffer")
-    fw_ptr, fw_bytes = pl.device_buffer("FilterWeightsBuffer")
-    img_ptr, img_bytes = pl.device_buffer("NextFrameImageCL")
-    t_wr = torch.as_tensor(DevView(wr_ptr, wr_bytes), device=dev)
-    t_fw = torch.as_tensor(DevView(fw_ptr, fw_bytes), device=dev)
-    t_img = torch.as_tensor(DevView(img_ptr, img_bytes), device=dev)
-    merger = multi_gpu.PipelinedMerger(P, dev) if world > 1 else None
+    # N > 1: the one collective of the path, behind the C ABI (ptb_merge_accumulation): ncclReduce of the 20 B/pixel
+    # accumulation buffer to rank 0 on the context's stream + the division there; only rank 0 reads the image back
+    comm = multi_gpu.create_comm(pl, rank, world) if world > 1 else None
     host_imgs = [torch.empty(4 * P, dtype=torch.float32, pin_memory=True) for _ in range(2)]   # double-buffered
     host_nps = [t.numpy() for t in host_imgs]
     host_np = host_nps[0]
@@ -269,14 +270,12 @@ def own_arm(args):
         return camera.make_camera(scene.camera, W, H, off), off
 
     def merge():
-        """One NCCL all-reduce of the accumulation buffers per step, pipelined: the collective of this step
-        overlaps the next step's kernels; every rank ends with the merged image (merge_flush after the loop)."""
-        merger.finish(t_img)
-        merger.begin(t_wr, t_fw)
+        """One ncclReduce of the accumulation buffers to rank 0 per step (progressive display).  It runs on the
+        context's stream behind this step's accumulation, while the next frames render on their side streams."""
+        pt._check(lib.ptb_merge_accumulation(h, comm, 0))
 
     def merge_flush():
-        if world > 1:
-            merger.finish(t_img)
+        pass
 
     def device_step(frame, cam, off):
         """C-ABI calls only; the camera struct was built before the timed region."""
@@ -295,7 +294,8 @@ def own_arm(args):
         pl.update()
         if world > 1:
             merge()
-        pl.read_buffer_async("NextFrameImageCL", host_nps[slot & 1])
+        if rank == 0:                   # the merged image exists on the root only
+            pl.read_buffer_async("NextFrameImageCL", host_nps[slot & 1])
 
     def barrier():
         if world > 1:
@@ -444,6 +444,9 @@ def own_arm(args):
                         "acc_type": acc_type, "on_device": int(stats.get("last_build_on_device", 0)) if isinstance(stats, dict) else None,
                         "commit_s": float(stats.get("build_seconds", 0.0)) if isinstance(stats, dict) else None}}
         emit(line)
+    if comm is not None:
+        pl.synchronize()
+        multi_gpu.destroy_comm(comm)
     pl.scene.destroy()
     rr.IntersectionApi.Delete(api)
     if world > 1:

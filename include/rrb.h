@@ -140,7 +140,9 @@ int rrb_get_stream(rrb_api* api, int* cuda_device, void** cuda_stream);
 
 
 /* ---- host-only builder access (no CUDA call; used by the CPU test-suite to validate the tree):
- * builds the compressed 8-wide BVH of one tightly packed triangle soup with per-face shape ids. */
+ * builds the compressed 8-wide BVH of one tightly packed triangle soup with per-face shape ids.
+ * use_sah: bit 0 = binned SAH (else median splits); bit 1 = diagnostic, switches off the depth guard that rebuilds
+ * a tree deeper than the traversal stack allows (19 levels) -- the result must then not be traversed. */
 typedef struct rrb_host_bvh rrb_host_bvh;
 int rrb_host_bvh_build(const float* vertices, int vnum, const int* indices, int numfaces, const int* face_shape_ids,
                        int use_sah, rrb_host_bvh** out);

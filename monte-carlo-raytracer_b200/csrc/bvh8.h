@@ -56,6 +56,7 @@ struct BuildOptions {
     int num_bins = 16;            // bins per axis for the binned SAH sweep
     float traversal_cost = 1.2f;  // relative to one triangle test, for the BVH2 leaf decision
     int num_threads = 0;          // 0 = hardware concurrency
+    bool depth_guard = true;      // rebuild with balanced splits when the tree is deeper than the traversal stack allows
 };
 
 // Builds the compressed wide BVH over all faces of all meshes.  Throws std::runtime_error.

@@ -464,7 +464,7 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
         out.scene_max[a] = n2[(size_t)root].box.hi[a];
     }
     if (out.num_tris != (int64_t)N) throw std::runtime_error("internal error: triangle count mismatch");
-    if ((int)out.level_offsets.size() - 1 <= kMaxWideLevels) break;
+    if ((int)out.level_offsets.size() - 1 <= kMaxWideLevels || !opt.depth_guard) break;
     if (caps[attempt] == 0) throw std::runtime_error("internal error: balanced tree deeper than the traversal stack");
     }
 }

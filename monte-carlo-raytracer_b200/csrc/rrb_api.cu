@@ -871,7 +871,8 @@ int rrb_host_bvh_build(const float* vertices, int vnum, const int* indices, int 
     }
     std::unique_ptr<rrb_host_bvh> h(new rrb_host_bvh());
     mcrt::BuildOptions opt;
-    opt.use_sah = use_sah != 0;
+    opt.use_sah = (use_sah & 1) != 0;
+    opt.depth_guard = (use_sah & 2) == 0;
     try {
         mcrt::build_bvh8(meshes, opt, h->bvh);
     } catch (const std::exception& ex) {

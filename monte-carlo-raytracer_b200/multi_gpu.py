@@ -1,10 +1,15 @@
 """Multi-GPU plumbing of the path tracer: one process per GPU, scene and BVH replicated,
-work split by image tiles (A) or by sample index (B), and ONE collective -- an all-reduce (sum) of the
-accumulation buffers  sum(w*L) (float4[P])  and  sum(w) (float[P]) -- followed by the division
+work split by image tiles (A) or by sample index (B), and ONE collective -- a sum of the accumulation
+buffers  sum(w*L) (float4[P]) || sum(w) (float[P])  over the ranks -- followed by the division
 ReconstructionPass does (reconstruction.cl:50-58).  The reference has no multi-device path; this is
 the whole exchange step.
 
-Works on CUDA tensors over NCCL (bench.py) and on CPU tensors over gloo (tests)."""
+The product path is behind the C ABI: ptb_merge_accumulation (include/ptb.h) issues one ncclReduce /
+ncclAllReduce on the context's stream over the single 20 B/pixel allocation and divides in one kernel;
+create_comm() below only carries the NCCL unique id between the ranks over the launcher's process group.
+merge_accumulation() / PipelinedMerger are the same arithmetic on torch tensors (CPU tensors over gloo in
+the tests; they were bench.py's path in r01).
+"""
 import ctypes
 
 import numpy as np
@@ -84,3 +89,27 @@ class PipelinedMerger:
         torch.div(self.stage[:4 * P].view(P, 4), self.stage[4 * P:].view(P, 1), out=image.view(P, 4))
         self.pending = False
         return image
+
+
+def create_comm(pipeline, rank, world, group=None):
+    """An ncclComm_t for ptb_merge_accumulation: rank 0 makes the NCCL unique id (ptb_nccl_unique_id), the
+    launcher's torch.distributed group carries its 128 bytes to the other ranks, every rank joins on the device
+    of its context (ptb_nccl_comm_create).  Returns a ctypes.c_void_p; free it with destroy_comm()."""
+    import torch.distributed as dist
+    from . import pt
+    lib = pt._lib()
+    buf = (ctypes.c_ubyte * 128)()
+    if rank == 0:
+        pt._check(lib.ptb_nccl_unique_id(buf))
+    box = [bytes(buf)]
+    dist.broadcast_object_list(box, src=0, group=group)
+    ident = (ctypes.c_ubyte * 128).from_buffer_copy(box[0])
+    comm = ctypes.c_void_p()
+    pt._check(lib.ptb_nccl_comm_create(pipeline.scene._h, ident, int(rank), int(world), ctypes.byref(comm)))
+    return comm
+
+
+def destroy_comm(comm):
+    from . import pt
+    if comm:
+        pt._check(pt._lib().ptb_nccl_comm_destroy(comm))

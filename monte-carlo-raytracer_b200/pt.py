@@ -72,6 +72,9 @@ def _lib():
             "ptb_selftest_fdiv": [vp, vp, vp, vp, vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
+            "ptb_set_path_trace": [vp, i], "ptb_write_buffer": [vp, ctypes.c_char_p, vp, sz],
+            "ptb_bdpt_reserve": [vp, i], "ptb_merge_accumulation": [vp, vp, i],
+            "ptb_nccl_unique_id": [vp], "ptb_nccl_comm_create": [vp, vp, i, i, pp], "ptb_nccl_comm_destroy": [vp],
         }
         for name, args in sig.items():
             fn = getattr(lib, name)
@@ -298,6 +301,62 @@ class RenderPipeline:
     def set_estimator(self, russian_roulette=False, nee_mis=False):
         """Opt-in estimator switches (include/ptb.h PTB_EST_*); both off = the reference's estimator."""
         _check(_lib().ptb_set_estimator(self.scene._h, (1 if russian_roulette else 0) | (2 if nee_mis else 0)))
+
+    def write_buffer(self, name, data):
+        """Whole-buffer host -> device write (ptb_write_buffer): checkpoint restore."""
+        data = np.ascontiguousarray(data)
+        _check(_lib().ptb_write_buffer(self.scene._h, name.encode(), _ptr(data), data.nbytes))
+
+    def set_path_trace(self, max_depth):
+        """Diagnostic per-bounce record of the fused wavefront ("PathTraceBuffer", include/ptb.h); 0 = off."""
+        self.ensure_size()
+        _check(_lib().ptb_set_path_trace(self.scene._h, int(max_depth)))
+
+    def path_trace(self, max_depth):
+        """(max_depth, P, 4) int32 records of the frame rendered last."""
+        w, h = self._size
+        return self.read_buffer("PathTraceBuffer", np.int32).reshape(-1, w * h, 4)[:max_depth]
+
+    def merge_accumulation(self, comm=None, root=0):
+        """The one collective of the multi-GPU path (ptb_merge_accumulation): NCCL reduce of the accumulation
+        buffers to `root` (all-reduce when root < 0) + the division, on the context's stream."""
+        _check(_lib().ptb_merge_accumulation(self.scene._h, comm, int(root)))
+
+    # ---- checkpoint / resume of the accumulation state (SURVEY 8f row 4; the reference keeps it only on the device,
+    # RTReconstructionPass.cpp:212-213)
+    def _integrator(self):
+        for p in self.passes:
+            if isinstance(p, (RTPathTracingPass, RTBDPTPass)):
+                return p
+        raise PathTracerError("the pipeline has no integrator pass")
+
+    def save_checkpoint(self, path):
+        """(sum(w L), sum(w), frame index) -- and for BDPT the sampled-light records the next frame reads before
+        it rewrites them (E12) -- as one .npz; a render resumed from it continues bit for bit."""
+        integ = self._integrator()
+        w, h = self._size
+        state = {"width": w, "height": h, "frame_index": integ.m_frameIndex, "max_depth": int(self.GI.maxDepth),
+                 "bdpt": isinstance(integ, RTBDPTPass),
+                 "accumulation": self.read_buffer("AccumulationBuffer"),
+                 "image": self.read_buffer("NextFrameImageCL")}
+        if state["bdpt"] and integ.m_frameIndex > 0:
+            state["bdpt_sampled_light"] = self.read_buffer("BDPTSampledLightBuffer")
+        np.savez(path, **state)
+
+    def load_checkpoint(self, path):
+        z = np.load(path)
+        self.ensure_size()
+        integ = self._integrator()
+        if (int(z["width"]), int(z["height"])) != self._size or bool(z["bdpt"]) != isinstance(integ, RTBDPTPass) \
+                or int(z["max_depth"]) != int(self.GI.maxDepth):
+            raise PathTracerError("checkpoint does not match this pipeline (size, integrator or depth)")
+        self.write_buffer("AccumulationBuffer", z["accumulation"])
+        self.write_buffer("NextFrameImageCL", z["image"])
+        if "bdpt_sampled_light" in z.files:
+            _check(_lib().ptb_bdpt_reserve(self.scene._h, int(self.GI.maxDepth)))
+            self.write_buffer("BDPTSampledLightBuffer", z["bdpt_sampled_light"])
+        integ.m_frameIndex = int(z["frame_index"])
+        self.frameIndex = integ.m_frameIndex
 
     def set_partition(self, part, num_parts):
         _check(_lib().ptb_set_partition(self.scene._h, int(part), int(num_parts)))

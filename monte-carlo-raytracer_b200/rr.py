@@ -362,7 +362,7 @@ def host_bvh(vertices, indices, face_shape_ids=None, use_sah=True, refit_info=Fa
     ix = np.ascontiguousarray(indices, np.int32)
     ids = None if face_shape_ids is None else np.ascontiguousarray(face_shape_ids, np.int32)
     h = ctypes.c_void_p()
-    _check(lib.rrb_host_bvh_build(_np_ptr(v), v.shape[0], _np_ptr(ix), ix.shape[0], _np_ptr(ids), 1 if use_sah else 0,
+    _check(lib.rrb_host_bvh_build(_np_ptr(v), v.shape[0], _np_ptr(ix), ix.shape[0], _np_ptr(ids), int(use_sah),
                                   ctypes.byref(h)))
     try:
         pn, pt = ctypes.c_void_p(), ctypes.c_void_p()

@@ -53,6 +53,8 @@ class RefOracle:
         self.sobol_table = None if sobol_table is None else np.ascontiguousarray(sobol_table, np.uint32)
         self.lib = ctypes.CDLL(lib_path(fast, self.sobol_table is not None))
         lib = self.lib
+        lib.ref_set_threads.argtypes = [ctypes.c_int]
+        lib.ref_get_threads.restype = ctypes.c_int
         lib.ref_rr_world_create.restype = ctypes.c_void_p
         lib.ref_rr_world_destroy.argtypes = [ctypes.c_void_p]
         lib.ref_rr_world_add_mesh.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
@@ -72,6 +74,14 @@ class RefOracle:
                                      ctypes.c_void_p]
         lib.ref_pt_shadow_pass.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+
+    def set_threads(self, n=None):
+        """Run the kernels' OpenMP loops on `n` threads (default: every core this process may use), whatever
+        OMP_NUM_THREADS says; returns the team size a parallel region then really gets."""
+        if n is None:
+            n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        self.lib.ref_set_threads(int(n))
+        return int(self.lib.ref_get_threads())
 
     # ------------------------------------------------------------------ Radeon Rays side
     def build_bvh(self, meshes, use_sah=True, traversal_cost=10.0, num_bins=64):
@@ -153,23 +163,48 @@ class RefPathTracer:
         self.rays_traced = 0
         self.shadow_rays_traced = 0
 
-    def render_sample(self, camera, frame, max_depth, trace=None):
+    def render_sample(self, camera, frame, max_depth, trace=None, pixels=None):
         """One frame = one sample per pixel.  `trace`, if a dict, receives copies of the primary
-        hits and of every bounce's temp radiance (for per-stage parity checks)."""
+        hits, of every bounce's temp radiance (for per-stage parity checks) and the per-bounce path record
+        ("path_trace", the layout of the CUDA side's "PathTraceBuffer").  `pixels`: global indices of the
+        only pixels that carry a path (tile partition); the others stay black."""
         lib, o = self.o.lib, self.o
         desc = o.scene_desc(self.scene, camera)
         lib.ref_pt_generate_rays(_ptr(self.rays), _ptr(self.diffs), _ptr(camera))
+        if pixels is not None:
+            # only these pixels carry a path (a rank's tile partition): every other ray is switched off, which is
+            # what the kernels' `extra.y != 0` tests key on; indices and W*H stay global (E14)
+            keep = np.zeros(self.w * self.h, bool)
+            keep[np.asarray(pixels, np.int64)] = True
+            self.rays["extra"][~keep, 1] = 0
+            self.isect["shapeid"][~keep] = -1
         o.intersect(self.nodes, self.rays, self.isect)
         self.rays_traced += int((self.rays["extra"][:, 1] != 0).sum())
         if trace is not None:
             trace["primary_rays"] = self.rays.copy()
             trace["primary_hits"] = self.isect.copy()
             trace["bounce_radiance"] = []
+        if trace is not None:
+            trace["path_trace"] = np.zeros((max_depth, self.w * self.h, 4), np.int32)
         for b in range(max_depth):
+            if trace is not None:
+                # the record ptb_set_path_trace keeps on the CUDA side (include/ptb.h), from the reference's buffers
+                rec = trace["path_trace"][b]
+                shaded = (self.rays["extra"][:, 1] != 0) & (self.isect["shapeid"] != -1) & (self.isect["primid"] != -1)
+                rec[:, 0] = np.where(shaded, self.isect["shapeid"], 0)
+                rec[:, 1] = np.where(shaded, self.isect["primid"], 0)
             lib.ref_pt_shade(ctypes.byref(desc), self.w, self.h, _ptr(self.shadow_rays), _ptr(self.rays),
                              _ptr(self.isect), frame, max_depth, b, _ptr(self.temp_radiance), _ptr(self.throughput))
+            if trace is not None:
+                emitted = shaded & (self.throughput["ignoreOcclusion"] != 0)
+                shadow = shaded & ~emitted & (self.temp_radiance[:, :3] != 0).any(axis=1)
+                spawned = shaded & ~emitted & (self.rays["extra"][:, 1] != 0) & (b + 1 < max_depth)
+                rec[:, 2] = (shaded * 1 + shadow * 2 + emitted * 4 + spawned * 8 +
+                             np.where(shaded, self.throughput["prevBsdfFlags"] << 8, 0))
             o.occluded(self.nodes, self.shadow_rays, self.occlusion)
             self.shadow_rays_traced += int((self.shadow_rays["extra"][:, 1] != 0).sum())
+            if trace is not None:
+                rec[:, 3] = np.where(shadow, (self.occlusion != -1) | (self.shadow_rays["extra"][:, 1] == 0), 0)
             lib.ref_pt_shadow_pass(_ptr(self.shadow_rays), _ptr(self.occlusion), self.w, self.h, b,
                                    _ptr(self.throughput), _ptr(self.temp_radiance), _ptr(self.radiance))
             if trace is not None:

@@ -27,6 +27,10 @@ typedef struct ref_scene_desc {
     int64_t num_indices, num_vertices, texdata_bytes;
 } ref_scene_desc;
 
+/* OpenMP team size of every kernel loop of this library: set explicitly / counted inside a parallel region */
+void ref_set_threads(int n);
+int ref_get_threads(void);
+
 /* Radeon Rays host builder + kernels */
 void* ref_rr_world_create(void);
 void ref_rr_world_destroy(void* w);

@@ -36,6 +36,22 @@ static void launch2d(int width, int height, Fn fn) {
 
 extern "C" {
 
+// The OpenMP team size is set by the caller, not inherited from the environment: a launcher such as torchrun exports
+// OMP_NUM_THREADS=1 to its children, which would silently turn the CPU baseline into a single-threaded run.
+void ref_set_threads(int n) {
+    if (n > 0) omp_set_num_threads(n);
+}
+// the team size an `omp parallel` region actually gets (counted inside one)
+int ref_get_threads(void) {
+    int n = 0;
+#pragma omp parallel
+    {
+#pragma omp atomic
+        n += 1;
+    }
+    return n;
+}
+
 int ref_pt_struct_sizes(int* out, int n) {
     const int sizes[] = {(int)sizeof(RTShape),      (int)sizeof(RTMaterial),   (int)sizeof(RTLight),
                          (int)sizeof(RTThroughput), (int)sizeof(RTInteraction), (int)sizeof(RTBDPTVertex),

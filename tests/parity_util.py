@@ -1,0 +1,173 @@
+"""Parity helpers shared by the full-size GPU parity tests and tools/parity_report.py.
+
+The bar (BASELINE.json north_star): per-sample radiance within 1e-4 relative of the oracle's with the identical
+per-pixel RNG stream, *documented* exceptions only.  What can differ at all between the CUDA path and the strict
+host build of the reference's kernels (oracle/_ref) is CUDA's libm (sinf / cosf / logf / powf / atanf / tanf are
+within 2 ulp of glibc's, not bit-equal): a sampled direction or a disk-light sample can differ in its last bit.
+That perturbation is harmless (relative radiance error ~1e-6) unless it flips a DISCRETE event later along the path:
+the next ray lands on the other side of a geometric edge (different triangle, or hit / miss), a shadow ray's
+visibility flips at an occluder's edge, or a path's `pdf ~ 0` / `black throughput` termination test flips.  After
+such a flip the two paths are different samples and nothing bounds their difference.
+
+So every pixel outside the tolerance must SHOW such a flip: both sides record, per bounce, the hit ids, whether a
+shadow ray was traced and its visibility, whether the path went on and the sampled lobe flags
+("PathTraceBuffer", include/ptb.h; oracle.ref.RefPathTracer.render_sample(trace=...)), and classify() names the
+first bounce at which the records differ.  A pixel that leaves the tolerance with identical records at every
+bounce is `unexplained` -- a shading bug -- and the tests allow none.
+"""
+import numpy as np
+
+REL_TOL = 1e-4
+
+# flags of a path-trace record (include/ptb.h)
+F_SHADED, F_SHADOW, F_EMITTED, F_SPAWNED = 1, 2, 4, 8
+
+CLASSES = ("closest_hit_flip", "shadow_visibility_flip", "shadow_ray_flip", "termination_flip", "lobe_flip",
+           "emission_flip", "unexplained")
+
+
+def rel_err(a, b):
+    """Per-pixel max-channel relative error with an absolute floor for near-black pixels."""
+    return (np.abs(a - b) / np.maximum(np.abs(b), 1e-3)).max(axis=1)
+
+
+def first_divergence(got_trace, want_trace):
+    """For every pixel: (bounce, class index) of the first discrete difference between the two records, or
+    (-1, index of 'unexplained') when the records agree at every bounce.  Traces are (D, P, 4) int32."""
+    D, P, _ = got_trace.shape
+    bounce = np.full(P, -1, np.int32)
+    cls = np.full(P, CLASSES.index("unexplained"), np.int32)
+    open_ = np.ones(P, bool)
+    for b in range(D):
+        g, w = got_trace[b], want_trace[b]
+        gs, ws = (g[:, 2] & F_SHADED) != 0, (w[:, 2] & F_SHADED) != 0
+        both = gs & ws
+        tests = [
+            ("closest_hit_flip", (gs != ws) | (both & ((g[:, 0] != w[:, 0]) | (g[:, 1] != w[:, 1])))),
+            ("emission_flip", both & (((g[:, 2] ^ w[:, 2]) & F_EMITTED) != 0)),
+            ("shadow_ray_flip", both & (((g[:, 2] ^ w[:, 2]) & F_SHADOW) != 0)),
+            ("shadow_visibility_flip", both & ((g[:, 2] & w[:, 2] & F_SHADOW) != 0) & (g[:, 3] != w[:, 3])),
+            ("termination_flip", both & (((g[:, 2] ^ w[:, 2]) & F_SPAWNED) != 0)),
+            ("lobe_flip", both & ((g[:, 2] & w[:, 2] & F_SPAWNED) != 0) & ((g[:, 2] >> 8) != (w[:, 2] >> 8))),
+        ]
+        for name, m in tests:
+            hit = open_ & m
+            bounce[hit] = b
+            cls[hit] = CLASSES.index(name)
+            open_ &= ~hit
+    return bounce, cls
+
+
+def classify(got, want, got_trace, want_trace, pixels=None, tol=REL_TOL):
+    """Parity report of one frame.  got / want: (P, >=3) radiance; traces (D, P, 4); `pixels`: restrict to these
+    global indices (tile partition).  Returns a dict of plain numbers (JSON-able)."""
+    e = rel_err(got[:, :3], want[:, :3])
+    sel = np.ones(e.shape[0], bool) if pixels is None else np.isin(np.arange(e.shape[0]), pixels)
+    out_tol = sel & ~(e <= tol)              # NaN counts as out of tolerance
+    bounce, cls = first_divergence(got_trace, want_trace)
+    diverged = sel & (bounce >= 0)
+    rep = {
+        "pixels": int(sel.sum()),
+        "within_tol": int((sel & (e <= tol)).sum()),
+        "out_of_tol": int(out_tol.sum()),
+        "frac_within": float((sel & (e <= tol)).sum() / max(int(sel.sum()), 1)),
+        "max_rel_err_of_undiverged": float(e[sel & ~diverged].max()) if (sel & ~diverged).any() else 0.0,
+        "diverged_paths": int(diverged.sum()),          # paths with a discrete flip, inside the tolerance or not
+        "bounce0_record_mismatches": int((sel & (bounce == 0)).sum()),
+        "by_class": {c: int((out_tol & (cls == i)).sum()) for i, c in enumerate(CLASSES)},
+        "by_bounce": {int(b): int((out_tol & (bounce == b)).sum()) for b in np.unique(bounce[out_tol])},
+        "mean_got": [float(x) for x in got[sel, :3].mean(0)],
+        "mean_want": [float(x) for x in want[sel, :3].mean(0)],
+    }
+    rep["unexplained"] = rep["by_class"]["unexplained"]
+    rep["unexplained_pixels"] = [int(i) for i in np.nonzero(out_tol & (cls == CLASSES.index("unexplained")))[0][:16]]
+    return rep
+
+
+def assert_parity(rep, max_out_frac, what=""):
+    """The test bar: no unexplained pixel, nothing differs at bounce 0 (the primary hit, its shading and its shadow
+    ray involve no libm-dependent input except a disk light's sample), the out-of-tolerance fraction stays below
+    `max_out_frac` (2x the observed one, per config), and the image means agree."""
+    assert rep["unexplained"] == 0, "%s: %d pixels leave the tolerance without any discrete divergence: %s" % (
+        what, rep["unexplained"], rep["unexplained_pixels"])
+    frac_out = rep["out_of_tol"] / max(rep["pixels"], 1)
+    assert frac_out <= max_out_frac, "%s: %.6f of the pixels outside %g (allowed %.6f): %s" % (
+        what, frac_out, REL_TOL, max_out_frac, rep["by_class"])
+    assert np.allclose(rep["mean_got"], rep["mean_want"], rtol=5e-3), (what, rep["mean_got"], rep["mean_want"])
+
+
+# ---------------------------------------------------------------------------------------------- drivers
+def cuda_frames(scene, w, h, depth, frames, part=None, device=0):
+    """Fused wavefront through the C ABI with the diagnostic record on.  frames: iterable of frame indices.
+    Returns ([radiance (P,4)], [trace (D,P,4)], final image)."""
+    from mcrt_b200 import rr, pt
+    api = rr.IntersectionApi.Create(device)
+    try:
+        pl = pt.make_pt_pipeline(api, scene, w, h, depth)
+        pl.ensure_size()
+        if part is not None:
+            pl.set_partition(*part)
+        pl.set_path_trace(depth)
+        integ = pl.passes[0]
+        rad, tr = [], []
+        for f in frames:
+            integ.m_frameIndex = f
+            pl.update()
+            rad.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+            tr.append(pl.path_trace(depth).copy())
+        img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+        pl.scene.destroy()
+    finally:
+        rr.IntersectionApi.Delete(api)
+    return rad, tr, img
+
+
+def oracle_frames(scene, w, h, depth, frames, pixels=None):
+    """The compiled reference kernels (oracle/_ref) on the host, same frames; ([radiance], [trace])."""
+    from mcrt_b200 import camera
+    from oracle import ref
+    o = ref.RefOracle()
+    rp = ref.RefPathTracer(o, scene, o.build_scene_bvh(scene), w, h)
+    rad, tr = [], []
+    for f in frames:
+        cam = camera.make_camera(scene.camera, w, h, camera.taa_pixel_offset(f))
+        t = {}
+        rad.append(rp.render_sample(cam, f, depth, trace=t, pixels=pixels).copy())
+        tr.append(t["path_trace"])
+    return rad, tr
+
+
+# ---------------------------------------------------------------------------------------------- the benchmarked configs
+def config(name):
+    """(scene, width, height, depth, frames, partition) of BASELINE.json's configs as bench.py / tools/bench_configs.py
+    render them.  Frame lists are bounded so that the oracle finishes in seconds to a few minutes on the host cores."""
+    from mcrt_b200 import scene_library
+    if name == "C1":      # in full: 512^2, 16 spp, depth 5
+        return scene_library.cornell_box(), 512, 512, 5, list(range(16)), None
+    if name == "C2":      # one full 1080p frame at 871,202 triangles, depth 8
+        return scene_library.dragon_class(), 1920, 1080, 8, [0], None
+    if name == "C3":      # one full 1080p frame with the 1024^2 textures bench.py uses
+        return scene_library.sponza_class(1024), 1920, 1080, 5, [0], None
+    if name == "C5":      # 10 M triangles at 4K: rank 0's tiles of a 64-way partition, frame 127 -- the seed
+        # idx + (frame + 1) * W * H * (bounce + 1) wraps in uint32 from bounce 3 on (E14), indices stay global
+        return scene_library.traversal_bench_scene(2236), 3840, 2160, 5, [127], (0, 64)
+    raise KeyError(name)
+
+
+def run_config(name, device=0):
+    """Per-frame parity reports of one config: CUDA fused wavefront vs oracle/_ref."""
+    from mcrt_b200 import multi_gpu
+    scene, w, h, depth, frames, part = config(name)
+    pixels = None if part is None else multi_gpu.partition_pixels(w, h, part[0], part[1])
+    got, got_tr, _ = cuda_frames(scene, w, h, depth, frames, part=part, device=device)
+    want, want_tr = oracle_frames(scene, w, h, depth, frames, pixels=pixels)
+    reps = []
+    for i, f in enumerate(frames):
+        r = classify(got[i], want[i], got_tr[i], want_tr[i], pixels=pixels)
+        r["config"], r["frame"] = name, f
+        if pixels is not None:      # pixels outside the partition stay exactly black on both sides
+            outside = np.ones(w * h, bool)
+            outside[pixels] = False
+            r["outside_partition_nonzero"] = int(np.count_nonzero(got[i][outside, :3])) + int(np.count_nonzero(want[i][outside, :3]))
+        reps.append(r)
+    return reps

@@ -198,3 +198,51 @@ def test_refit_metadata_and_node_encoding_is_a_function_of_child_bounds():
                 while qhi < 255 and np.float32(lo[a]) + np.float32(qhi) * scale < np.float32(chi[a]):
                     qhi += 1
                 assert q[a][s] == qlo and q[3 + a][s] == qhi
+
+
+def _chain_soup(n=420, ratio=1.18):
+    """Triangles whose size and position shrink geometrically: SAH peels them off one by one, so the binary tree
+    is a chain ~n levels deep and its wide collapse is far deeper than the traversal stack allows."""
+    s = ratio ** -np.arange(n, dtype=np.float64)
+    base = np.array([[0.0, 0.0, 0.0], [1.0, 0.0, 0.0], [0.0, 1.0, 0.3]])
+    v = (base[None, :, :] * s[:, None, None] + (s * 3.0)[:, None, None]).reshape(-1, 3).astype(np.float32)
+    idx = np.arange(3 * n, dtype=np.int32).reshape(n, 3)
+    return v, idx
+
+
+def test_deep_sah_tree_is_rebuilt_to_fit_the_traversal_stack():
+    """the traversal keeps two stack entries per wide level on a 40-entry stack, so the host builder
+    must not emit more than 19 levels (the bound the device builder enforces).  A chain-shaped input (29 levels
+    with the guard switched off) is rebuilt with balanced splits below a depth cap; the tree stays well formed and
+    the emulated walk still finds the brute-force hits."""
+    v, idx = _chain_soup()
+    unguarded = rr.host_bvh(v, idx, None, 1 | 2, refit_info=True)
+    assert len(unguarded[3]) - 1 > 19
+    nodes, tris, tri_mesh, levels = rr.host_bvh(v, idx, None, True, refit_info=True)
+    assert len(levels) - 1 <= 19, len(levels) - 1
+    assert np.array_equal(np.sort(tris[:, 7].view(np.int32)), np.arange(idx.shape[0]))
+    bvh8_emul.subtree_bounds(nodes, tris)
+    # rays at the centroids of the larger triangles (the smallest are 1e-30 across: below what ANY fp32 slab test
+    # resolves from a few units away, SURVEY App. A E4 -- not what this test is about)
+    rng = np.random.RandomState(4)
+    rays = L.make_rays(64)
+    rays["o"][:, :3] = (rng.rand(64, 3) * 4.0 + 4.5).astype(np.float32)
+    k = rng.randint(0, 50, 64)
+    tgt = v.reshape(-1, 3, 3)[k].mean(axis=1)
+    d = tgt - rays["o"][:, :3]
+    rays["d"][:, :3] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    rays["o"][:, 3] = 100.0
+    got, _ = _emulate(nodes, tris, rays)
+    want = port.intersect(port.mesh_triangles([(v, idx, 0, None)]), rays)
+    big = want["primid"] < 60
+    assert big.sum() >= 48 and (want["primid"][big] >= 0).sum() >= 40
+    assert np.array_equal(got["primid"][big], want["primid"][big])
+
+
+def test_non_finite_vertices_are_rejected():
+    v = np.array([[0, 0, 0], [1, 0, 0], [0, np.nan, 0], [0, 0, 1]], np.float32)
+    with pytest.raises(rr.RadeonRaysError, match="non-finite"):
+        rr.host_bvh(v, np.array([[0, 1, 2], [0, 1, 3]], np.int32))
+    v[2, 1] = np.inf
+    with pytest.raises(rr.RadeonRaysError, match="non-finite"):
+        rr.host_bvh(v, np.array([[0, 1, 2], [0, 1, 3]], np.int32))
