@@ -208,6 +208,11 @@ int ptb_nccl_comm_create(ptb_context* ctx, const void* id_in, int rank, int num_
 int ptb_nccl_comm_destroy(void* nccl_comm);
 int ptb_merge_accumulation(ptb_context* ctx, void* nccl_comm, int root);
 
+/* Self-test (no reference counterpart): the shading code's sin / cos / log (csrc/pt_libm.h, which restate the host C
+ * library's algorithms so that sampled directions are bit-identical to the oracle's), evaluated on the device
+ * element-wise over a host array; fn 0 = sin, 1 = cos, 2 = log. */
+int ptb_selftest_libm(ptb_context* ctx, int fn, const float* in, float* out, int n);
+
 int ptb_get_buffer(ptb_context* ctx, const char* name, void** device_ptr, size_t* bytes);
 /* Blocking host->device write of a whole named buffer: restores a checkpoint of the accumulation state
  * ("AccumulationBuffer" = sum(w L) || sum(w), RTReconstructionPass.cpp:212-213; for BDPT also "BDPTSampledLightBuffer",

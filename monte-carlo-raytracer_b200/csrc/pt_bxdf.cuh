@@ -130,7 +130,7 @@ HD V3 sampleLambertianReflection(V3 R, V2 u, V3 wo, V3* wi, float* pdf) {
 // bxdfs.cl:385-390
 HD float roughnessToAlpha(float roughness) {
     roughness = fmaxf(roughness, 1e-3f);
-    float x = logf(roughness);
+    float x = log_ref(roughness);
     return 1.62142f + 0.819955f * x + 0.1734f * x * x + 0.0171201f * x * x * x + 0.000640711f * x * x * x * x;
 }
 
@@ -195,15 +195,15 @@ HD_BXDF V3 sampleTrowbridgeReitzDistribution_wh(V2 u, V3 wo, V2 alpha) {
     } else {
         phi = atanf(alpha.y / alpha.x * tanf(2.0f * PT_PI * u.y + 0.5f * PT_PI));
         if (u.y > .5f) phi += PT_PI;
-        float sinPhi = sinf(phi);
-        float cosPhi = cosf(phi);
+        float sinPhi = sin_ref(phi);
+        float cosPhi = cos_ref(phi);
         const float alphax2 = alpha.x * alpha.x, alphay2 = alpha.y * alpha.y;
         const float alpha2 = 1.0f / (cosPhi * cosPhi / alphax2 + sinPhi * sinPhi / alphay2);
         float tanTheta2 = alpha2 * u.x / (1.0f - u.x);
         cosTheta = 1.0f / sqrtf(1.0f + tanTheta2);
     }
     float sinTheta = sqrtf(fmaxf(0.0f, 1.0f - cosTheta * cosTheta));
-    V3 wh = v3(sinTheta * cosf(phi), cosTheta, sinTheta * sinf(phi));
+    V3 wh = v3(sinTheta * cos_ref(phi), cosTheta, sinTheta * sin_ref(phi));
     if (!isSameHemisphere(wo, wh)) wh = -wh;
     return wh;
 }

@@ -358,6 +358,292 @@ k_shade_est(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
     shade_queue<true>(s, cur, frame, bounce, maxDepth, cap, s.estimator);
 }
 
+// ---------------------------------------------------------------------------------------------
+// shade, sorted: the default (coherence mode 3)
+// ---------------------------------------------------------------------------------------------
+// One CTA takes a CHUNK of consecutive queue entries (neighbouring pixels: they share geometry and texels), SORTS it
+// in shared memory and shades it in sorted order, warp by warp:
+//   * entries whose ray missed are dropped before any shading code runs (in k_shade they idle through all of it);
+//   * the key is what the lanes of a warp would otherwise diverge on -- the TYPE of the light the vertex will sample
+//     and the half of its lobe-selection variate, both known from the sampler alone (samplers.cl:75-84: a pure
+//     function of pixel, frame, bounce), major; the material id, minor (a warp's texel fetches go to one texture set).
+// r01 measured 21 of 32 lanes active on k_shade even on the coherent first bounce, where the queue is in pixel order
+// and every warp walks all three light types and both lobes.  Sorting at CONSUMPTION (here) instead of at production
+// (r01's mode 3: buckets inside the producer's 512-entry chunk, whose 8 boundaries cut through half of its 16 warps)
+// knows hit / miss and the material, covers bounce 0, and needs no key evaluation in the producer.
+// The small scene tables every vertex reads -- shapes, materials, lights, texture descriptors, per-material alpha --
+// are copied into shared memory once per CTA by bulk asynchronous copies (cp.async.bulk, completion on an mbarrier)
+// when they fit; the reference copies a 160-byte RTShape and a 128-byte RTMaterial by value several times per vertex
+// (geometry.cl:181, lights.cl:104, materials.cl:78).
+// Survivors are collected in shared memory and appended to the next queue as ONE contiguous run per chunk, so
+// neighbouring pixels stay neighbours.  Per-path results do not depend on the order (bitwise: the coherence tests).
+#ifndef PT_SORT_CHUNK
+#define PT_SORT_CHUNK 2048
+#endif
+#define PT_SORT_PER_THREAD (PT_SORT_CHUNK / PT_SHADE_BLOCK)
+#define PT_SORT_KEYS 256        // (light type 4) x (lobe half 2) x (material id mod 32)
+static_assert(PT_SORT_CHUNK % PT_SHADE_BLOCK == 0 && PT_SORT_KEYS <= PT_SHADE_BLOCK, "sort geometry");
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned arrivals) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// global -> shared bulk asynchronous copy (the 1-D form of TMA); bytes % 16 == 0, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_copy_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra MBAR_DONE;\n"
+        "bra MBAR_WAIT;\n"
+        "MBAR_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// byte sizes of the staged tables, rounded to the 16 bytes a bulk copy moves
+struct StagedTables {
+    unsigned shapes, materials, lights, textures, alpha;
+    __host__ __device__ unsigned total() const { return shapes + materials + lights + textures + alpha; }
+};
+__host__ __device__ inline StagedTables staged_tables(const PtState& s) {
+    StagedTables t;
+    t.shapes = (unsigned)s.numShapes * 160u;
+    t.materials = (unsigned)s.numMaterials * 128u;
+    t.lights = (unsigned)s.numLights * 80u;
+    t.textures = (unsigned)s.numTextures * 16u;
+    t.alpha = (((unsigned)s.numMaterials * 8u) + 15u) & ~15u;
+    return t;
+}
+#define PT_STAGE_MAX_BYTES (48 * 1024)
+
+template <bool EST>
+__device__ __forceinline__ void shade_sorted(const PtState& s, int cur, int frame, int bounce, int maxDepth, int estimator,
+                                             int stage_tables) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    int4* s_hit = (int4*)smem;                                                   // [CHUNK] sorted hits
+    uint32_t* s_px = (uint32_t*)(smem + PT_SORT_CHUNK * 16);                     // [CHUNK] sorted pixels
+    uint32_t* s_next = s_px + PT_SORT_CHUNK;                                     // [CHUNK] survivors of the chunk
+    unsigned* s_bin = s_next + PT_SORT_CHUNK;                                    // [KEYS] counts, then offsets
+    unsigned* s_misc = s_bin + PT_SORT_KEYS;                                     // [0] live, [1] survivors, [2] queue base, [4..11] warp sums
+    uint64_t* s_bar = (uint64_t*)(s_misc + 16);
+    unsigned char* s_tab = (unsigned char*)(s_bar + 2);
+
+    Scene sc = make_scene(s);
+    if (stage_tables) {
+        const StagedTables t = staged_tables(s);
+        if (threadIdx.x == 0) mbar_init(s_bar, 1);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(s_bar, t.total());
+            unsigned char* d = s_tab;
+            if (t.shapes) bulk_copy_g2s(d, s.shapes, t.shapes, s_bar);
+            d += t.shapes;
+            if (t.materials) bulk_copy_g2s(d, s.materials, t.materials, s_bar);
+            d += t.materials;
+            if (t.lights) bulk_copy_g2s(d, s.lights, t.lights, s_bar);
+            d += t.lights;
+            if (t.textures) bulk_copy_g2s(d, s.textures2D, t.textures, s_bar);
+            d += t.textures;
+            if (t.alpha) bulk_copy_g2s(d, s.material_alpha, t.alpha, s_bar);
+        }
+        unsigned char* d = s_tab;
+        sc.shapes = (const RTShape*)d;
+        d += t.shapes;
+        sc.materials = (const RTMaterial*)d;
+        d += t.materials;
+        sc.lights = (const RTLight*)d;
+        d += t.lights;
+        sc.textures2D = (const TextureDesc2D*)d;
+        d += t.textures;
+        sc.materialAlpha = (const float2*)d;
+        sc.staged = 1;
+        mbar_wait(s_bar, 0);
+    }
+
+    const unsigned count = s.cnt[cur];
+    // chunk: full-size while there is a chunk for every CTA, else shrunk (in whole blocks) so that all SMs shade
+    unsigned chunk = PT_SORT_CHUNK;
+    const unsigned per_cta = (count + gridDim.x - 1) / gridDim.x;
+    if (per_cta < PT_SORT_CHUNK) chunk = max((unsigned)PT_SHADE_BLOCK, (per_cta + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK * PT_SHADE_BLOCK);
+    const unsigned nchunks = (count + chunk - 1) / chunk;
+    const uint32_t* __restrict__ queue = s.queue[cur];
+    const size_t P = (size_t)s.width * s.height;
+
+    for (unsigned c = blockIdx.x; c < nchunks; c += gridDim.x) {
+        const unsigned base = c * chunk;
+        const unsigned n = min(chunk, count - base);
+        if (threadIdx.x < PT_SORT_KEYS) s_bin[threadIdx.x] = 0;
+        if (threadIdx.x == 0) s_misc[1] = 0;
+        __syncthreads();
+        // ---- 1. keys and ranks
+        uint32_t e_px[PT_SORT_PER_THREAD];
+        int4 e_hit[PT_SORT_PER_THREAD];
+        unsigned e_key[PT_SORT_PER_THREAD], e_rank[PT_SORT_PER_THREAD];
+#pragma unroll
+        for (int j = 0; j < PT_SORT_PER_THREAD; ++j) {
+            const unsigned e = threadIdx.x + j * PT_SHADE_BLOCK;
+            e_key[j] = 0xffffffffu;
+            if (e < n) {
+                const uint32_t px = queue[base + e];
+                const int4 h = s.hit[px];
+                e_px[j] = px;
+                e_hit[j] = h;
+                if (h.x != -1 && h.y != -1) {
+                    Sampler sp = makeSampler(s.sobol, (int)px, frame, s.width, s.height, bounce);
+                    uint32_t lightIdx = ((uint32_t)floorf(getSample1D(&sp) * s.numLights));
+                    lightIdx %= (uint32_t)s.numLights;
+                    skipSamples(&sp, 2);
+                    const unsigned lobe = getSample1D(&sp) >= 0.5f ? 1u : 0u;
+                    const unsigned ltype = (unsigned)sc.lights[lightIdx].type & 3u;
+                    const unsigned mat = (unsigned)sc.shapes[h.x].materialId & 31u;
+                    e_key[j] = ((ltype * 2u + lobe) << 5) | mat;
+                    e_rank[j] = atomicAdd(s_bin + e_key[j], 1u);
+                } else if (s.path_trace) {
+                    s.path_trace[(size_t)bounce * P + px] = make_int4(h.x, h.y, 0, 0);
+                }
+            }
+        }
+        __syncthreads();
+        // ---- 2. exclusive scan of the bins (one value per thread of the first KEYS threads)
+        {
+            const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+            unsigned v = threadIdx.x < PT_SORT_KEYS ? s_bin[threadIdx.x] : 0u;
+            unsigned incl = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned t = __shfl_up_sync(0xffffffffu, incl, d);
+                if ((int)lane >= d) incl += t;
+            }
+            if (lane == 31 && warp < PT_SORT_KEYS / 32) s_misc[4 + warp] = incl;
+            __syncthreads();
+            if (threadIdx.x < PT_SORT_KEYS) {
+                unsigned before = 0;
+                for (unsigned w = 0; w < warp; ++w) before += s_misc[4 + w];
+                s_bin[threadIdx.x] = before + incl - v;
+                if (threadIdx.x == PT_SORT_KEYS - 1) s_misc[0] = before + incl;
+            }
+            __syncthreads();
+        }
+        // ---- 3. scatter into sorted order
+#pragma unroll
+        for (int j = 0; j < PT_SORT_PER_THREAD; ++j)
+            if (e_key[j] != 0xffffffffu) {
+                const unsigned pos = s_bin[e_key[j]] + e_rank[j];
+                s_px[pos] = e_px[j];
+                s_hit[pos] = e_hit[j];
+            }
+        __syncthreads();
+        const unsigned n_live = s_misc[0];
+        // ---- 4. shade, a block of sorted entries at a time (whole warps drop out at the tail)
+        for (unsigned r = (threadIdx.x & ~31u); r < n_live; r += PT_SHADE_BLOCK) {
+            const unsigned j = r + (threadIdx.x & 31u);
+            const bool active = j < n_live;
+            bool pushNext = false, pushShadow = false;
+            ShadeOut out;
+            ShadeIn in;
+            uint32_t px = 0;
+            in.pixel = 0;
+            in.shapeId = in.primId = 0;
+            in.bu = in.bv = 0.0f;
+            in.rayDir = in.throughput = v3(0.0f);
+            in.prevBsdfFlags = 0;
+            in.prevPdf = 0.0f;
+            in.prevOrigin = in.prevDirectWeight = v3(0.0f);
+            if (active) {
+                px = s_px[j];
+                const int4 h = s_hit[j];
+                in.pixel = (int)px;
+                in.shapeId = h.x;
+                in.primId = h.y;
+                in.bu = __int_as_float(h.z);
+                in.bv = __int_as_float(h.w);
+                const float4 d = s.ray_d[px];
+                in.rayDir = v3(d.x, d.y, d.z);
+                const float4 tp = s.throughput[px];
+                in.throughput = v3(tp.x, tp.y, tp.z);
+                in.prevBsdfFlags = __float_as_int(tp.w);
+                if (EST) {
+                    in.prevPdf = d.w;
+                    const float4 o = s.ray_o[px];
+                    in.prevOrigin = v3(o.x, o.y, o.z);
+                    if (d.w > 0.0f) {
+                        const float4 dw = s.direct_weight[px];
+                        in.prevDirectWeight = v3(dw.x, dw.y, dw.z);
+                    }
+                }
+            }
+            shade_vertex<false, EST>(sc, in, active, frame, s.width, s.height, bounce, maxDepth, &out, estimator);
+            if (active) {
+                if (out.hasEmission || (EST && (out.emitted.x != 0.0f || out.emitted.y != 0.0f || out.emitted.z != 0.0f))) {
+                    float4 rr = s.radiance[px];
+                    rr.x += out.emitted.x;
+                    rr.y += out.emitted.y;
+                    rr.z += out.emitted.z;
+                    s.radiance[px] = rr;
+                }
+                if (!out.hasEmission) {
+                    pushShadow = out.shadow.written &&
+                                 !(out.direct.x == 0.0f && out.direct.y == 0.0f && out.direct.z == 0.0f);
+                    pushNext = out.continues;
+                }
+                if (s.path_trace) {
+                    const int flags = 1 | (pushShadow ? 2 : 0) | (out.hasEmission ? 4 : 0) | (pushNext ? 8 : 0) | (out.bsdfFlags << 8);
+                    s.path_trace[(size_t)bounce * P + px] = make_int4(in.shapeId, in.primId, flags, 0);
+                }
+            }
+            const unsigned si = warp_push(pushShadow, s.cnt + 5 + (bounce & 1));
+            if (pushShadow) {
+                s.sh_o[si] = make_float4(out.shadow.o.x, out.shadow.o.y, out.shadow.o.z, out.shadow.tmax);
+                s.sh_d[si] = make_float4(out.shadow.d.x, out.shadow.d.y, out.shadow.d.z, __int_as_float((int)px));
+                s.sh_L[si] = make_float4(out.direct.x, out.direct.y, out.direct.z, 0.0f);
+            }
+            const unsigned ni = warp_push(pushNext, s_misc + 1);      // shared-memory counter
+            if (pushNext) {
+                s_next[ni] = px;
+                s.ray_o[px] = make_float4(out.nextO.x, out.nextO.y, out.nextO.z, RT_MAX_TRACE_DISTANCE);
+                s.ray_d[px] = make_float4(out.nextD.x, out.nextD.y, out.nextD.z, EST ? out.nextPdf : 0.0f);
+                if (EST && out.nextPdf > 0.0f)
+                    s.direct_weight[px] = make_float4(out.nextDirectWeight.x, out.nextDirectWeight.y, out.nextDirectWeight.z, 0.0f);
+                s.throughput[px] = make_float4(out.throughput.x, out.throughput.y, out.throughput.z,
+                                               __int_as_float(out.bsdfFlags));
+            }
+        }
+        __syncthreads();
+        // ---- 5. the chunk's survivors become one contiguous run of the next queue
+        const unsigned n_next = s_misc[1];
+        if (threadIdx.x == 0) s_misc[2] = n_next ? atomicAdd(s.cnt + (1 - cur), n_next) : 0u;
+        __syncthreads();
+        const unsigned qbase = s_misc[2];
+        for (unsigned k = threadIdx.x; k < n_next; k += PT_SHADE_BLOCK) s.queue[1 - cur][qbase + k] = s_next[k];
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, 1)
+k_shade_sorted(PtState s, int cur, int frame, int bounce, int maxDepth, int stage_tables) {
+    shade_sorted<false>(s, cur, frame, bounce, maxDepth, 0, stage_tables);
+}
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, 1)
+k_shade_sorted_est(PtState s, int cur, int frame, int bounce, int maxDepth, int stage_tables) {
+    shade_sorted<true>(s, cur, frame, bounce, maxDepth, s.estimator, stage_tables);
+}
+// dynamic shared memory of the sorted shade kernels: sort arrays + bins + barrier + staged tables
+static size_t shade_sorted_smem(unsigned table_bytes) {
+    return (size_t)PT_SORT_CHUNK * 16 + 2 * (size_t)PT_SORT_CHUNK * 4 + PT_SORT_KEYS * 4 + 16 * 4 + 16 + table_bytes;
+}
+
 static int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
@@ -398,6 +684,18 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         cudaStreamWaitEvent(overlap->stream, overlap->fork, 0);
     }
     int cur[2] = {0, 0};
+    // the sorted shade kernel stages the small scene tables in shared memory when they fit
+    const unsigned table_bytes = staged_tables(s).total();
+    static const int stage_enabled = env_int("MCRT_STAGE_TABLES", 1);
+    const int stage_tables = (stage_enabled && table_bytes > 0 && table_bytes <= PT_STAGE_MAX_BYTES) ? 1 : 0;
+    const size_t sorted_smem = shade_sorted_smem(stage_tables ? table_bytes : 0);
+    static bool smem_attr_set = false;
+    if (!smem_attr_set) {
+        const int max_smem = (int)shade_sorted_smem(PT_STAGE_MAX_BYTES);
+        cudaFuncSetAttribute(k_shade_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        cudaFuncSetAttribute(k_shade_sorted_est, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        smem_attr_set = true;
+    }
     auto blocks_trace = [&](int n) { return min(sms * trace_per_sm, (n + 127) / 128); };
     auto blocks_shade = [&](int n) { return min(sms * shade_per_sm, (n + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK); };
     for (int h = 0; h < nh; ++h) {
@@ -425,7 +723,13 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                     k_trace_mixed<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1, b - 1);
                 }
                 if (timer) timer->mark(h, H.stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
-                if (s.estimator)
+                if (s.coherence == 3) {
+                    const int nb = min(sms, (H.n + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK);
+                    if (s.estimator)
+                        k_shade_sorted_est<<<nb, PT_SHADE_BLOCK, sorted_smem, H.stream>>>(H.s, cur[h], frame, b, max_depth, stage_tables);
+                    else
+                        k_shade_sorted<<<nb, PT_SHADE_BLOCK, sorted_smem, H.stream>>>(H.s, cur[h], frame, b, max_depth, stage_tables);
+                } else if (s.estimator)
                     k_shade_est<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
                 else
                     k_shade<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);

@@ -28,6 +28,7 @@ struct PtState {
     const uint32_t* sobol;   // Sobol generator matrices when that sampler is selected, else NULL
     const float2* material_alpha;   // roughnessToAlpha of every material (launch_material_alpha), may be NULL
     int numLights;
+    int numShapes, numMaterials, numTextures;   // table sizes (the sorted shade kernel stages the tables in shared memory)
     int width, height;
     // acceleration structure
     const uint4* nodes;
@@ -125,6 +126,7 @@ cudaError_t launch_pt_shadow_resolve_aos(const PtState& s, int bounce, cudaStrea
 // alpha[i] = (roughnessToAlpha(materials[i].roughness.x), roughnessToAlpha(materials[i].roughness.y))
 cudaError_t launch_material_alpha(const void* materials, float2* alpha, int num_materials, cudaStream_t stream);
 
+cudaError_t launch_selftest_libm(int fn, const float* in, float* out, int n, cudaStream_t stream);
 cudaError_t launch_selftest_fdiv(const float* a, const float* b, float* shortcut, float* plain, int n, cudaStream_t stream);
 
 struct FilterProps {

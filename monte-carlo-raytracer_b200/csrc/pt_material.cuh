@@ -41,7 +41,7 @@ HD void getUberMaterialProperties(const Scene& sc, int materialIdx, const RTInte
     p->eta = m->eta;
     if (m->iorTexId != RT_INVALID_ID) p->eta = readTexture2Df(sc, m->iorTexId, si->uv).x;
     if (m->roughnessTexId == RT_INVALID_ID && sc.materialAlpha) {
-        const float2 a = __ldg(sc.materialAlpha + materialIdx);     // = the two roughnessToAlpha() below, precomputed
+        const float2 a = sc.staged ? sc.materialAlpha[materialIdx] : __ldg(sc.materialAlpha + materialIdx);   // = the two roughnessToAlpha() below, precomputed
         p->roughness = v2(a.x, a.y);
     } else {
         V2 r = v2(m->roughness.x, m->roughness.y);

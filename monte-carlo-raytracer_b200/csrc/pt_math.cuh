@@ -9,7 +9,24 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "pt_libm.h"
+
 namespace mcrt {
+
+// sin / cos / log of the shading path: bit-identical to the host C library the oracle links (pt_libm.h), so that a
+// sampled direction is the SAME float on both sides.  PT_LIBM_GLIBC = 0 falls back to CUDA's libm (1-2 ulp away).
+#ifndef PT_LIBM_GLIBC
+#define PT_LIBM_GLIBC 1
+#endif
+#if PT_LIBM_GLIBC
+__device__ __forceinline__ float sin_ref(float x) { return libm::sinf_glibc(x); }
+__device__ __forceinline__ float cos_ref(float x) { return libm::cosf_glibc(x); }
+__device__ __forceinline__ float log_ref(float x) { return libm::logf_glibc(x); }
+#else
+__device__ __forceinline__ float sin_ref(float x) { return sinf(x); }
+__device__ __forceinline__ float cos_ref(float x) { return cosf(x); }
+__device__ __forceinline__ float log_ref(float x) { return logf(x); }
+#endif
 
 #define PT_PI 3.14159265359f
 #define PT_PI_INV 0.31830988618f
@@ -217,7 +234,7 @@ HD V3 uniformSampleSphere(V2 u) {
     float y = 1.0f - 2.0f * u.x;
     float r = sqrtf(fmaxf(0.0f, 1.0f - y * y));
     float phi = 2.0f * 3.14159265359f * u.y;
-    return v3(r * cosf(phi), y, r * sinf(phi));
+    return v3(r * cos_ref(phi), y, r * sin_ref(phi));
 }
 
 HD V2 concentricSampleDisc(V2 u) {
@@ -231,7 +248,7 @@ HD V2 concentricSampleDisc(V2 u) {
         r = uOffset.y;
         theta = PT_PI_DIV_2 - PT_PI_DIV_4 * (uOffset.x / uOffset.y);
     }
-    return r * v2(cosf(theta), sinf(theta));
+    return r * v2(cos_ref(theta), sin_ref(theta));
 }
 
 HD V3 cosineSampleHemisphere(V2 u) {

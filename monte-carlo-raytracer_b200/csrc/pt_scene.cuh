@@ -71,6 +71,7 @@ struct Scene {              // kernel_data.h:353-370 (device pointers)
     // material has no roughness texture.  NULL = always evaluate.
     const float2* __restrict__ materialAlpha;
     int numLights;
+    int staged;   // 1 = shapes / materials / lights / textures2D / materialAlpha point into SHARED memory (no __ldg)
 };
 
 struct RTInteraction {      // kernel_data.h:162-200, the fields this path uses

@@ -43,6 +43,7 @@ __device__ __forceinline__ Scene make_scene2(const PtState& s) {
     sc.sobolMatrices = s.sobol;
     sc.materialAlpha = nullptr;   // the stage-wise kernels evaluate roughnessToAlpha per lookup, like the reference
     sc.numLights = s.numLights;
+    sc.staged = 0;
     return sc;
 }
 
@@ -309,6 +310,19 @@ __global__ void k_selftest_fdiv(const float* __restrict__ a, const float* __rest
 cudaError_t launch_selftest_fdiv(const float* a, const float* b, float* shortcut, float* plain, int n, cudaStream_t stream) {
     if (n <= 0) return cudaSuccess;
     k_selftest_fdiv<<<(n + 255) / 256, 256, 0, stream>>>(a, b, shortcut, plain, n);
+    return cudaGetLastError();
+}
+
+// self-test of pt_libm.h on the device (ptb_selftest_libm): fn 0 = sin, 1 = cos, 2 = log
+__global__ void k_selftest_libm(int fn, const float* __restrict__ in, float* __restrict__ out, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x = in[i];
+    out[i] = fn == 0 ? libm::sinf_glibc(x) : (fn == 1 ? libm::cosf_glibc(x) : libm::logf_glibc(x));
+}
+cudaError_t launch_selftest_libm(int fn, const float* in, float* out, int n, cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    k_selftest_libm<<<(n + 255) / 256, 256, 0, stream>>>(fn, in, out, n);
     return cudaGetLastError();
 }
 

@@ -23,6 +23,7 @@ __device__ __forceinline__ Scene make_scene(const PtState& s) {
     sc.sobolMatrices = s.sobol;
     sc.materialAlpha = s.material_alpha;
     sc.numLights = s.numLights;
+    sc.staged = 0;
     return sc;
 }
 

@@ -462,7 +462,8 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
     c->st.materials = p;
     {
         void* a = nullptr;
-        if ((rc = alloc_into(c->scene_bufs, "material_alpha", (size_t)std::max(d->num_materials, 1) * sizeof(float2), true,
+        // (rounded up to the 16 bytes a bulk copy into shared memory moves: pt_kernels.cu, staged_tables)
+        if ((rc = alloc_into(c->scene_bufs, "material_alpha", ((size_t)std::max(d->num_materials, 1) * sizeof(float2) + 15) / 16 * 16, true,
                              c->stream, &a)))
             return rc;
         c->st.material_alpha = (const float2*)a;
@@ -470,6 +471,9 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
         PTB_CUDA(mcrt::launch_material_alpha(c->st.materials, (float2*)a, d->num_materials, c->stream));
     }
     c->st.numLights = d->num_lights;
+    c->st.numShapes = d->num_shapes;
+    c->st.numMaterials = d->num_materials;
+    c->st.numTextures = d->num_textures;
     if (d->sobol && (rc = set_sobol_table(c, d->sobol, 1024))) return rc;   // the engine's table (scene/RTScene.cpp:55)
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->scene_loaded = true;
@@ -1020,6 +1024,23 @@ int ptb_selftest_fdiv(ptb_context* c, const float* a, const float* b, float* out
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(d);
     if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("fdiv self-test: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+int ptb_selftest_libm(ptb_context* c, int fn, const float* in, float* out, int n) {
+    if (!c || !in || !out || n < 0 || fn < 0 || fn > 2) return pfail(RRB_ERROR_INVALID_ARGUMENT, "bad argument");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    if (n == 0) return 0;
+    float* d = nullptr;
+    const size_t bytes = (size_t)n * sizeof(float);
+    PTB_CUDA(cudaMalloc((void**)&d, 2 * bytes));
+    cudaError_t e = cudaMemcpyAsync(d, in, bytes, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = mcrt::launch_selftest_libm(fn, d, d + n, n, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d + n, bytes, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return pfail(RRB_ERROR_CUDA, std::string("libm self-test: ") + cudaGetErrorString(e));
     return 0;
 }
 

