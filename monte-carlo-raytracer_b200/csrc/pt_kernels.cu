@@ -175,7 +175,7 @@ k_trace_closest(PtState s, int cur) {
             fetch_closest_ray(s, queue, idx, r);
             return false;
         },
-        [&](unsigned idx, const Ray& r, const TravState& st) { store_closest_hit(s, queue, idx, r, st); });
+        [&](unsigned idx, const Ray& r, const TravState& st) { store_closest_hit(s, queue, idx, r, st); }, s.numNodes, s.stageTop);
 }
 
 // any-hit traversal fused with the reference's ShadowPass; shadow rays of bounce parity `sh`
@@ -188,7 +188,7 @@ k_trace_shadow(PtState s, int sh, int bounce) {
             fetch_shadow_ray(s, idx, r);
             return true;
         },
-        [&](unsigned idx, const Ray&, const TravState& st) { resolve_shadow(s, idx, st, bounce); });
+        [&](unsigned idx, const Ray&, const TravState& st) { resolve_shadow(s, idx, st, bounce); }, s.numNodes, s.stageTop);
 }
 
 // One launch for the two ray sets that are ready after a shade stage: the closest-hit rays of the next bounce
@@ -211,7 +211,8 @@ k_trace_mixed(PtState s, int cur, int sh, int sh_bounce) {
         [&](unsigned idx, const Ray& r, const TravState& st) {
             if (idx < n_closest) store_closest_hit(s, queue, idx, r, st);
             else resolve_shadow(s, idx - n_closest, st, sh_bounce);
-        });
+        },
+        s.numNodes, s.stageTop);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -383,34 +384,6 @@ k_shade_est(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
 #define PT_SORT_PER_THREAD (PT_SORT_CHUNK / PT_SHADE_BLOCK)
 #define PT_SORT_KEYS 256        // (light type 4) x (lobe half 2) x (material id mod 32)
 static_assert(PT_SORT_CHUNK % PT_SHADE_BLOCK == 0 && PT_SORT_KEYS <= PT_SHADE_BLOCK, "sort geometry");
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned arrivals) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-// global -> shared bulk asynchronous copy (the 1-D form of TMA); bytes % 16 == 0, both addresses 16-byte aligned
-__device__ __forceinline__ void bulk_copy_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred P1;\n"
-        "MBAR_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-        "@P1 bra MBAR_DONE;\n"
-        "bra MBAR_WAIT;\n"
-        "MBAR_DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
 
 // byte sizes of the staged tables, rounded to the 16 bytes a bulk copy moves
 struct StagedTables {

@@ -33,6 +33,8 @@ struct PtState {
     // acceleration structure
     const uint4* nodes;
     const float4* tris;
+    int numNodes;         // nodes in the tree; the first MCRT_TOP_NODES are staged in shared memory by the traversal CTAs
+    int stageTop;         // 0 = every node from global memory (experiment switch MCRT_STAGE_TOP=0)
     // SoA wavefront state
     float4* ray_o;        // xyz origin, w tmax
     float4* ray_d;        // xyz direction

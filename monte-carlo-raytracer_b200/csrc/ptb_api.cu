@@ -165,10 +165,14 @@ int set_sobol_table(ptb_context* c, const uint32_t* matrices, int num_dimensions
 
 int refresh_bvh(ptb_context* c) {
     const void *nodes = nullptr, *tris = nullptr;
-    int rc = rrb_get_bvh(c->api, &nodes, &tris, nullptr, nullptr);
+    int64_t num_nodes = 0;
+    int rc = rrb_get_bvh(c->api, &nodes, &tris, &num_nodes, nullptr);
     if (rc) return pfail(rc, rrb_last_error());
     c->st.nodes = (const uint4*)nodes;
     c->st.tris = (const float4*)tris;
+    c->st.numNodes = (int)std::min<int64_t>(num_nodes, 0x7fffffff);
+    static const int stage_top = getenv("MCRT_STAGE_TOP") ? atoi(getenv("MCRT_STAGE_TOP")) : 1;
+    c->st.stageTop = stage_top;
     return 0;
 }
 

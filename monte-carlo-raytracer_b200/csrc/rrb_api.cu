@@ -223,7 +223,8 @@ int query_common(rrb_api* api, bool any_hit, const rrb_buffer* rays, const rrb_b
     if (rc) return rc;
     cudaError_t e = mcrt::launch_query(any_hit, counts != nullptr, api->d_nodes, api->d_tris, rays->dptr,
                                        numrays_buf ? (const int*)numrays_buf->dptr : nullptr, numrays, out->dptr,
-                                       api->d_counter, counts ? (int*)counts->dptr : nullptr, api->stream);
+                                       api->d_counter, counts ? (int*)counts->dptr : nullptr, api->stream,
+                                       (int)std::min<int64_t>(api->num_nodes, 0x7fffffff));
     if (e != cudaSuccess) return cuda_fail(e, "traversal kernel launch");
     if (numrays > 0) api->launches++;
     return record_done(api, done);

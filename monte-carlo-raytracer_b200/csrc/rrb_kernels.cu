@@ -6,6 +6,8 @@
 // I/O uses the reference's API layouts: ray 48 B in, Intersection 32 B / int32 out
 // (intersect_bvh2_lds.cl:66-77,229-240).
 #include "rrb_kernels.h"
+
+#include <cstdlib>
 #include "traverse.cuh"
 
 namespace mcrt {
@@ -20,11 +22,14 @@ template <bool ANY_HIT, bool COUNT>
 __global__ void __launch_bounds__(128, 8)
 query_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const ApiRay* __restrict__ rays,
              const int* __restrict__ numrays_ptr, int numrays_max, void* __restrict__ out,
-             unsigned int* __restrict__ work_counter, int* __restrict__ counts) {
+             unsigned int* __restrict__ work_counter, int* __restrict__ counts, int num_nodes, int stage_top) {
     // a negative device-side count means no rays, as the reference's `index < *num_rays` does
     const int numrays = numrays_ptr ? max(0, min(*numrays_ptr, numrays_max)) : numrays_max;
     const unsigned lane = threadIdx.x & 31u;
+    __shared__ TopNodes s_top;
     Traverser<ANY_HIT, COUNT> trav{nodes, tris};
+    trav.top = s_top.nodes;
+    trav.top_count = stage_top_nodes(s_top, nodes, num_nodes, stage_top);
     uint2 stack[MCRT_STACK_SIZE];
     TravState st;
     Ray ray;
@@ -107,8 +112,9 @@ static int grid_blocks() {
 
 cudaError_t launch_query(bool any_hit, bool counted, const void* nodes, const void* tris, const void* rays,
                          const int* numrays_dev, int numrays_max, void* out, unsigned int* work_counter,
-                         int* counts, cudaStream_t stream) {
+                         int* counts, cudaStream_t stream, int num_nodes) {
     if (numrays_max <= 0) return cudaSuccess;
+    static const int stage_top = getenv("MCRT_STAGE_TOP") ? atoi(getenv("MCRT_STAGE_TOP")) : 1;
     cudaError_t e = cudaMemsetAsync(work_counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
     const int warps_needed = (numrays_max + 31) / 32;
@@ -119,11 +125,11 @@ cudaError_t launch_query(bool any_hit, bool counted, const void* nodes, const vo
     const float4* t = (const float4*)tris;
     const ApiRay* r = (const ApiRay*)rays;
     if (any_hit) {
-        query_kernel<true, false><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts);
+        query_kernel<true, false><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts, num_nodes, stage_top);
     } else if (counted) {
-        query_kernel<false, true><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts);
+        query_kernel<false, true><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts, num_nodes, stage_top);
     } else {
-        query_kernel<false, false><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts);
+        query_kernel<false, false><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts, num_nodes, stage_top);
     }
     return cudaGetLastError();
 }

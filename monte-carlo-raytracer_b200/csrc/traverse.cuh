@@ -16,6 +16,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "async_copy.cuh"
+
 namespace mcrt {
 
 #define MCRT_STACK_SIZE 40
@@ -157,6 +159,8 @@ template <bool ANY_HIT, bool COUNT, bool MIXED = false>
 struct Traverser {
     const uint4* __restrict__ nodes;
     const float4* __restrict__ tris;
+    const uint4* top = nullptr;     // shared-memory copy of nodes [0, top_count) (stage_top_nodes), or unused
+    unsigned top_count = 0;
 
     __device__ __forceinline__ void init(TravState& s, const Ray& r) const {
         s.ngroup = make_uint2(0u, 0x80000000u);   // root node = child slot 7^octinv of a virtual parent
@@ -197,11 +201,21 @@ struct Traverser {
                 const uint32_t slot = (child_bit - 24u) ^ octinv;
                 const uint32_t rel = __popc(imask & ~(0xFFFFFFFFu << slot));
                 const uint32_t ni = ngroup.x + rel;
-                const uint4 n0 = __ldg(nodes + 5 * (size_t)ni + 0);
-                const uint4 n1 = __ldg(nodes + 5 * (size_t)ni + 1);
-                const uint4 n2 = __ldg(nodes + 5 * (size_t)ni + 2);
-                const uint4 n3 = __ldg(nodes + 5 * (size_t)ni + 3);
-                const uint4 n4 = __ldg(nodes + 5 * (size_t)ni + 4);
+                uint4 n0, n1, n2, n3, n4;
+                if (ni < top_count) {      // a top-level node: from the CTA's shared-memory copy
+                    const uint4* np = top + 5 * ni;
+                    n0 = np[0];
+                    n1 = np[1];
+                    n2 = np[2];
+                    n3 = np[3];
+                    n4 = np[4];
+                } else {
+                    n0 = __ldg(nodes + 5 * (size_t)ni + 0);
+                    n1 = __ldg(nodes + 5 * (size_t)ni + 1);
+                    n2 = __ldg(nodes + 5 * (size_t)ni + 2);
+                    n3 = __ldg(nodes + 5 * (size_t)ni + 3);
+                    n4 = __ldg(nodes + 5 * (size_t)ni + 4);
+                }
                 if (COUNT) counters[0]++;
 
                 ngroup.x = n1.x;

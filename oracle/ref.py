@@ -188,6 +188,8 @@ class RefPathTracer:
             trace["path_trace"] = np.zeros((max_depth, self.w * self.h, 4), np.int32)
         for b in range(max_depth):
             if trace is not None:
+                if trace.get("keep_rays"):      # the ray whose hit bounce b shades (RTRay records, before the kernel rewrites them)
+                    trace.setdefault("closest_rays", []).append(self.rays.copy())
                 # the record ptb_set_path_trace keeps on the CUDA side (include/ptb.h), from the reference's buffers
                 rec = trace["path_trace"][b]
                 shaded = (self.rays["extra"][:, 1] != 0) & (self.isect["shapeid"] != -1) & (self.isect["primid"] != -1)
@@ -203,6 +205,8 @@ class RefPathTracer:
                              np.where(shaded, self.throughput["prevBsdfFlags"] << 8, 0))
             o.occluded(self.nodes, self.shadow_rays, self.occlusion)
             self.shadow_rays_traced += int((self.shadow_rays["extra"][:, 1] != 0).sum())
+            if trace is not None and trace.get("keep_rays"):
+                trace.setdefault("shadow_rays", []).append(self.shadow_rays.copy())
             if trace is not None:
                 rec[:, 3] = np.where(shadow, (self.occlusion != -1) | (self.shadow_rays["extra"][:, 1] == 0), 0)
             lib.ref_pt_shadow_pass(_ptr(self.shadow_rays), _ptr(self.occlusion), self.w, self.h, b,

@@ -39,3 +39,29 @@ def test_quantised_plane_conversion_is_exact_and_biased_outwards():
     hi = (np.uint32(0x3F800002) | (b << 8)).view(np.float32).astype(np.float64)
     assert np.array_equal(lo, 1.0 + b * 2.0 ** -15)
     assert np.array_equal((hi - lo) * 2.0 ** 15, np.full(256, 2.0 ** -7))
+
+
+def test_division_through_a_double_reciprocal_is_ieee_division():
+    """pt_math.cuh:fdiv (PT_FDIV_MODE 2) as an algorithm, on the host: (float)((double)a * r) with r within 1.5 ulp
+    (double) of 1 / b is the correctly rounded fp32 quotient for every finite non-zero b -- a quotient of two 24-bit
+    numbers cannot lie within 2^-49 (relatively) of a float midpoint, the double result is within 2^-51 of it.  The
+    reciprocal is perturbed randomly inside its error bound, as the device's Newton iteration may land anywhere in
+    it.  The device code itself: tests/test_pt_gpu.py::test_division_shortcut_is_ieee_division."""
+    rng = np.random.RandomState(3)
+    n = 1 << 22
+    rnd = lambda k: rng.randint(0, 2 ** 32, k, dtype=np.uint64).astype(np.uint32).view(np.float32)
+    unit = lambda k: (rng.rand(k).astype(np.float32) * np.float32(4.0) - np.float32(2.0))
+    special = np.array([0.0, -0.0, 1.0, -1.0, np.inf, -np.inf, np.nan, 1e-45, -1e-45, 1e-39, 3e38, -3e38,
+                        1.17549435e-38, 2.0 ** -40, 2.0 ** -100, 2.0 ** 100, 0.1, -7.5, 3.0, 1.0 / 3.0], np.float32)
+    a = np.concatenate([np.repeat(special, special.size), rnd(n), unit(n), unit(n), np.zeros(1 << 12, np.float32)])
+    b = np.concatenate([np.tile(special, special.size), rnd(n), unit(n), rnd(n), unit(1 << 12)])
+    ok = np.isfinite(b) & (b != 0)          # the device takes the plain division for b = 0, inf, NaN
+    a, b = a[ok], b[ok]
+    with np.errstate(all="ignore"):
+        want = (a / b).astype(np.float32)
+        r = 1.0 / b.astype(np.float64)
+        r = r * (1.0 + (rng.rand(r.size) - 0.5) * 3.0 * 2.0 ** -53)
+        got = (a.astype(np.float64) * r).astype(np.float32)
+    nan = np.isnan(want)
+    assert np.array_equal(np.isnan(got), nan)
+    assert np.array_equal(got[~nan].view(np.uint32), want[~nan].view(np.uint32))

@@ -8,12 +8,15 @@ reference kernels (oracle/_ref), with every pixel outside the tolerance classifi
   C5  10 M triangles at 3840 x 2160, frame 127, the tiles of rank 0 of a 64-way partition: global pixel indices and
       W * H in the sampler seed, which wraps in uint32 there
 
-Bar: no pixel leaves 1e-4 relative without a discrete divergence from the oracle's path (a closest-hit, shadow or
-termination flip at some bounce, caused by a last-bit libm difference in a sampled direction); the bounce-0 records
-agree everywhere; the out-of-tolerance fraction is at most 2x the one observed when the test was written
-(profiles/r02_parity.md); image means agree to 0.5 %.  The converged-image criterion of north_star -- RMSE of the
-accumulated image against the oracle's at equal spp <= 1e-3 of the mean luminance -- is
-tested on C1 in full through ptb_accumulate against reconstruction.cl run by the oracle.
+Bar (tests/parity_util.py).  The shading arithmetic is bit-identical to the oracle's, libm included
+(csrc/pt_libm.h), so: every pixel whose path shows no discrete divergence is BIT-IDENTICAL to the oracle's; every
+divergence is a traversal answer on an identical ray where the CUDA walk agrees with the brute-force restatement of
+the reference's triangle test and the reference's own BVH2 kernel does not (its fp32 slab test culls a leaf at
+t ~ tmax, SURVEY App. A E4, or it reports another of several equal-t duplicates, E1) -- none where the CUDA walk is
+the wrong one; and the fraction of pixels that leave 1e-4 through such a divergence is at most 2x the observed one
+(profiles/r02_parity.md).  The converged-image criterion of north_star -- RMSE of the accumulated image against
+the oracle's at equal spp <= 1e-3 of the mean luminance -- is tested on C1 in full through
+ptb_accumulate against reconstruction.cl run by the oracle.
 """
 import ctypes
 
@@ -26,8 +29,8 @@ from oracle import ref
 
 pytestmark = pytest.mark.gpu
 
-# observed out-of-tolerance fractions (profiles/r02_parity.md) x 2
-MAX_OUT_FRAC = {"C1": 2 * 1.0e-3, "C2": 2 * 1.0e-2, "C3": 2 * 2.0e-3, "C5": 2 * 5.0e-3}
+# observed out-of-tolerance fractions (profiles/r02_parity.md: C1 4.8e-4 worst frame, C2 1.9e-6, C3 1.5e-4, C5 0) x 2
+MAX_OUT_FRAC = {"C1": 1.0e-3, "C2": 1.0e-5, "C3": 3.0e-4, "C5": 1.0e-5}
 RMSE_BOUND = 1e-3          # x mean luminance of the oracle's image
 
 
@@ -41,16 +44,12 @@ def need_ref():
 
 
 @pytest.mark.parametrize("name", ["C2", "C3", "C5"])
-def test_benchmarked_config_every_outlier_is_a_classified_divergence(name):
+def test_benchmarked_config_every_divergence_is_the_references_own_traversal(name):
     need_ref()
     for rep in pu.run_config(name):
-        what = "%s frame %d" % (name, rep["frame"])
-        pu.assert_parity(rep, MAX_OUT_FRAC[name], what)
-        if name != "C2":      # C2 has a disk light: its sample goes through sinf / cosf already at bounce 0
-            assert rep["bounce0_record_mismatches"] == 0, (what, rep)
+        pu.assert_parity(rep, MAX_OUT_FRAC[name], "%s frame %d" % (name, rep["frame"]))
         if "outside_partition_nonzero" in rep:
             assert rep["outside_partition_nonzero"] == 0
-        assert rep["max_rel_err_of_undiverged"] <= pu.REL_TOL, (what, rep["max_rel_err_of_undiverged"])
 
 
 def test_c1_in_full_per_sample_parity_and_converged_image_rmse():
@@ -59,13 +58,10 @@ def test_c1_in_full_per_sample_parity_and_converged_image_rmse():
     reference's own ReconstructionPass kernel (reconstruction.cl:6-60)."""
     need_ref()
     scene, w, h, depth, frames, _ = pu.config("C1")
-    got, got_tr, img = pu.cuda_frames(scene, w, h, depth, frames)
-    want, want_tr = pu.oracle_frames(scene, w, h, depth, frames)
-    for i, f in enumerate(frames):
-        rep = pu.classify(got[i], want[i], got_tr[i], want_tr[i])
-        pu.assert_parity(rep, MAX_OUT_FRAC["C1"], "C1 frame %d" % f)
-        assert rep["bounce0_record_mismatches"] == 0, rep
-        assert rep["max_rel_err_of_undiverged"] <= pu.REL_TOL
+    keep = {}
+    for rep in pu.run_config("C1", keep=keep):
+        pu.assert_parity(rep, MAX_OUT_FRAC["C1"], "C1 frame %d" % rep["frame"])
+    img, want = keep["cuda_image"], keep["oracle_radiance"]
     lib = ref.RefOracle().lib
     lib.ref_reconstruction_all_filters.argtypes = [ctypes.c_int] * 3 + [ctypes.c_void_p] * 4
     from mcrt_b200 import pt
@@ -92,7 +88,7 @@ def test_c1_in_full_per_sample_parity_and_converged_image_rmse():
 def test_c4_bdpt_1024_two_frames_vs_reference():
     """C4 at its full size.  BDPT sums strategies into pixels with float atomics in an unspecified order (in the
     reference too) and splats light-tracing strategies into other pixels, so the per-pixel record of the PT tests
-    does not apply; the bar is the fraction within 1e-4 (observed 0.994 / 0.993: profiles/r02_parity.md), the image
+    does not apply; the bar is the fraction within 1e-4 (observed 0.9996: profiles/r02_parity.md), the image
     mean, and the image RMSE against the spread of two oracle-sized estimates."""
     need_ref()
     from test_bdpt_gpu import gpu_frames, ref_frames, rel_err
@@ -103,13 +99,13 @@ def test_c4_bdpt_1024_two_frames_vs_reference():
     for f in range(2):
         e = rel_err(got[f][:, :3], want[f][:, :3])
         frac = float((e <= 1e-4).mean())
-        assert frac >= 0.985, "frame %d: only %.5f of pixels within 1e-4" % (f, frac)
-        assert np.allclose(got[f][:, :3].mean(0), want[f][:, :3].mean(0), rtol=5e-3)
+        assert frac >= 0.999, "frame %d: only %.5f of pixels within 1e-4" % (f, frac)
+        assert np.allclose(got[f][:, :3].mean(0), want[f][:, :3].mean(0), rtol=1e-3)
     # converged-image criterion for BDPT: the CUDA image's distance from the oracle's is far inside the distance
     # between two independent estimates of the same size (frame 0 vs frame 1 of the oracle)
     a = 0.5 * (got[0][:, :3] + got[1][:, :3])
     b = 0.5 * (want[0][:, :3] + want[1][:, :3])
     rmse = float(np.sqrt(np.mean((a - b) ** 2)))
     spread = float(np.sqrt(np.mean((want[0][:, :3] - want[1][:, :3]) ** 2))) / 2.0
-    assert rmse <= 0.1 * spread, (rmse, spread)
+    assert rmse <= 0.01 * spread, (rmse, spread)
     assert cnt["samples"] == 2 * w * h

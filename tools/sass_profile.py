@@ -62,7 +62,9 @@ def main():
     by_fn, by_line, by_op = collections.defaultdict(lambda: [0, 0, 0]), collections.defaultdict(lambda: [0, 0, 0]), collections.Counter()
     tot = [0, 0, 0]
     for r in rows[2:]:
-        if len(r) != len(hdr):
+        if r and r[0] == "Kernel Name":      # a second launch in the same page: the first one is the profile
+            break
+        if len(r) != len(hdr) or r[ia] == "Address":
             continue
         a = int(r[ia], 16)
         base = a if base is None else base
