@@ -54,6 +54,11 @@ def parse_args():
     ap.add_argument("--tex", type=int, default=1024, help="texture edge length (1024 = the named workload)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--halves", type=int, default=0, choices=[0, 1, 2],
+                    help="how a frame is issued (ptb_set_overlap): 0 = 1 wavefront when frames are in flight, else 2 half-frame wavefronts")
+    ap.add_argument("--no-extras", action="store_true", help="skip the sustained loop, the L2 measurement and traversal T")
+    ap.add_argument("--sustain-seconds", type=float, default=2.0)
+    ap.add_argument("--t-res", type=int, default=4096, help="traversal T: rays per set = t_res^2 (SURVEY 8d: 2^24)")
     ap.add_argument("--frames-in-flight", type=int, default=2,
                     help="consecutive samples rendered concurrently on side streams (ptb_set_frames_in_flight); results "
                          "are bit-identical.  Measured on this workload (profiles/r01_c5_tiles.md): 1 -> 3.87 ms per step "
@@ -252,7 +257,7 @@ def own_arm(args):
     pl.set_frames_in_flight(fif)
     # with frames in flight a frame is issued as ONE wavefront: whole frames overlap each other, and that fills the
     # kernel tails better than two half-frame wavefronts of the same frame do (profiles/r01_frames_in_flight.md)
-    timed_halves = 1 if fif > 1 else 2
+    timed_halves = args.halves or (1 if fif > 1 else 2)
     pl.set_overlap(timed_halves)
     pt_pass = pl.passes[0]
     lib, h = pt._lib(), pl.scene._h
@@ -412,12 +417,7 @@ def own_arm(args):
         top_ms, top_bytes, nb = stages[top]
         nb = max(nb, 1)
         achieved = top_bytes / max(top_ms * 1e-3, 1e-12) / 1e9
-        traffic = None
-        try:
-            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                traffic = json.load(f).get(top)
-        except OSError:
-            pass
+        traffic = None      # measured per build: run_extras() fills it from profiles/kernel_counters.json
         roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                     "launches": nb, "avg_launch_ms": top_ms / nb, "algorithmic_bytes_per_launch": top_bytes / nb,
@@ -431,6 +431,11 @@ def own_arm(args):
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cpu = run_cpu_baseline(scene, args, args.cpu_seconds)
+        # ---------------- outside `value`, N = 1 only: sustained loop, L2 / issue rooflines, traversal micro-benchmark T
+        extras = {}
+        if world == 1 and not args.no_extras:
+            extras = run_extras(args, torch, stream, dev, local, device_step, frames, cams, Wm, K, pl, api, scene,
+                                roofline, top, stages, clocks)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": config_of(args, world),
@@ -439,7 +444,7 @@ def own_arm(args):
                 "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / K, "h2d_bytes_per_step": 176,
                         "d2h_bytes_per_step": int(host_np.nbytes), "image_mean": img_mean},
-                "gpu_launches": launches_total, "clocks": clocks,
+                "gpu_launches": launches_total, "clocks": clocks, **extras,
                 "bvh": {"build_and_upload_s": setup_s, "nodes": int(stats.get("num_nodes", 0)) if isinstance(stats, dict) else None,
                         "acc_type": acc_type, "on_device": int(stats.get("last_build_on_device", 0)) if isinstance(stats, dict) else None,
                         "commit_s": float(stats.get("build_seconds", 0.0)) if isinstance(stats, dict) else None}}
@@ -452,6 +457,99 @@ def own_arm(args):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def build_fingerprint():
+    from mcrt_b200 import build
+    return build._fingerprint()[:16]
+
+
+def load_sidecar():
+    """Per-kernel hardware counters of ONE step of this workload, measured by tools/measure_counters.py under ncu
+    (dram bytes, L2 bytes, warp instructions per launch).  They are tied to the build they were measured on: a
+    sidecar whose fingerprint differs from the library's is refused (None), never silently reused."""
+    path = os.path.join(ROOT, "profiles", "kernel_counters.json")
+    try:
+        with open(path) as f:
+            d = json.load(f)
+    except OSError:
+        return None
+    return d if d.get("build_fingerprint") == build_fingerprint() else None
+
+
+def measure_l2_copy_gbs(torch, dev, stream):
+    """Device-to-device copy of a buffer that fits the L2 twice over (2 x 24 MB), read + write bytes per second:
+    the denominator of roofline.l2 (SURVEY 8d #2), obtained the way MEASURED_PEAKS.json's hbm_gbs was."""
+    n = 24 * 1024 * 1024 // 4
+    a = torch.empty(n, dtype=torch.float32, device=dev).normal_()
+    b = torch.empty_like(a)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 0.0
+    for _ in range(5):
+        for _ in range(3):
+            b.copy_(a)
+        e0.record(stream)
+        for _ in range(40):
+            b.copy_(a)
+        e1.record(stream)
+        e1.synchronize()
+        best = max(best, 40 * 2 * n * 4 / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+    return best
+
+
+def run_extras(args, torch, stream, dev, local, device_step, frames, cams, Wm, K, pl, api, scene, roofline, top, stages,
+               clocks):
+    from mcrt_b200 import rr, scene_library, traversal_bench
+    out = {}
+    # (1) sustained: the same device-resident step for >= sustain_seconds, clocks sampled while it runs
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    pl.reset_counters()
+    n, t0 = 0, time.perf_counter()
+    ev0.record(stream)
+    while time.perf_counter() - t0 < args.sustain_seconds:
+        for s in range(Wm, Wm + K):
+            device_step(frames[s], *cams[s])
+        n += K
+        pl.synchronize()
+    ev1.record(stream)
+    ev1.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    c = sampler.stop()
+    out["sustained"] = {"seconds": ms * 1e-3, "steps": n, "value": pl.counters()["samples"] / (ms * 1e-3), "unit": UNIT,
+                        "sm_mhz": c.get("sm_mhz"), "power_w_max": c.get("power_w_max"), "reasons": c.get("reasons")}
+    # (2) the non-HBM rooflines of the dominant kernel: issue slots and L2 bytes, from the measured per-launch counters
+    side = load_sidecar()
+    l2_peak = measure_l2_copy_gbs(torch, dev, stream)
+    mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    roofline["l2_copy_gbs_measured"] = l2_peak
+    if side and top in side.get("kernels", {}):
+        k = side["kernels"][top]
+        t_launch = roofline["avg_launch_ms"] * 1e-3
+        roofline["traffic"] = k["dram_bytes_per_launch"]
+        roofline["traffic_source"] = "ncu, %s, build %s" % (side.get("when"), side.get("build_fingerprint"))
+        issue_peak = sms * 4 * mhz * 1e6
+        roofline["issue"] = {"warp_insts_per_launch": k["warp_insts_per_launch"], "achieved_per_s": k["warp_insts_per_launch"] / t_launch,
+                             "peak_per_s": issue_peak, "frac": k["warp_insts_per_launch"] / t_launch / issue_peak,
+                             "threads_per_inst": k.get("threads_per_inst"), "sm_mhz": mhz}
+        roofline["l2"] = {"bytes_per_launch": k["l2_bytes_per_launch"], "achieved": k["l2_bytes_per_launch"] / t_launch / 1e9,
+                          "peak": l2_peak, "unit": "GB/s", "frac": k["l2_bytes_per_launch"] / t_launch / 1e9 / l2_peak}
+    else:
+        roofline["traffic"] = None
+        roofline["traffic_source"] = "no counters for this build (tools/measure_counters.py writes profiles/kernel_counters.json)"
+    # (3) traversal micro-benchmark T (SURVEY 8d): the 1 M-triangle knot, and this workload's closed atrium
+    t_scene = scene_library.traversal_bench_scene(707)
+    api_t = rr.IntersectionApi.Create(local, cuda_stream=stream.cuda_stream)
+    rr.attach_scene(api_t, t_scene)
+    api_t.Commit()
+    out["traversal_T"] = {"rays_per_set": args.t_res * args.t_res,
+                          "knot_1M": traversal_bench.run(api_t, t_scene, stream, args.t_res),
+                          "sponza_class": traversal_bench.run(api, scene, stream, args.t_res),
+                          "bytes_per_ray": {"closest": BYTES_CLOSEST_PER_RAY, "anyhit": BYTES_SHADOW_PER_RAY}}
+    rr.IntersectionApi.Delete(api_t)
+    return out
 
 
 _RESULT_FD = None

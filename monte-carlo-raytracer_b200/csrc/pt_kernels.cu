@@ -604,11 +604,11 @@ __device__ __forceinline__ void shade_sorted(const PtState& s, int cur, int fram
     }
 }
 
-__global__ void __launch_bounds__(PT_SHADE_BLOCK, 1)
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
 k_shade_sorted(PtState s, int cur, int frame, int bounce, int maxDepth, int stage_tables) {
     shade_sorted<false>(s, cur, frame, bounce, maxDepth, 0, stage_tables);
 }
-__global__ void __launch_bounds__(PT_SHADE_BLOCK, 1)
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
 k_shade_sorted_est(PtState s, int cur, int frame, int bounce, int maxDepth, int stage_tables) {
     shade_sorted<true>(s, cur, frame, bounce, maxDepth, s.estimator, stage_tables);
 }

@@ -23,7 +23,7 @@ def main():
         objs, procs = [], []
         for src in b._sources():
             obj = os.path.join(odir, os.path.basename(src) + ".o")
-            cmd = [b._nvcc()] + b.NVCC_FLAGS + defs.split() + ["-I", b.INCLUDE, "-I", b.CSRC, "-c", src, "-o", obj]
+            cmd = [b._nvcc()] + b.NVCC_FLAGS + defs.split() + ["-I", b.INCLUDE, "-I", b.CSRC, "-I", b._nccl()[0], "-c", src, "-o", obj]
             procs.append(subprocess.Popen(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True))
             objs.append(obj)
         jobs.append((name, objs, procs))
@@ -34,7 +34,9 @@ def main():
                 print(err)
                 raise SystemExit("variant %s failed" % name)
         lib = os.path.join(out_dir, "libmcrt_%s.so" % name)
-        subprocess.check_call([b._nvcc(), "-shared", "-o", lib] + objs + ["-lcudart", "-lpthread"])
+        nccl_lib = b._nccl()[1]
+        subprocess.check_call([b._nvcc(), "-shared", "-o", lib] + objs + ["-lcudart", "-lpthread", "-L" + nccl_lib, "-l:libnccl.so.2",
+                                                                          "-Xlinker", "-rpath=" + nccl_lib])
         print("built", lib)
 
 
