@@ -27,6 +27,7 @@ struct PtState {
     const void* camera;
     const uint32_t* sobol;   // Sobol generator matrices when that sampler is selected, else NULL
     const float2* material_alpha;   // roughnessToAlpha of every material (launch_material_alpha), may be NULL
+    const float4* tri_shade;        // per-triangle shading records (launch_build_tri_shade), 9 float4 each, may be NULL
     int numLights;
     int numShapes, numMaterials, numTextures;   // table sizes (the sorted shade kernel stages the tables in shared memory)
     int width, height;
@@ -128,6 +129,9 @@ cudaError_t launch_pt_shadow_resolve_aos(const PtState& s, int bounce, cudaStrea
 // alpha[i] = (roughnessToAlpha(materials[i].roughness.x), roughnessToAlpha(materials[i].roughness.y))
 cudaError_t launch_material_alpha(const void* materials, float2* alpha, int num_materials, cudaStream_t stream);
 
+// records[9 * t ..] = the triangle-only half of computeSurfaceInteraction for scene triangle t (index-array order);
+// tri_shape[t] = its RTShape.  Re-run after the shapes array changes.
+cudaError_t launch_build_tri_shade(const PtState& s, const int* tri_shape, float4* records, int n_tris, cudaStream_t stream);
 cudaError_t launch_selftest_libm(int fn, const float* in, float* out, int n, cudaStream_t stream);
 cudaError_t launch_selftest_fdiv(const float* a, const float* b, float* shortcut, float* plain, int n, cudaStream_t stream);
 

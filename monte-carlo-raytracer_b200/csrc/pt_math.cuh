@@ -72,21 +72,22 @@ HD V3 v3(float a) { return v3(a, a, a); }
 HD V3 v3(const float4& f) { return v3(f.x, f.y, f.z); }
 HD V2 v2(float x, float y) { V2 r; r.x = x; r.y = y; return r; }
 
-// IEEE a / b, i.e. the correctly rounded fp32 quotient the oracle's `/` gives, without the hardware division sequence.
-// ncu r02 (profiles/r02_shade.md): with --prec-div the 21 `V3 / float` sites and their neighbours were 40 % of the
-// warp instructions k_shade executed -- per division a reciprocal, seven dependent FFMA, a range check (FCHK) and a
-// BSSY / BSYNC / BRA frame for its slow path, and r01's branch-free patch for zero numerators on top.
-// Here the quotient is formed in DOUBLE precision, a * (1 / b), and rounded once to float.  That is exact: the
-// reciprocal (MUFU.RCP64H seed + two Newton steps) is within 1.5 ulp of double, the product adds half an ulp, so the
-// double result is within 2^-51 of a / b relatively, while a / b, being a quotient of two 24-bit numbers, cannot lie
-// closer than 2^-49 (relatively) to a midpoint between two floats unless it IS a float -- so rounding the double
-// gives the float that rounding a / b itself gives, for every operand, zero numerators, signed zeros, denormal and
-// overflowing quotients included (double has the exponent range to spare).  b = 0, inf, NaN take the plain division.
-// One reciprocal serves the three components of a vector.  Checked against IEEE division over 4 M operand pairs on
-// the device (ptb_selftest_fdiv) and as an algorithm on the host (tests/test_math_cpu.py).
-// PT_FDIV_MODE: 2 = this (default), 1 = r01's zero-numerator shortcut around the hardware sequence, 0 = plain `/`.
+// IEEE a / b.  The hardware division sequence range-checks its operands (FCHK) and sends a ZERO numerator down a
+// ~25-instruction subroutine; components of axis-aligned normals, tangents and colours are zero all the time
+// (ncu r01: every warp of k_shade took that subroutine at 21 call sites, 10 % of its instructions).
+// PT_FDIV_MODE 1 (default) -- branch-free shortcut: a zero numerator is replaced by 2^-40, whose quotient t cannot
+// overflow for any finite b (>= 2^-149), and the result is a * t: a signed zero with sign(a) ^ sign(b) for finite
+// non-zero b and for b = inf (t = 0), NaN for b = 0 (t = inf) and b = NaN -- exactly what 0 / b gives.  Non-zero
+// numerators are untouched.
+// PT_FDIV_MODE 2 -- the quotient formed in DOUBLE precision, a * (1 / b) with the reciprocal from MUFU.RCP64H + two
+// Newton steps, rounded once to float.  It is exact for every operand (a quotient of two 24-bit numbers cannot lie
+// within 2^-49, relatively, of a float midpoint; the double result is within 2^-51: tests/test_math_cpu.py, and
+// ptb_selftest_fdiv on the device) and needs a third of the instructions (ncu r02: with --prec-div the `V3 / float`
+// sites are 40 % of the warp instructions k_shade executes) -- and it is SLOWER on B200: the F2F conversions and
+// DFMA / DMUL run on narrow pipes, k_shade 1.94 -> 2.76 ms per step (profiles/r02_shade.md).  Kept as a switch.
+// PT_FDIV_MODE 0 -- plain `/`.
 #ifndef PT_FDIV_MODE
-#define PT_FDIV_MODE 2
+#define PT_FDIV_MODE 1
 #endif
 HD double rcp_f64(float b) {           // 1 / b for finite non-zero b
     const double bd = (double)b;

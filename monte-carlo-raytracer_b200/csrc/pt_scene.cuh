@@ -70,6 +70,12 @@ struct Scene {              // kernel_data.h:353-370 (device pointers)
     // (k_material_alpha); read instead of re-evaluating two logf polynomials per material lookup when the
     // material has no roughness texture.  NULL = always evaluate.
     const float2* __restrict__ materialAlpha;
+    // Per-triangle shading records (k_build_tri_shade), 9 float4 per scene triangle in index-array order
+    // (record = startIdx / 3 + prim), or NULL: world-space positions, transformed normals, uvs, the geometric
+    // normal and the uv partial derivatives -- everything computeSurfaceInteraction derives from the triangle alone,
+    // computed once by the same expressions.  A vertex then needs ONE round of independent 16-byte loads instead
+    // of the dependent chain shape -> indices -> 3 x (position, normal, uv) and two matrix products per vertex.
+    const float4* __restrict__ triShade;
     int numLights;
     int staged;   // 1 = shapes / materials / lights / textures2D / materialAlpha point into SHARED memory (no __ldg)
 };
@@ -101,6 +107,14 @@ HD void computeTrianglePartialDerivates(V2 uv0, V2 uv1, V2 uv2, V3 p0, V3 p1, V3
 
 HD void loadTrianglePositions(const Scene& sc, const RTShape* shape, int primIdx, V3* p0, V3* p1, V3* p2,
                               uint32_t* i0, uint32_t* i1, uint32_t* i2) {
+    if (sc.triShade) {      // world-space vertices straight from the per-triangle record (the indices are not needed)
+        const float4* r = sc.triShade + 9 * (size_t)(shape->startIdx / 3u + (uint32_t)primIdx);
+        *p0 = v3(__ldg(r + 0));
+        *p1 = v3(__ldg(r + 1));
+        *p2 = v3(__ldg(r + 2));
+        *i0 = *i1 = *i2 = 0;
+        return;
+    }
     const uint32_t base = shape->startIdx + 3u * (uint32_t)primIdx;
     *i0 = sc.indices[base];
     *i1 = sc.indices[base + 1];
@@ -110,9 +124,92 @@ HD void loadTrianglePositions(const Scene& sc, const RTShape* shape, int primIdx
     *p2 = transformPoint3(shape->toWorld, v3(__ldg(sc.positions + shape->startVertex + *i2)));
 }
 
+// The triangle-only part of computeSurfaceInteraction (geometry.cl:177-215), evaluated once per triangle.
+struct TriShade {
+    V3 p0, p1, p2, n0, n1, n2, gn, dpdu, dpdv;
+    V2 uv0, uv1, uv2;
+    bool hasDerivatives;    // the uv determinant is not near zero: dpdu / dpdv do not depend on the shading normal
+};
+HD TriShade computeTriShade(const Scene& sc, int shapeId, int primIdx) {
+    TriShade t;
+    const RTShape* shape = sc.shapes + shapeId;
+    const uint32_t base = shape->startIdx + 3u * (uint32_t)primIdx;
+    const uint32_t i0 = sc.indices[base], i1 = sc.indices[base + 1], i2 = sc.indices[base + 2];
+    const uint32_t sv = shape->startVertex;
+    t.p0 = transformPoint3(shape->toWorld, v3(__ldg(sc.positions + sv + i0)));
+    t.p1 = transformPoint3(shape->toWorld, v3(__ldg(sc.positions + sv + i1)));
+    t.p2 = transformPoint3(shape->toWorld, v3(__ldg(sc.positions + sv + i2)));
+    const float2 a = __ldg(sc.uvs + sv + i0), b = __ldg(sc.uvs + sv + i1), c = __ldg(sc.uvs + sv + i2);
+    t.uv0 = v2(a.x, a.y);
+    t.uv1 = v2(b.x, b.y);
+    t.uv2 = v2(c.x, c.y);
+    t.n0 = transformVector3(shape->toWorldInvT, v3(__ldg(sc.normals + sv + i0)));
+    t.n1 = transformVector3(shape->toWorldInvT, v3(__ldg(sc.normals + sv + i1)));
+    t.n2 = transformVector3(shape->toWorldInvT, v3(__ldg(sc.normals + sv + i2)));
+    t.gn = normalize(cross(t.p0 - t.p2, t.p1 - t.p2));
+    const V2 duv02 = t.uv0 - t.uv2, duv12 = t.uv1 - t.uv2;
+    const float det = duv02.x * duv12.y - duv02.y * duv12.x;
+    t.hasDerivatives = isNotNearZero(det);
+    t.dpdu = t.dpdv = v3(0.0f);
+    if (t.hasDerivatives) computeTrianglePartialDerivates(t.uv0, t.uv1, t.uv2, t.p0, t.p1, t.p2, v3(0.0f), &t.dpdu, &t.dpdv);
+    return t;
+}
+HD void storeTriShade(float4* __restrict__ r, const TriShade& t) {
+    r[0] = make_float4(t.p0.x, t.p0.y, t.p0.z, t.uv0.x);
+    r[1] = make_float4(t.p1.x, t.p1.y, t.p1.z, t.uv0.y);
+    r[2] = make_float4(t.p2.x, t.p2.y, t.p2.z, t.uv1.x);
+    r[3] = make_float4(t.n0.x, t.n0.y, t.n0.z, t.uv1.y);
+    r[4] = make_float4(t.n1.x, t.n1.y, t.n1.z, t.uv2.x);
+    r[5] = make_float4(t.n2.x, t.n2.y, t.n2.z, t.uv2.y);
+    r[6] = make_float4(t.gn.x, t.gn.y, t.gn.z, t.hasDerivatives ? 1.0f : 0.0f);
+    r[7] = make_float4(t.dpdu.x, t.dpdu.y, t.dpdu.z, 0.0f);
+    r[8] = make_float4(t.dpdv.x, t.dpdv.y, t.dpdv.z, 0.0f);
+}
+HD TriShade loadTriShade(const float4* __restrict__ r) {
+    const float4 a = __ldg(r + 0), b = __ldg(r + 1), c = __ldg(r + 2), d = __ldg(r + 3), e = __ldg(r + 4), f = __ldg(r + 5),
+                 g = __ldg(r + 6), h = __ldg(r + 7), i = __ldg(r + 8);
+    TriShade t;
+    t.p0 = v3(a);
+    t.p1 = v3(b);
+    t.p2 = v3(c);
+    t.n0 = v3(d);
+    t.n1 = v3(e);
+    t.n2 = v3(f);
+    t.uv0 = v2(a.w, b.w);
+    t.uv1 = v2(c.w, d.w);
+    t.uv2 = v2(e.w, f.w);
+    t.gn = v3(g);
+    t.hasDerivatives = g.w != 0.0f;
+    t.dpdu = v3(h);
+    t.dpdv = v3(i);
+    return t;
+}
+
 // geometry.cl:177-215 computeSurfaceInteraction (wo / traceErrorOffset are set by the caller)
 HD RTInteraction computeSurfaceInteraction(const Scene& sc, int shapeId, int primIdx, float bu, float bv) {
     RTInteraction si;
+    if (sc.triShade) {      // the same arithmetic, its triangle-only half read back from the per-triangle record
+        const RTShape* shp = sc.shapes + shapeId;
+        const TriShade t = loadTriShade(sc.triShade + 9 * (size_t)(shp->startIdx / 3u + (uint32_t)primIdx));
+        const float w = 1.0f - bu - bv;
+        si.p = t.p0 * w + t.p1 * bu + t.p2 * bv;
+        si.uv = t.uv0 * w + t.uv1 * bu + t.uv2 * bv;
+        si.gn = t.gn;
+        si.sn = normalize(t.n0 * w + t.n1 * bu + t.n2 * bv);
+        if (t.hasDerivatives) {
+            si.dpdu = t.dpdu;
+            si.dpdv = t.dpdv;
+        } else {
+            si.dpdu = normalize(computeOrthogonalVector(si.sn));
+            si.dpdv = normalize(cross(si.sn, si.dpdu));
+        }
+        si.sdpdu = normalize(si.dpdu - dot(si.sn, si.dpdu) * si.sn);
+        si.sdpdv = normalize(si.dpdv - dot(si.sn, si.dpdv) * si.sn - dot(si.sdpdu, si.dpdv) * si.sdpdu);
+        si.shapeIdx = shapeId;
+        si.wo = v3(0.f);
+        si.traceErrorOffset = 0.f;
+        return si;
+    }
     const RTShape* shape = sc.shapes + shapeId;
     uint32_t i0, i1, i2;
     V3 p0, p1, p2;

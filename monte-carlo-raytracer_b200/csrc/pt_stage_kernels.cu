@@ -42,6 +42,7 @@ __device__ __forceinline__ Scene make_scene2(const PtState& s) {
     sc.camera = (const RTPinholeCamera*)s.camera;
     sc.sobolMatrices = s.sobol;
     sc.materialAlpha = nullptr;   // the stage-wise kernels evaluate roughnessToAlpha per lookup, like the reference
+    sc.triShade = nullptr;        // ... and walk shape -> indices -> vertices per vertex, like the reference
     sc.numLights = s.numLights;
     sc.staged = 0;
     return sc;
@@ -310,6 +311,23 @@ __global__ void k_selftest_fdiv(const float* __restrict__ a, const float* __rest
 cudaError_t launch_selftest_fdiv(const float* a, const float* b, float* shortcut, float* plain, int n, cudaStream_t stream) {
     if (n <= 0) return cudaSuccess;
     k_selftest_fdiv<<<(n + 255) / 256, 256, 0, stream>>>(a, b, shortcut, plain, n);
+    return cudaGetLastError();
+}
+
+// per-triangle shading records (pt_scene.cuh: TriShade): one thread per scene triangle, `tri_shape` names its RTShape
+__global__ void __launch_bounds__(256)
+k_build_tri_shade(PtState s, const int* __restrict__ tri_shape, float4* __restrict__ records, int n_tris) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tris) return;
+    Scene sc = make_scene2(s);
+    sc.triShade = nullptr;
+    const int shapeId = tri_shape[t];
+    const RTShape* shape = sc.shapes + shapeId;
+    storeTriShade(records + 9 * (size_t)t, computeTriShade(sc, shapeId, t - (int)(shape->startIdx / 3u)));
+}
+cudaError_t launch_build_tri_shade(const PtState& s, const int* tri_shape, float4* records, int n_tris, cudaStream_t stream) {
+    if (n_tris <= 0) return cudaSuccess;
+    k_build_tri_shade<<<(n_tris + 255) / 256, 256, 0, stream>>>(s, tri_shape, records, n_tris);
     return cudaGetLastError();
 }
 

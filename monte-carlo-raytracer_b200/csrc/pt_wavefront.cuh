@@ -22,6 +22,7 @@ __device__ __forceinline__ Scene make_scene(const PtState& s) {
     sc.camera = (const RTPinholeCamera*)s.camera;
     sc.sobolMatrices = s.sobol;
     sc.materialAlpha = s.material_alpha;
+    sc.triShade = s.tri_shade;
     sc.numLights = s.numLights;
     sc.staged = 0;
     return sc;

@@ -77,6 +77,8 @@ struct ptb_context {
     int snap_next = 0;
     int halves = 2;
     int num_materials = 0;
+    int num_scene_tris = 0;                       // triangles covered by the per-triangle shading records (0 = none)
+    const int* d_tri_shape = nullptr;
     // Frames in flight (ptb_set_frames_in_flight): with D > 1 consecutive ptb_pt_render_sample calls run on D side
     // streams with their own wavefront state, so that the latency chain of one frame (the few long rays that keep
     // every traversal launch alive, profiles/r01_c5_tiles.md) is filled by the next frames' work.  ptb_accumulate
@@ -474,6 +476,46 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
         c->num_materials = d->num_materials;
         PTB_CUDA(mcrt::launch_material_alpha(c->st.materials, (float2*)a, d->num_materials, c->stream));
     }
+    // per-triangle shading records: index-array order, so a hit's (shape, prim) addresses startIdx / 3 + prim
+    c->st.tri_shade = nullptr;
+    c->num_scene_tris = 0;
+    c->d_tri_shape = nullptr;
+    static const int tri_records = getenv("MCRT_TRI_RECORDS") ? atoi(getenv("MCRT_TRI_RECORDS")) : 1;
+    if (tri_records && d->num_shapes > 0 && d->num_indices >= 3) {
+        struct ShapeHdr {      // RTShape, kernel_data.h:36-52
+            float m[32];
+            uint32_t startIdx, startVertex, numTriangles;
+            int materialId, lightID;
+            float area;
+            int pad[2];
+        };
+        static_assert(sizeof(ShapeHdr) == 160, "RTShape");
+        const ShapeHdr* sh = (const ShapeHdr*)d->shapes;
+        const int64_t n_tris = d->num_indices / 3;
+        std::vector<int> tri_shape((size_t)n_tris, -1);
+        bool ok = true;
+        for (int i = 0; i < d->num_shapes && ok; ++i) {
+            if (sh[i].startIdx % 3u) ok = false;
+            const int64_t first = sh[i].startIdx / 3u;
+            if (first + (int64_t)sh[i].numTriangles > n_tris) ok = false;
+            for (int64_t t = first; ok && t < first + (int64_t)sh[i].numTriangles; ++t) {
+                if (tri_shape[(size_t)t] != -1) ok = false;      // shapes sharing index ranges: records would be ambiguous
+                tri_shape[(size_t)t] = i;
+            }
+        }
+        for (int64_t t = 0; ok && t < n_tris; ++t)
+            if (tri_shape[(size_t)t] < 0) tri_shape[(size_t)t] = 0, ok = ok;   // unreferenced triangles: any shape, never read
+        if (ok) {
+            const void* ts = nullptr;
+            if ((rc = upload(c, "tri_shape", tri_shape.data(), (size_t)n_tris * 4, &ts))) return rc;
+            void* rec = nullptr;
+            if ((rc = alloc_into(c->scene_bufs, "tri_shade", (size_t)n_tris * 144, false, c->stream, &rec))) return rc;
+            c->d_tri_shape = (const int*)ts;
+            c->num_scene_tris = (int)n_tris;
+            PTB_CUDA(mcrt::launch_build_tri_shade(c->st, c->d_tri_shape, (float4*)rec, c->num_scene_tris, c->stream));
+            c->st.tri_shade = (const float4*)rec;
+        }
+    }
     c->st.numLights = d->num_lights;
     c->st.numShapes = d->num_shapes;
     c->st.numMaterials = d->num_materials;
@@ -497,6 +539,8 @@ int ptb_update_scene_array(ptb_context* c, const char* array, const void* data, 
     if (rc) return rc;
     if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaMemcpyAsync(it->second.p, data, bytes, cudaMemcpyHostToDevice, c->stream));
+    if (name == "shapes" && c->st.tri_shade)      // transforms changed: the per-triangle records follow
+        PTB_CUDA(mcrt::launch_build_tri_shade(c->st, c->d_tri_shape, (float4*)c->st.tri_shade, c->num_scene_tris, c->stream));
     if (name == "materials")
         PTB_CUDA(mcrt::launch_material_alpha(c->st.materials, (float2*)c->st.material_alpha, c->num_materials, c->stream));
     if (!c->slots.empty()) PTB_CUDA(cudaStreamSynchronize(c->stream));   // frames on side streams must see the update

@@ -147,7 +147,7 @@ def run(api, scene, stream, res=4096, reps=3):
         rb, hb, ob, cb = api.CreateBuffer(n * 48, rays), api.CreateBuffer(n * 32), api.CreateBuffer(n * 4), api.CreateBuffer(n * 8)
         t_c = _time(lambda: api.QueryIntersection(rb, n, hb), stream, reps)
         t_a = _time(lambda: api.QueryOcclusion(rb, n, ob), stream, reps)
-        api.QueryIntersectionCounted(rb, n, hb, cb).Wait()
+        api.QueryIntersectionCounted(rb, n, hb, cb)
         cnt, ev = api.MapBuffer(cb, rr.MAP_READ, 0, n * 8, dtype=np.int32)
         ev.Wait()
         c = cnt.reshape(-1, 2).astype(np.float64).mean(0)
