@@ -134,8 +134,11 @@ int ptb_set_frames_in_flight(ptb_context* ctx, int depth);
  * bounce) (samplers.cl:75-84), so which light a vertex will sample and which half of the lobe-selection variate it
  * will draw are known before its ray is traced: 1 = queues of bounces >= 1 are bucketed by that key (warps of the
  * shade kernel take the same light / lobe branches), 2 = bounce 0 as well, 3 = bucketed inside each thread block's
- * chunk of the queue only (keeps neighbouring pixels together: texture / geometry locality), 0 = push order.
- * Per-sample results are identical in all modes. */
+ * chunk of the queue only (keeps neighbouring pixels together: texture / geometry locality), 0 = push order,
+ * 4 = the consumer sorts: every thread block of the shade kernel sorts its 2048-entry chunk of the queue in shared
+ * memory by (light type, lobe half, material id), drops the rays that missed, and stages the scene's small tables in
+ * shared memory with bulk asynchronous copies (csrc/pt_kernels.cu: shade_sorted; measured slower than 3 on the
+ * benchmark scene, profiles/r02_shade.md).  Per-sample results are identical in all modes. */
 #define PTB_DEFAULT_COHERENCE 3
 /* Opt-in estimator switches of ptb_pt_render_sample (default 0 = the reference's estimator, PathTracing.cl:52-184,
  * which has neither): Russian roulette from the third vertex on, and power-heuristic MIS between next-event

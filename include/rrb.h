@@ -127,9 +127,19 @@ typedef struct rrb_stats {
                                      bvh.builder = "lbvh": Morton codes, radix sort, radix tree, wide collapse as CUDA
                                      kernels -- Radeon Rays' own GPU builder sits behind the same option,
                                      intersector_hlbvh.cpp); 0 for the multi-threaded host SAH builder */
-    int64_t num_levels;         /* breadth-first levels of the tree when known (device build or "bvh.refit"), else 0 */
+    int64_t num_levels;         /* breadth-first levels of the tree when known (device build or "bvh.refit"), else 0;
+                                   two-level world: levels of the top-level tree */
+    int64_t two_level;          /* 1 when the committed world is a top-level tree over shapes with one bottom-level
+                                   tree per distinct mesh (instances attached, or option "bvh.force2level"), else 0 */
+    int64_t num_instances;      /* shapes in the top level */
+    int64_t two_level_rebuilds; /* commits that (re)laid out the bottom-level trees */
+    int64_t top_level_updates;  /* commits that only rebuilt the top level and the shape table (transform / id changes) */
 } rrb_stats;
 int rrb_get_stats(rrb_api* api, rrb_stats* out);
+/* The shape table of a two-level world (NULL / 0 for a flat one): 64-byte records in the top-level tree's leaf order,
+ * rows 0..2 of the world -> object matrix, bottom-level root node, shape id (csrc/bvh8.h: InstanceRecord).  Like
+ * rrb_get_bvh, for the path-tracer half of the library, which traces against the same structure. */
+int rrb_get_instances(rrb_api* api, const void** instances, int* num_instances);
 /* Instrumented query: per-ray visited-node and tested-triangle counts into int32[2*numrays]. */
 int rrb_query_intersection_counted(rrb_api* api, const rrb_buffer* rays, int numrays, rrb_buffer* hits,
                                    rrb_buffer* counts);

@@ -51,15 +51,29 @@ struct Bvh8 {
     float scene_max[3] = {0, 0, 0};
 };
 
+// One attached shape of the two-level structure (the role of the `Shape` record of Radeon Rays' two-level kernel,
+// intersect_bvh2level_skiplinks.cl:75-93): rows 0..2 of the world -> object matrix, the node index of the root of its
+// mesh's bottom-level tree, and the id hits report.  64 bytes, in the order of the top-level tree's leaves.
+struct InstanceRecord {
+    float minv[12];
+    int blas_root;
+    int shape_id;
+    int pad[2];
+};
+
 struct BuildOptions {
     bool use_sah = true;          // bvh.builder = sah | median
     int num_bins = 16;            // bins per axis for the binned SAH sweep
     float traversal_cost = 1.2f;  // relative to one triangle test, for the BVH2 leaf decision
     int num_threads = 0;          // 0 = hardware concurrency
     bool depth_guard = true;      // rebuild with balanced splits when the tree is deeper than the traversal stack allows
+    int max_levels = 19;          // ... i.e. than this many levels (two stack entries per level, 40-entry stack)
 };
 
 // Builds the compressed wide BVH over all faces of all meshes.  Throws std::runtime_error.
 void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& opt, Bvh8& out);
+// The same tree over `n` axis-aligned boxes (6 floats each: lo.xyz, hi.xyz) -- the top level of the two-level
+// structure.  Leaf record i (12 floats, in out.triangles) carries the index of its box in the int bits of word 3.
+void build_bvh8_boxes(const float* boxes, int n, const BuildOptions& opt, Bvh8& out);
 
 }  // namespace mcrt

@@ -234,6 +234,9 @@ struct WideNode {
 
 }  // namespace
 
+static void build_core(Builder& B, const std::vector<float>& tri, const std::vector<int32_t>& tri_mesh_in, size_t N,
+                       const BuildOptions& opt, Bvh8& out);
+
 void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& opt, Bvh8& out) {
     // ---- 1. gather world-space triangles
     int64_t total = 0;
@@ -279,12 +282,46 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
         }
     }
 
+    build_core(B, tri, tri_mesh_in, N, opt, out);
+}
+
+// Top level of the two-level structure: a tree over `n` boxes (lo.xyz, hi.xyz each).  The leaf "triangle" records of
+// the result carry, in the int bits of word 3, the index of the box they stand for, in emission order: the caller
+// lays its instance table out in that order, so a leaf's record index IS the instance index.
+void build_bvh8_boxes(const float* boxes, int n, const BuildOptions& opt, Bvh8& out) {
+    if (n <= 0) throw std::runtime_error("Scene is empty.");
+    const size_t N = (size_t)n;
+    std::vector<float> rec(12 * N, 0.0f);
+    std::vector<int32_t> owner(N);
+    Builder B(opt);
+    B.pbox.resize(N);
+    B.pcent.resize(3 * N);
+    B.prim.resize(N);
+    for (size_t i = 0; i < N; ++i) {
+        Box b;
+        for (int a = 0; a < 3; ++a) {
+            b.lo[a] = boxes[6 * i + a];
+            b.hi[a] = boxes[6 * i + 3 + a];
+            if (!std::isfinite(b.lo[a]) || !std::isfinite(b.hi[a])) throw std::runtime_error("non-finite instance bounds");
+        }
+        B.pbox[i] = b;
+        for (int a = 0; a < 3; ++a) B.pcent[3 * i + a] = 0.5f * (b.lo[a] + b.hi[a]);
+        B.prim[i] = (int)i;
+        const int idx = (int)i;
+        std::memcpy(&rec[12 * i + 3], &idx, 4);
+        owner[i] = idx;
+    }
+    build_core(B, rec, owner, N, opt, out);
+}
+
+static void build_core(Builder& B, const std::vector<float>& tri, const std::vector<int32_t>& tri_mesh_in, size_t N,
+                       const BuildOptions& opt, Bvh8& out) {
     // The traversal keeps at most two stack entries per wide level (a node group and a postponed triangle group) on a
     // 40-entry stack (traverse.cuh), so a tree may have at most kMaxWideLevels levels -- the bound the device builder
     // enforces too (lbvh_build.h).  A SAH tree over strongly non-uniform input can be deeper: it is then rebuilt with
     // equal-count splits below a binary depth that is lowered until the wide tree fits (0 = balanced everywhere, which
     // always fits: ceil(log2(2^30 / 2) / 3) + 1 = 11 levels).
-    enum { kMaxWideLevels = 19 };
+    const int kMaxWideLevels = opt.max_levels;
     static const int caps[] = {std::numeric_limits<int>::max(), 40, 24, 12, 0};
     for (int attempt = 0;; ++attempt) {
     B.sah_depth_cap = caps[attempt];

@@ -130,19 +130,24 @@ __device__ __forceinline__ void fetch_closest_ray(const PtState& s, const uint32
     r.dx = d.x; r.dy = d.y; r.dz = d.z;
     r.mask = -1;   // setRay(): extra = 0xFFFFFFFF (kernel_data.h:434-440)
 }
+template <bool TWO_LEVEL = false>
 __device__ __forceinline__ void store_closest_hit(const PtState& s, const uint32_t* __restrict__ queue, unsigned idx,
-                                                  const Ray& r, const TravState& st) {
+                                                  const Ray& rw, const TravState& st) {
     const uint32_t px = queue[idx];
     int4 h = make_int4(-1, -1, 0, 0);
     if (st.best_tri >= 0) {
         const float4 v0 = __ldg(s.tris + 3 * (size_t)st.best_tri + 0);
         const float4 v1 = __ldg(s.tris + 3 * (size_t)st.best_tri + 1);
         const float4 v2 = __ldg(s.tris + 3 * (size_t)st.best_tri + 2);
+        // two levels: the hit point and its barycentrics are taken in the object space the triangle was hit in, like
+        // the reference's two-level kernel (intersect_bvh2level_skiplinks.cl:205-222)
+        const Ray r = TWO_LEVEL ? hit_space_ray(s.instances, rw, st.best_inst) : rw;
         const float hx = add_(r.ox, mul_(st.closest, r.dx));
         const float hy = add_(r.oy, mul_(st.closest, r.dy));
         const float hz = add_(r.oz, mul_(st.closest, r.dz));
         const float2 uv = barycentrics_ref(hx, hy, hz, v0, v1, v2);
-        h = make_int4(__float_as_int(v0.w), __float_as_int(v1.w), __float_as_int(uv.x), __float_as_int(uv.y));
+        h = make_int4(TWO_LEVEL ? st.best_sid : __float_as_int(v0.w), __float_as_int(v1.w), __float_as_int(uv.x),
+                      __float_as_int(uv.y));
     }
     s.hit[px] = h;
 }
@@ -165,40 +170,47 @@ __device__ __forceinline__ void resolve_shadow(const PtState& s, unsigned idx, c
     s.radiance[px] = r;
 }
 
-__global__ void __launch_bounds__(128, 8)
+// TWO_LEVEL: the world is a top-level tree over shapes with per-mesh bottom-level trees (rrb_commit with instances);
+// separate instantiations, so the flat kernels keep their 64 registers / 8 CTAs per SM.
+template <bool TWO_LEVEL>
+__global__ void __launch_bounds__(128, TWO_LEVEL ? 6 : 8)
 k_trace_closest(PtState s, int cur) {
     const unsigned count = s.cnt[cur];
     const uint32_t* __restrict__ queue = s.queue[cur];
-    persistent_trace<false>(
+    persistent_trace<false, false, TWO_LEVEL>(
         s.nodes, s.tris, count, s.cnt + 3,
         [&](unsigned idx, Ray& r) {
             fetch_closest_ray(s, queue, idx, r);
             return false;
         },
-        [&](unsigned idx, const Ray& r, const TravState& st) { store_closest_hit(s, queue, idx, r, st); }, s.numNodes, s.stageTop);
+        [&](unsigned idx, const Ray& r, const TravState& st) { store_closest_hit<TWO_LEVEL>(s, queue, idx, r, st); },
+        s.numNodes, s.stageTop, s.instances);
 }
 
 // any-hit traversal fused with the reference's ShadowPass; shadow rays of bounce parity `sh`
-__global__ void __launch_bounds__(128, 8)
+template <bool TWO_LEVEL>
+__global__ void __launch_bounds__(128, TWO_LEVEL ? 6 : 8)
 k_trace_shadow(PtState s, int sh, int bounce) {
     const unsigned count = s.cnt[5 + sh];
-    persistent_trace<true>(
+    persistent_trace<true, false, TWO_LEVEL>(
         s.nodes, s.tris, count, s.cnt + 4,
         [&](unsigned idx, Ray& r) {
             fetch_shadow_ray(s, idx, r);
             return true;
         },
-        [&](unsigned idx, const Ray&, const TravState& st) { resolve_shadow(s, idx, st, bounce); }, s.numNodes, s.stageTop);
+        [&](unsigned idx, const Ray&, const TravState& st) { resolve_shadow(s, idx, st, bounce); }, s.numNodes, s.stageTop,
+        s.instances);
 }
 
 // One launch for the two ray sets that are ready after a shade stage: the closest-hit rays of the next bounce
 // (queue `cur`) and the shadow rays of the bounce just shaded (parity `sh`).  They are independent of each other, so
 // sharing the persistent warps removes one drain-out tail and one launch per bounce.  Long rays first.
-__global__ void __launch_bounds__(128, 8)
+template <bool TWO_LEVEL>
+__global__ void __launch_bounds__(128, TWO_LEVEL ? 6 : 8)
 k_trace_mixed(PtState s, int cur, int sh, int sh_bounce) {
     const unsigned n_closest = s.cnt[cur], n_shadow = s.cnt[5 + sh];
     const uint32_t* __restrict__ queue = s.queue[cur];
-    persistent_trace<false, true>(
+    persistent_trace<false, true, TWO_LEVEL>(
         s.nodes, s.tris, n_closest + n_shadow, s.cnt + 3,
         [&](unsigned idx, Ray& r) {
             if (idx < n_closest) {
@@ -209,10 +221,10 @@ k_trace_mixed(PtState s, int cur, int sh, int sh_bounce) {
             return true;
         },
         [&](unsigned idx, const Ray& r, const TravState& st) {
-            if (idx < n_closest) store_closest_hit(s, queue, idx, r, st);
+            if (idx < n_closest) store_closest_hit<TWO_LEVEL>(s, queue, idx, r, st);
             else resolve_shadow(s, idx - n_closest, st, sh_bounce);
         },
-        s.numNodes, s.stageTop);
+        s.numNodes, s.stageTop, s.instances);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -360,7 +372,7 @@ k_shade_est(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// shade, sorted: the default (coherence mode 3)
+// shade, sorted (coherence mode 4; opt-in -- measured slower than mode 3 on the benchmark, see the end of this comment)
 // ---------------------------------------------------------------------------------------------
 // One CTA takes a CHUNK of consecutive queue entries (neighbouring pixels: they share geometry and texels), SORTS it
 // in shared memory and shades it in sorted order, warp by warp:
@@ -378,6 +390,12 @@ k_shade_est(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
 // (geometry.cl:181, lights.cl:104, materials.cl:78).
 // Survivors are collected in shared memory and appended to the next queue as ONE contiguous run per chunk, so
 // neighbouring pixels stay neighbours.  Per-path results do not depend on the order (bitwise: the coherence tests).
+// MEASURED (C3 1080p, profiles/r02_shade.md): the sort does what it was built for -- 26.7 of 32 lanes active instead
+// of 17.9, 29 % fewer warp instructions per launch -- and the launch still takes LONGER (219 vs 189 us, bounce-1 half
+// frame): a warp's lanes now come from all over the 2048-pixel chunk, the L1 hit rate falls from 53 % to 31 % and the
+// exposed memory latency (long_scoreboard + barrier + no_instructions: 62 % of the stall samples) grows by more than
+// the instruction stream shrinks; shade 1.94 -> 2.29 ms per step.  Staging the tables changes nothing measurable
+// (2.34 vs 2.41 ms without / with).  So it is an option (ptb_set_coherence(4)), not the default.
 #ifndef PT_SORT_CHUNK
 #define PT_SORT_CHUNK 2048
 #endif
@@ -657,6 +675,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         cudaStreamWaitEvent(overlap->stream, overlap->fork, 0);
     }
     int cur[2] = {0, 0};
+    const bool two_level = s.instances != nullptr;
     // the sorted shade kernel stages the small scene tables in shared memory when they fit
     const unsigned table_bytes = staged_tables(s).total();
     static const int stage_enabled = env_int("MCRT_STAGE_TABLES", 1);
@@ -690,13 +709,15 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                 if (b == 0) {
                     // experiment knob: start the second half one stage behind the first
                     if (h == 1 && stagger) cudaStreamWaitEvent(H.stream, overlap->stagger, 0);
-                    k_trace_closest<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h]);
+                    if (two_level) k_trace_closest<true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h]);
+                    else k_trace_closest<false><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h]);
                     if (h == 0 && nh == 2 && stagger) cudaEventRecord(overlap->stagger, H.stream);
                 } else {
-                    k_trace_mixed<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1, b - 1);
+                    if (two_level) k_trace_mixed<true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1, b - 1);
+                    else k_trace_mixed<false><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1, b - 1);
                 }
                 if (timer) timer->mark(h, H.stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
-                if (s.coherence == 3) {
+                if (s.coherence == 4) {
                     const int nb = min(sms, (H.n + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK);
                     if (s.estimator)
                         k_shade_sorted_est<<<nb, PT_SHADE_BLOCK, sorted_smem, H.stream>>>(H.s, cur[h], frame, b, max_depth, stage_tables);
@@ -715,7 +736,8 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
             const Half& H = half[h];
             k_sample_end<<<1, 32, 0, H.stream>>>(H.s.cnt, H.s.stats, max_depth - 1);
             if (timer) timer->mark(h, H.stream);
-            k_trace_shadow<<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1, max_depth - 1);
+            if (two_level) k_trace_shadow<true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1, max_depth - 1);
+            else k_trace_shadow<false><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1, max_depth - 1);
             if (timer) timer->mark(h, H.stream, StageTimer::TRACE_SHADOW);
             launches += 2;
         }

@@ -34,6 +34,7 @@ struct PtState {
     // acceleration structure
     const uint4* nodes;
     const float4* tris;
+    const float4* instances;   // two-level world (rrb_commit with instances): the shape table, 4 float4 per shape; else NULL
     int numNodes;         // nodes in the tree; the first MCRT_TOP_NODES are staged in shared memory by the traversal CTAs
     int stageTop;         // 0 = every node from global memory (experiment switch MCRT_STAGE_TOP=0)
     // SoA wavefront state

@@ -32,13 +32,14 @@ __device__ __forceinline__ Scene make_scene(const PtState& s) {
 // persistent traversal over a queue
 // ---------------------------------------------------------------------------------------------
 // MIXED: fetch() returns the kind of the ray it loaded (true = any hit); otherwise its result is ignored.
-template <bool ANY_HIT, bool MIXED = false, typename Fetch, typename Store>
+template <bool ANY_HIT, bool MIXED = false, bool TWO_LEVEL = false, typename Fetch, typename Store>
 __device__ __forceinline__ void persistent_trace(const uint4* nodes, const float4* tris, unsigned count,
                                                  unsigned int* work_counter, Fetch fetch, Store store,
-                                                 int num_nodes = 0, int stage_top = 0) {
+                                                 int num_nodes = 0, int stage_top = 0, const float4* instances = nullptr) {
     const unsigned lane = threadIdx.x & 31u;
     __shared__ TopNodes s_top;
-    Traverser<ANY_HIT, false, MIXED> trav{nodes, tris};
+    Traverser<ANY_HIT, false, MIXED, TWO_LEVEL> trav{nodes, tris};
+    trav.instances = instances;
     trav.top = s_top.nodes;
     trav.top_count = stage_top_nodes(s_top, nodes, num_nodes, stage_top);
     uint2 stack[MCRT_STACK_SIZE];

@@ -173,6 +173,9 @@ int refresh_bvh(ptb_context* c) {
     c->st.nodes = (const uint4*)nodes;
     c->st.tris = (const float4*)tris;
     c->st.numNodes = (int)std::min<int64_t>(num_nodes, 0x7fffffff);
+    const void* inst = nullptr;
+    if ((rc = rrb_get_instances(c->api, &inst, nullptr))) return pfail(rc, rrb_last_error());
+    c->st.instances = (const float4*)inst;
     static const int stage_top = getenv("MCRT_STAGE_TOP") ? atoi(getenv("MCRT_STAGE_TOP")) : 1;
     c->st.stageTop = stage_top;
     return 0;
@@ -365,7 +368,7 @@ int ptb_create(rrb_api* api, ptb_context** out) {
     c->st.camera = p;
     if (const char* v = getenv("MCRT_OVERLAP_HALVES")) c->halves = atoi(v) == 1 ? 1 : 2;   // profiling aid
     c->st.coherence = PTB_DEFAULT_COHERENCE;
-    if (const char* v = getenv("MCRT_COHERENCE")) c->st.coherence = std::max(0, std::min(3, atoi(v)));   // variant runs
+    if (const char* v = getenv("MCRT_COHERENCE")) c->st.coherence = std::max(0, std::min(4, atoi(v)));   // variant runs
     PTB_CUDA(cudaStreamCreateWithFlags(&c->overlap.stream, cudaStreamNonBlocking));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.fork, cudaEventDisableTiming));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.join, cudaEventDisableTiming));
@@ -396,7 +399,7 @@ int ptb_set_estimator(ptb_context* c, int flags) {
 }
 
 int ptb_set_coherence(ptb_context* c, int mode) {
-    if (!c || mode < 0 || mode > 3) return pfail(RRB_ERROR_INVALID_ARGUMENT, "coherence mode must be 0 .. 3");
+    if (!c || mode < 0 || mode > 4) return pfail(RRB_ERROR_INVALID_ARGUMENT, "coherence mode must be 0 .. 4");
     int rc = set_dev(c);
     if (rc) return rc;
     if ((rc = join_and_drop_frames(c))) return rc;
@@ -480,7 +483,9 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
     c->st.tri_shade = nullptr;
     c->num_scene_tris = 0;
     c->d_tri_shape = nullptr;
-    static const int tri_records = getenv("MCRT_TRI_RECORDS") ? atoi(getenv("MCRT_TRI_RECORDS")) : 1;
+    // off by default: measured neutral for the default shade kernel (1.991 vs 1.998 ms per step), +6 % for the sorted
+    // one (profiles/r02_shade.md); MCRT_TRI_RECORDS=1 or ptb_set_option-style builds switch it on
+    static const int tri_records = getenv("MCRT_TRI_RECORDS") ? atoi(getenv("MCRT_TRI_RECORDS")) : 0;
     if (tri_records && d->num_shapes > 0 && d->num_indices >= 3) {
         struct ShapeHdr {      // RTShape, kernel_data.h:36-52
             float m[32];
@@ -840,6 +845,9 @@ int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
 int ptb_bdpt_reserve(ptb_context* c, int max_depth) {
     int rc = ready(c);
     if (rc) return rc;
+    if (c->st.instances)
+        return pfail(RRB_ERROR_INVALID_ARGUMENT,
+                     "the BDPT kernels trace the flat tree only: commit the world with the option bvh.forceflat = 1");
     if ((rc = join_and_drop_frames(c))) return rc;
     if (max_depth < 1) return pfail(RRB_ERROR_INVALID_ARGUMENT, "max_depth must be >= 1");
     if (c->bdpt_depth == max_depth) return 0;

@@ -10,6 +10,8 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <cfloat>
+#include <cmath>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -100,6 +102,16 @@ struct rrb_api {
     bool last_build_on_device = false;                 // acc.type = hlbvh / bvh.builder = lbvh (lbvh_build.cu)
     std::string device_build_fallback_reason;
     std::vector<int> pool_face_prefix;                 // faces before each pooled mesh, total last
+    // two-level structure (instances in the world, or option "bvh.force2level"): one bottom-level tree per distinct
+    // base mesh in OBJECT space, a top-level tree over the shapes' world bounds, an instance table
+    bool two_level = false;
+    void* d_instances = nullptr;                       // mcrt::InstanceRecord[num_instances], top-level leaf order
+    int num_instances = 0;
+    std::map<const rrb_shape*, std::shared_ptr<mcrt::Bvh8>> blas_cache;   // meshes are immutable: built once
+    std::vector<const rrb_shape*> blas_order;          // bottom-level trees as laid out behind the top level
+    std::vector<int64_t> blas_root;                    // node index of each bottom-level root
+    int64_t tlas_capacity = 0;                         // node slots reserved in front for the top level
+    int64_t two_level_rebuilds = 0, top_level_updates = 0;
     unsigned int* d_counter = nullptr;
     std::vector<rrb_event*> event_pool;
     // staging for the host-buffer entry points
@@ -174,6 +186,13 @@ void free_refit(rrb_api* api) {
 }
 
 void free_bvh(rrb_api* api) {
+    if (api->d_instances) cudaFree(api->d_instances);
+    api->d_instances = nullptr;
+    api->num_instances = 0;
+    api->two_level = false;
+    api->blas_order.clear();
+    api->blas_root.clear();
+    api->tlas_capacity = 0;
     if (api->d_nodes) cudaFree(api->d_nodes);
     if (api->d_tris) cudaFree(api->d_tris);
     api->d_nodes = api->d_tris = nullptr;
@@ -224,7 +243,7 @@ int query_common(rrb_api* api, bool any_hit, const rrb_buffer* rays, const rrb_b
     cudaError_t e = mcrt::launch_query(any_hit, counts != nullptr, api->d_nodes, api->d_tris, rays->dptr,
                                        numrays_buf ? (const int*)numrays_buf->dptr : nullptr, numrays, out->dptr,
                                        api->d_counter, counts ? (int*)counts->dptr : nullptr, api->stream,
-                                       (int)std::min<int64_t>(api->num_nodes, 0x7fffffff));
+                                       (int)std::min<int64_t>(api->num_nodes, 0x7fffffff), api->two_level ? api->d_instances : nullptr);
     if (e != cudaSuccess) return cuda_fail(e, "traversal kernel launch");
     if (numrays > 0) api->launches++;
     return record_done(api, done);
@@ -398,16 +417,196 @@ int rrb_detach_all(rrb_api* api) {
     return RRB_OK;
 }
 
+namespace {
+
+// CalcIntersectionDevice::Preprocess (src/device/calc_intersection_device.cpp:68-106): two levels when forced, never
+// when forced flat, else whenever the world holds an instance.
+bool wants_two_level(const rrb_api* api) {
+    auto f2 = api->f32_options.find("bvh.force2level");
+    if (f2 != api->f32_options.end() && f2->second > 0.0f) return true;
+    auto ff = api->f32_options.find("bvh.forceflat");
+    if (ff != api->f32_options.end() && ff->second > 0.0f) return false;
+    for (const rrb_shape* s : api->world)
+        if (s->is_instance) return true;
+    return false;
+}
+
+// Two-level commit.  Takes the role of IntersectorTwoLevel::Process (src/intersector/intersector_2level.cpp:257-520):
+// a bottom-level tree per distinct mesh in object space (built once per mesh and kept: meshes are immutable), a
+// top-level tree over the world bounds of every attached shape, and a shape table holding each shape's id, inverse
+// matrix and bottom-level root.  A commit that only changed transforms / ids rebuilds the top level and the table
+// (microseconds) and leaves the bottom levels where they are on the device.
+int commit_two_level(rrb_api* api, std::chrono::steady_clock::time_point t0) {
+    mcrt::BuildOptions opt;
+    auto b = api->str_options.find("bvh.builder");
+    opt.use_sah = !(b != api->str_options.end() && b->second == "median");
+    // stack budget (traverse.cuh): two entries per level of either tree + the two groups parked when a ray enters an
+    // instance must fit the 40-entry stack
+    mcrt::BuildOptions blas_opt = opt, tlas_opt = opt;
+    blas_opt.max_levels = 13;
+    tlas_opt.max_levels = 5;
+    // distinct base meshes in world order
+    std::vector<const rrb_shape*> order;
+    std::vector<int> blas_of_shape;
+    std::map<const rrb_shape*, int> index_of;
+    for (const rrb_shape* s : api->world) {
+        const rrb_shape* g = s->is_instance ? s->base : s;
+        if (!g || g->indices.empty()) {
+            blas_of_shape.push_back(-1);
+            continue;
+        }
+        auto it = index_of.find(g);
+        if (it == index_of.end()) {
+            it = index_of.emplace(g, (int)order.size()).first;
+            order.push_back(g);
+        }
+        blas_of_shape.push_back(it->second);
+    }
+    if (order.empty()) return fail(RRB_ERROR_EMPTY_SCENE, "Scene is empty.");
+    // bottom levels (cached per mesh)
+    for (const rrb_shape* g : order) {
+        if (api->blas_cache.count(g)) continue;
+        mcrt::BuildInputMesh m;
+        m.vertices = g->vertices.data();
+        m.vnum = (int)(g->vertices.size() / 3);
+        m.vstride = 12;
+        m.indices = g->indices.data();
+        m.istride = 12;
+        m.numfaces = (int)(g->indices.size() / 3);
+        m.shape_id = 0;                              // the shape table names the shape, not the triangle record
+        std::memcpy(m.m, kIdentity, sizeof(m.m));
+        auto bvh = std::make_shared<mcrt::Bvh8>();
+        try {
+            mcrt::build_bvh8(std::vector<mcrt::BuildInputMesh>(1, m), blas_opt, *bvh);
+        } catch (const std::exception& ex) {
+            return fail(RRB_ERROR_INVALID_ARGUMENT, ex.what());
+        }
+        api->blas_cache[g] = bvh;
+    }
+    // instances: world bounds of the transformed vertices, slightly inflated (the hit is found in object space:
+    // the two spaces round differently)
+    struct Inst {
+        const rrb_shape* s;
+        int blas;
+    };
+    std::vector<Inst> inst;
+    std::vector<float> boxes;
+    for (size_t w = 0; w < api->world.size(); ++w) {
+        if (blas_of_shape[w] < 0) continue;
+        const rrb_shape* s = api->world[w];
+        const rrb_shape* g = s->is_instance ? s->base : s;
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (size_t v = 0; v + 2 < g->vertices.size(); v += 3) {
+            const float x = g->vertices[v], y = g->vertices[v + 1], z = g->vertices[v + 2];
+            for (int a = 0; a < 3; ++a) {
+                const float* r = s->m + 4 * a;
+                const float c = ((r[0] * x + r[1] * y) + r[2] * z) + r[3];
+                lo[a] = std::min(lo[a], c);
+                hi[a] = std::max(hi[a], c);
+            }
+        }
+        for (int a = 0; a < 3; ++a) {
+            const float pad = 1e-5f * (hi[a] - lo[a]) + 4.0f * FLT_EPSILON * std::max(std::fabs(lo[a]), std::fabs(hi[a]));
+            lo[a] -= pad;
+            hi[a] += pad;
+        }
+        boxes.insert(boxes.end(), lo, lo + 3);
+        boxes.insert(boxes.end(), hi, hi + 3);
+        inst.push_back({s, blas_of_shape[w]});
+    }
+    mcrt::Bvh8 tlas;
+    try {
+        mcrt::build_bvh8_boxes(boxes.data(), (int)inst.size(), tlas_opt, tlas);
+    } catch (const std::exception& ex) {
+        return fail(RRB_ERROR_INVALID_ARGUMENT, ex.what());
+    }
+    const bool same_layout = api->two_level && api->d_nodes && api->blas_order == order &&
+                             tlas.num_nodes <= api->tlas_capacity && (int)inst.size() == api->num_instances;
+    RRB_CUDA(cudaStreamSynchronize(api->stream));
+    if (!same_layout) {
+        free_bvh(api);
+        api->tlas_capacity = std::max<int64_t>((int64_t)inst.size(), tlas.num_nodes);
+        int64_t nodes = api->tlas_capacity, tris = 0;
+        api->blas_root.clear();
+        for (const rrb_shape* g : order) {
+            api->blas_root.push_back(nodes);
+            nodes += api->blas_cache[g]->num_nodes;
+            tris += api->blas_cache[g]->num_tris;
+        }
+        std::vector<uint32_t> all_nodes((size_t)nodes * 20, 0u);
+        std::vector<float> all_tris((size_t)tris * 12);
+        int64_t tri_at = 0;
+        for (size_t k = 0; k < order.size(); ++k) {
+            const mcrt::Bvh8& bv = *api->blas_cache[order[k]];
+            uint32_t* dst = all_nodes.data() + (size_t)api->blas_root[k] * 20;
+            std::memcpy(dst, bv.nodes.data(), bv.nodes.size() * sizeof(uint32_t));
+            for (int64_t n = 0; n < bv.num_nodes; ++n) {      // child and triangle bases become absolute
+                dst[20 * n + 4] += (uint32_t)api->blas_root[k];
+                dst[20 * n + 5] += (uint32_t)tri_at;
+            }
+            std::memcpy(all_tris.data() + (size_t)tri_at * 12, bv.triangles.data(), bv.triangles.size() * sizeof(float));
+            tri_at += bv.num_tris;
+        }
+        RRB_CUDA(cudaMalloc(&api->d_nodes, all_nodes.size() * sizeof(uint32_t)));
+        RRB_CUDA(cudaMalloc(&api->d_tris, std::max<size_t>(all_tris.size(), 12) * sizeof(float)));
+        RRB_CUDA(cudaMalloc(&api->d_instances, inst.size() * sizeof(mcrt::InstanceRecord)));
+        RRB_CUDA(cudaMemcpyAsync(api->d_nodes, all_nodes.data(), all_nodes.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                                 api->stream));
+        RRB_CUDA(cudaMemcpyAsync(api->d_tris, all_tris.data(), all_tris.size() * sizeof(float), cudaMemcpyHostToDevice,
+                                 api->stream));
+        RRB_CUDA(cudaStreamSynchronize(api->stream));
+        api->num_nodes = nodes;
+        api->num_tris = tris;
+        api->num_instances = (int)inst.size();
+        api->blas_order = order;
+        api->two_level = true;
+        api->two_level_rebuilds++;
+    } else {
+        api->top_level_updates++;
+    }
+    // top level (front of the node array) + the shape table in the top level's leaf order
+    std::vector<mcrt::InstanceRecord> table(inst.size());
+    for (size_t i = 0; i < inst.size(); ++i) {
+        int src;
+        std::memcpy(&src, &tlas.triangles[12 * i + 3], 4);
+        const Inst& in = inst[(size_t)src];
+        mcrt::InstanceRecord& r = table[i];
+        std::memcpy(r.minv, in.s->minv, 12 * sizeof(float));
+        r.blas_root = (int)api->blas_root[(size_t)in.blas];
+        r.shape_id = in.s->id;
+        r.pad[0] = r.pad[1] = 0;
+    }
+    RRB_CUDA(cudaMemcpyAsync(api->d_nodes, tlas.nodes.data(), tlas.nodes.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                             api->stream));
+    RRB_CUDA(cudaMemcpyAsync(api->d_instances, table.data(), table.size() * sizeof(mcrt::InstanceRecord),
+                             cudaMemcpyHostToDevice, api->stream));
+    RRB_CUDA(cudaStreamSynchronize(api->stream));
+    api->level_offsets = tlas.level_offsets;
+    api->world_changed = false;
+    api->last_build_on_device = false;
+    for (const rrb_shape* s : api->world) {
+        const_cast<rrb_shape*>(s)->changed = false;
+        if (s->base) const_cast<rrb_shape*>(s->base)->changed = false;
+    }
+    api->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return RRB_OK;
+}
+
+}  // namespace
+
 int rrb_commit(rrb_api* api) {
     if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
     if (api->world.empty()) return fail(RRB_ERROR_EMPTY_SCENE, "Scene is empty.");
     bool dirty = api->world_changed || !api->d_nodes;
     for (const rrb_shape* s : api->world) dirty = dirty || s->changed || (s->base && s->base->changed);
+    if (wants_two_level(api) != api->two_level) dirty = true;
     if (!dirty) return RRB_OK;
     int rc = set_device(api);
     if (rc) return rc;
     auto t0 = std::chrono::steady_clock::now();
     api->last_commit_was_refit = false;
+    if (wants_two_level(api)) return commit_two_level(api, t0);
+    if (api->two_level) free_bvh(api);      // back from two levels to the flat tree
     // Option "bvh.refit" (an extension; the reference always rebuilds, intersector_lds.cpp:166): when the world
     // holds the same shapes as at the last full build and only transforms / ids changed, keep the topology
     // and refit on the device.
@@ -824,6 +1023,10 @@ int rrb_get_stats(rrb_api* api, rrb_stats* out) {
     out->last_commit_refit = api->last_commit_was_refit ? 1 : 0;
     out->last_build_on_device = api->last_build_on_device ? 1 : 0;
     out->num_levels = api->level_offsets.empty() ? 0 : (int64_t)api->level_offsets.size() - 1;
+    out->two_level = api->two_level ? 1 : 0;
+    out->num_instances = api->two_level ? api->num_instances : 0;
+    out->two_level_rebuilds = api->two_level_rebuilds;
+    out->top_level_updates = api->top_level_updates;
     return RRB_OK;
 }
 
@@ -834,6 +1037,13 @@ int rrb_get_bvh(rrb_api* api, const void** nodes, const void** triangles, int64_
     if (triangles) *triangles = api->d_tris;
     if (num_nodes) *num_nodes = api->num_nodes;
     if (num_tris) *num_tris = api->num_tris;
+    return RRB_OK;
+}
+
+int rrb_get_instances(rrb_api* api, const void** instances, int* num_instances) {
+    if (!api) return fail(RRB_ERROR_INVALID_ARGUMENT, "null api");
+    if (instances) *instances = api->two_level ? api->d_instances : nullptr;
+    if (num_instances) *num_instances = api->two_level ? api->num_instances : 0;
     return RRB_OK;
 }
 

@@ -18,16 +18,18 @@ struct ApiRay {      // RadeonRays::ray, include/math/ray.h:103-107
     int4 extra;      // x mask, y active, z doBackfaceCulling, w padding
 };
 
-template <bool ANY_HIT, bool COUNT>
-__global__ void __launch_bounds__(128, 8)
+template <bool ANY_HIT, bool COUNT, bool TWO_LEVEL>
+__global__ void __launch_bounds__(128, TWO_LEVEL ? 6 : 8)
 query_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris, const ApiRay* __restrict__ rays,
              const int* __restrict__ numrays_ptr, int numrays_max, void* __restrict__ out,
-             unsigned int* __restrict__ work_counter, int* __restrict__ counts, int num_nodes, int stage_top) {
+             unsigned int* __restrict__ work_counter, int* __restrict__ counts, int num_nodes, int stage_top,
+             const float4* __restrict__ instances) {
     // a negative device-side count means no rays, as the reference's `index < *num_rays` does
     const int numrays = numrays_ptr ? max(0, min(*numrays_ptr, numrays_max)) : numrays_max;
     const unsigned lane = threadIdx.x & 31u;
     __shared__ TopNodes s_top;
-    Traverser<ANY_HIT, COUNT> trav{nodes, tris};
+    Traverser<ANY_HIT, COUNT, false, TWO_LEVEL> trav{nodes, tris};
+    trav.instances = instances;
     trav.top = s_top.nodes;
     trav.top_count = stage_top_nodes(s_top, nodes, num_nodes, stage_top);
     uint2 stack[MCRT_STACK_SIZE];
@@ -77,12 +79,14 @@ query_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris, c
                         const float4 v0 = __ldg(tris + 3 * (size_t)st.best_tri + 0);
                         const float4 v1 = __ldg(tris + 3 * (size_t)st.best_tri + 1);
                         const float4 v2 = __ldg(tris + 3 * (size_t)st.best_tri + 2);
-                        const float px = add_(ray.ox, mul_(st.closest, ray.dx));
-                        const float py = add_(ray.oy, mul_(st.closest, ray.dy));
-                        const float pz = add_(ray.oz, mul_(st.closest, ray.dz));
+                        // (two levels: in the object space the triangle was hit in, intersect_bvh2level_skiplinks.cl:205-222)
+                        const Ray hr = TWO_LEVEL ? hit_space_ray(instances, ray, st.best_inst) : ray;
+                        const float px = add_(hr.ox, mul_(st.closest, hr.dx));
+                        const float py = add_(hr.oy, mul_(st.closest, hr.dy));
+                        const float pz = add_(hr.oz, mul_(st.closest, hr.dz));
                         const float2 uv = barycentrics_ref(px, py, pz, v0, v1, v2);
                         // shape_id, prim_id; the two padding ints are left as they are
-                        ((int2*)h)[0] = make_int2(__float_as_int(v0.w), __float_as_int(v1.w));
+                        ((int2*)h)[0] = make_int2(TWO_LEVEL ? st.best_sid : __float_as_int(v0.w), __float_as_int(v1.w));
                         ((float4*)h)[1] = make_float4(uv.x, uv.y, 0.0f, st.closest);
                     } else {
                         ((int2*)h)[0] = make_int2(-1, -1);   // uvwt untouched on a miss
@@ -112,7 +116,7 @@ static int grid_blocks() {
 
 cudaError_t launch_query(bool any_hit, bool counted, const void* nodes, const void* tris, const void* rays,
                          const int* numrays_dev, int numrays_max, void* out, unsigned int* work_counter,
-                         int* counts, cudaStream_t stream, int num_nodes) {
+                         int* counts, cudaStream_t stream, int num_nodes, const void* instances) {
     if (numrays_max <= 0) return cudaSuccess;
     static const int stage_top = getenv("MCRT_STAGE_TOP") ? atoi(getenv("MCRT_STAGE_TOP")) : 1;
     cudaError_t e = cudaMemsetAsync(work_counter, 0, sizeof(unsigned int), stream);
@@ -124,13 +128,19 @@ cudaError_t launch_query(bool any_hit, bool counted, const void* nodes, const vo
     const uint4* n = (const uint4*)nodes;
     const float4* t = (const float4*)tris;
     const ApiRay* r = (const ApiRay*)rays;
-    if (any_hit) {
-        query_kernel<true, false><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts, num_nodes, stage_top);
-    } else if (counted) {
-        query_kernel<false, true><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts, num_nodes, stage_top);
+    const float4* inst = (const float4*)instances;
+#define MCRT_LAUNCH_QUERY(A, C, T) \
+    query_kernel<A, C, T><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts, num_nodes, stage_top, inst)
+    if (inst) {
+        if (any_hit) MCRT_LAUNCH_QUERY(true, false, true);
+        else if (counted) MCRT_LAUNCH_QUERY(false, true, true);
+        else MCRT_LAUNCH_QUERY(false, false, true);
     } else {
-        query_kernel<false, false><<<grid, block, 0, stream>>>(n, t, r, numrays_dev, numrays_max, out, work_counter, counts, num_nodes, stage_top);
+        if (any_hit) MCRT_LAUNCH_QUERY(true, false, false);
+        else if (counted) MCRT_LAUNCH_QUERY(false, true, false);
+        else MCRT_LAUNCH_QUERY(false, false, false);
     }
+#undef MCRT_LAUNCH_QUERY
     return cudaGetLastError();
 }
 

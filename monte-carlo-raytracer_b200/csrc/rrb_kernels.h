@@ -10,7 +10,7 @@ namespace mcrt {
 // API object; `counts` is only used by the instrumented closest-hit variant.
 cudaError_t launch_query(bool any_hit, bool counted, const void* nodes, const void* tris, const void* rays,
                          const int* numrays_dev, int numrays_max, void* out, unsigned int* work_counter,
-                         int* counts, cudaStream_t stream, int num_nodes);
+                         int* counts, cudaStream_t stream, int num_nodes, const void* instances = nullptr);
 
 // ---- device refit (refit_kernels.cu)
 struct RefitMesh {

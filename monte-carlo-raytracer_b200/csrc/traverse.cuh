@@ -152,15 +152,45 @@ struct TravState {
     int best_tri;
     int best_sid, best_pid;
     bool any_hit;   // read only by Traverser<*, *, MIXED = true>: this ray wants any hit, not the closest
+    // two-level traversal only (Traverser<*, *, *, TWO_LEVEL = true>): the ray in the space of the tree being walked
+    // (world at the top level, the instance's object space below), the stack depth at which the instance was entered
+    // (-1 = at the top level), the instance being walked and the one that owns the best hit
+    float cox, coy, coz, cdx, cdy, cdz;
+    int inst_sp, cur_inst, cur_sid, best_inst;
 };
 
+// ray.o / ray.d through rows 0..2 of a world -> object matrix: transform_point / transform_vector of the reference's
+// two-level kernel (intersect_bvh2level_skiplinks.cl:103-131), same operation order; the direction is NOT
+// re-normalised, so t means the same in both spaces
+__device__ __forceinline__ void to_object_space(const float4 m0, const float4 m1, const float4 m2, const Ray& r, float& ox,
+                                                float& oy, float& oz, float& dx, float& dy, float& dz) {
+    ox = add_(add_(add_(mul_(m0.x, r.ox), mul_(m0.y, r.oy)), mul_(m0.z, r.oz)), m0.w);
+    oy = add_(add_(add_(mul_(m1.x, r.ox), mul_(m1.y, r.oy)), mul_(m1.z, r.oz)), m1.w);
+    oz = add_(add_(add_(mul_(m2.x, r.ox), mul_(m2.y, r.oy)), mul_(m2.z, r.oz)), m2.w);
+    dx = add_(add_(mul_(m0.x, r.dx), mul_(m0.y, r.dy)), mul_(m0.z, r.dz));
+    dy = add_(add_(mul_(m1.x, r.dx), mul_(m1.y, r.dy)), mul_(m1.z, r.dz));
+    dz = add_(add_(mul_(m2.x, r.dx), mul_(m2.y, r.dy)), mul_(m2.z, r.dz));
+}
+// the ray the best hit was found with: the world ray, or that ray in the object space of the hit's instance
+__device__ __forceinline__ Ray hit_space_ray(const float4* __restrict__ instances, const Ray& r, int best_inst) {
+    if (!instances || best_inst < 0) return r;
+    Ray o = r;
+    to_object_space(__ldg(instances + 4 * (size_t)best_inst), __ldg(instances + 4 * (size_t)best_inst + 1),
+                    __ldg(instances + 4 * (size_t)best_inst + 2), r, o.ox, o.oy, o.oz, o.dx, o.dy, o.dz);
+    return o;
+}
+
 // MIXED: closest-hit and any-hit rays share one launch; the kind is per ray (TravState::any_hit).
-template <bool ANY_HIT, bool COUNT, bool MIXED = false>
+// TWO_LEVEL: the node array starts with a top-level tree whose leaf entries are shapes (InstanceRecord table,
+// bvh8.h) instead of triangles; entering one transforms the ray into the shape's object space and walks the
+// bottom-level tree of its mesh (takes the role of intersect_bvh2level_skiplinks.cl:135-300,310-470).
+template <bool ANY_HIT, bool COUNT, bool MIXED = false, bool TWO_LEVEL = false>
 struct Traverser {
     const uint4* __restrict__ nodes;
     const float4* __restrict__ tris;
     const uint4* top = nullptr;     // shared-memory copy of nodes [0, top_count) (stage_top_nodes), or unused
     unsigned top_count = 0;
+    const float4* __restrict__ instances = nullptr;   // TWO_LEVEL: InstanceRecord table, 4 float4 each
 
     __device__ __forceinline__ void init(TravState& s, const Ray& r) const {
         s.ngroup = make_uint2(0u, 0x80000000u);   // root node = child slot 7^octinv of a virtual parent
@@ -178,6 +208,12 @@ struct Traverser {
         s.best_sid = 0x7fffffff;
         s.best_pid = 0x7fffffff;
         s.any_hit = ANY_HIT;
+        if (TWO_LEVEL) {
+            s.cox = r.ox; s.coy = r.oy; s.coz = r.oz;
+            s.cdx = r.dx; s.cdy = r.dy; s.cdz = r.dz;
+            s.inst_sp = -1;
+            s.cur_inst = s.cur_sid = s.best_inst = -1;
+        }
     }
 
     // Runs until the ray is finished (returns true) or the warp's active-lane count drops under
@@ -185,9 +221,12 @@ struct Traverser {
     __device__ __forceinline__ bool run(TravState& s, const Ray& r, uint2* stack, int* counters) const {
         uint2 ngroup = s.ngroup, tgroup = s.tgroup;
         int sp = s.sp;
-        const uint32_t octinv4 = s.octinv4;
-        const uint32_t octinv = octinv4 & 7u;
+        uint32_t octinv4 = s.octinv4;
+        uint32_t octinv = octinv4 & 7u;
         bool finished = false;
+        // the ray in the space being walked
+#define MCRT_RO(c) (TWO_LEVEL ? s.co##c : r.o##c)
+#define MCRT_RD(c) (TWO_LEVEL ? s.cd##c : r.d##c)
         while (true) {
 #if MCRT_POSTPONE_PERCENT > 0
             const int postpone_below = (__popc(__activemask()) * MCRT_POSTPONE_PERCENT) / 100;
@@ -227,16 +266,30 @@ struct Traverser {
                 const float aix = mul_(__uint_as_float((extract_byte(n0.w, 0) + 15u) << 23), s.idx);
                 const float aiy = mul_(__uint_as_float((extract_byte(n0.w, 1) + 15u) << 23), s.idy);
                 const float aiz = mul_(__uint_as_float((extract_byte(n0.w, 2) + 15u) << 23), s.idz);
-                const float orx = sub_(mul_(sub_(__uint_as_float(n0.x), r.ox), s.idx), aix);
-                const float ory = sub_(mul_(sub_(__uint_as_float(n0.y), r.oy), s.idy), aiy);
-                const float orz = sub_(mul_(sub_(__uint_as_float(n0.z), r.oz), s.idz), aiz);
+                const float orx = sub_(mul_(sub_(__uint_as_float(n0.x), MCRT_RO(x)), s.idx), aix);
+                const float ory = sub_(mul_(sub_(__uint_as_float(n0.y), MCRT_RO(y)), s.idy), aiy);
+                const float orz = sub_(mul_(sub_(__uint_as_float(n0.z), MCRT_RO(z)), s.idz), aiz);
 #else
                 const float aix = mul_(__uint_as_float(extract_byte(n0.w, 0) << 23), s.idx);
                 const float aiy = mul_(__uint_as_float(extract_byte(n0.w, 1) << 23), s.idy);
                 const float aiz = mul_(__uint_as_float(extract_byte(n0.w, 2) << 23), s.idz);
-                const float orx = mul_(sub_(__uint_as_float(n0.x), r.ox), s.idx);
-                const float ory = mul_(sub_(__uint_as_float(n0.y), r.oy), s.idy);
-                const float orz = mul_(sub_(__uint_as_float(n0.z), r.oz), s.idz);
+                const float orx = mul_(sub_(__uint_as_float(n0.x), MCRT_RO(x)), s.idx);
+                const float ory = mul_(sub_(__uint_as_float(n0.y), MCRT_RO(y)), s.idy);
+                const float orz = mul_(sub_(__uint_as_float(n0.z), MCRT_RO(z)), s.idz);
+#endif
+#if MCRT_QUANT_PRMT
+                // The offset or' = (p - o) * idir - ai' is rounded at the magnitude of ai' = 2^(e + 15) * idir: an error of
+                // up to 2^-9 quantisation step in the position of every plane.  HIGH planes carry an outward bias of 2^-7
+                // step that covers it; LOW planes do not -- and for a positive direction component the LOW plane is the
+                // NEAR one, so t_near can come out late by |ai'| * 2^-24.  Harmless while the interval is closed by the
+                // (biased) far plane, not when it is closed by the ray's own tmax: a shadow ray that ends on the emitter
+                // it was aimed at hits at t = tmax - a few ulp, exactly on the flat emitter's low face, and was culled
+                // (r02 parity report: 2-5 shadow rays per 512^2 Cornell frame, against the brute-force oracle).  The
+                // far side is therefore widened by 2^-22 * max |ai'| = four times the error bound, folded into the
+                // multiply-add that applies the relative widening: no extra instruction per child.
+                const float slack = mul_(fmaxf(fmaxf(fabsf(aix), fabsf(aiy)), fabsf(aiz)), 2.384185791015625e-07f);
+#else
+                const float slack = 0.0f;
 #endif
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
@@ -266,7 +319,7 @@ struct Traverser {
         const float tmaxz = __fmaf_rn(quant_byte_to_float<j>(zmax, czmax), aiz, orz);                          \
         const float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, 0.f));                                      \
         /* 1 + 3 ulp widening keeps the quantised slab test conservative w.r.t. fp32 rounding */               \
-        const float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, s.closest)) * 1.0000004f;                   \
+        const float cmax = __fmaf_rn(fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, s.closest)), 1.0000004f, slack);  \
         if (cmin <= cmax) hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);              \
     }
                     MCRT_CHILD_TEST(0)
@@ -291,6 +344,32 @@ struct Traverser {
             }
 
             while (tgroup.y != 0u) {
+                if (TWO_LEVEL && s.inst_sp < 0) {
+                    // top level: the group's entries are shapes.  Take one, park what is still pending up here, and
+                    // go down into its mesh's tree with the ray in its object space.
+                    const uint32_t ii = tgroup.x + (31u - __clz(tgroup.y));
+                    tgroup.y &= ~(1u << (31u - __clz(tgroup.y)));
+                    const float4 m0 = __ldg(instances + 4 * (size_t)ii + 0);
+                    const float4 m1 = __ldg(instances + 4 * (size_t)ii + 1);
+                    const float4 m2 = __ldg(instances + 4 * (size_t)ii + 2);
+                    const float4 w3 = __ldg(instances + 4 * (size_t)ii + 3);
+                    const int sid = __float_as_int(w3.y);
+                    if (r.mask == sid) continue;      // masked vs this ray (intersect_bvh2level_skiplinks.cl:236-240)
+                    if (tgroup.y != 0u) stack[sp++] = tgroup;
+                    if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
+                    s.inst_sp = sp;
+                    s.cur_inst = (int)ii;
+                    s.cur_sid = sid;
+                    to_object_space(m0, m1, m2, r, s.cox, s.coy, s.coz, s.cdx, s.cdy, s.cdz);
+                    s.idx = safe_inv(s.cdx);
+                    s.idy = safe_inv(s.cdy);
+                    s.idz = safe_inv(s.cdz);
+                    octinv = 7u - ((s.idx < 0.f ? 1u : 0u) | (s.idy < 0.f ? 2u : 0u) | (s.idz < 0.f ? 4u : 0u));
+                    octinv4 = octinv * 0x01010101u;
+                    ngroup = make_uint2((uint32_t)__float_as_int(w3.x), 0x80000000u);
+                    tgroup = make_uint2(0u, 0u);
+                    break;
+                }
 #if MCRT_POSTPONE_PERCENT > 0
                 if (__popc(__activemask()) < postpone_below) {
                     stack[sp++] = tgroup;
@@ -311,13 +390,19 @@ struct Traverser {
                 const float4 v1 = __ldg(tris + 3 * ta + 1);
                 const float4 v2 = __ldg(tris + 3 * ta + 2);
                 if (COUNT) counters[1]++;
-                const int sid = __float_as_int(v0.w);
-                if (r.mask == sid) continue;
+                const int sid = TWO_LEVEL ? s.cur_sid : __float_as_int(v0.w);
+                if (!TWO_LEVEL && r.mask == sid) continue;
                 float t;
-                if (intersect_triangle_ref(r, v0, v1, v2, s.closest, t)) {
+                Ray cr = r;
+                if (TWO_LEVEL) {
+                    cr.ox = s.cox; cr.oy = s.coy; cr.oz = s.coz;
+                    cr.dx = s.cdx; cr.dy = s.cdy; cr.dz = s.cdz;
+                }
+                if (intersect_triangle_ref(cr, v0, v1, v2, s.closest, t)) {
                     if (ANY_HIT || (MIXED && s.any_hit)) {
                         if (t < s.closest) {
                             s.best_tri = (int)ta;
+                            if (TWO_LEVEL) s.best_inst = s.cur_inst;
                             finished = true;
                             break;
                         }
@@ -331,6 +416,7 @@ struct Traverser {
                             s.best_tri = (int)ta;
                             s.best_sid = sid;
                             s.best_pid = pid;
+                            if (TWO_LEVEL) s.best_inst = s.cur_inst;
                         }
                     }
                 }
@@ -338,6 +424,17 @@ struct Traverser {
             if (finished) break;
 
             if (ngroup.y <= 0x00FFFFFFu) {
+                if (TWO_LEVEL && sp == s.inst_sp) {
+                    // the shape's subtree is exhausted: back to world space and to what was parked at the top level
+                    s.inst_sp = -1;
+                    s.cox = r.ox; s.coy = r.oy; s.coz = r.oz;
+                    s.cdx = r.dx; s.cdy = r.dy; s.cdz = r.dz;
+                    s.idx = safe_inv(r.dx);
+                    s.idy = safe_inv(r.dy);
+                    s.idz = safe_inv(r.dz);
+                    octinv = 7u - ((s.idx < 0.f ? 1u : 0u) | (s.idy < 0.f ? 2u : 0u) | (s.idz < 0.f ? 4u : 0u));
+                    octinv4 = octinv * 0x01010101u;
+                }
                 if (sp == 0) {
                     finished = true;
                     break;
@@ -347,9 +444,12 @@ struct Traverser {
             // dynamic fetch: leave when too few lanes of the warp still traverse
             if (__popc(__activemask()) < MCRT_DYNAMIC_FETCH_THRESHOLD) break;
         }
+#undef MCRT_RO
+#undef MCRT_RD
         s.ngroup = ngroup;
         s.tgroup = tgroup;
         s.sp = sp;
+        s.octinv4 = octinv4;
         return finished;
     }
 };

@@ -175,3 +175,56 @@ def load_obj(path, scale=1.0, camera=None, extra_lights=(), name=None) -> Scene:
                camera or CameraSpec(position=(0.0, 0.0, -5.0), euler_deg=(0.0, 0.0, 0.0)),
                textures=textures, texdata=texdata)
     return sc.finalize()
+
+
+def load_entities(entities, camera=None, extra_lights=(), name="entities") -> Scene:
+    """A scene of placed assets: `entities` is a list of (obj_path, transform 4x4 row-major or None[, scale]) -- the
+    engine's MeshRenderer entities.  The first use of an asset imports it (load_obj's rules); every later use of the
+    SAME asset shares its geometry, as RTScene::attachMesh does (RTScene.cpp:570-598): one more RTShape per sub-mesh
+    with the template's startIdx / startVertex / numTriangles and material, its own transform, and
+    IntersectionApi::CreateInstance instead of CreateMesh -- which makes Radeon Rays (and this library) commit a
+    two-level structure.  Materials and textures are pooled over all assets."""
+    meshes, mats, lights = [], [], []
+    tex_chunks, texdata_chunks, tex_bytes, tex_count = [], [], 0, 0
+    first_use = {}
+    for ent in entities:
+        path, xf = ent[0], ent[1]
+        scale = ent[2] if len(ent) > 2 else 1.0
+        T = None if xf is None else np.ascontiguousarray(xf, f4).reshape(4, 4)
+        key = (os.path.abspath(path), float(scale))
+        if key in first_use:
+            for t in first_use[key]:
+                tm = meshes[t]
+                meshes.append(Mesh(tm.name, tm.positions, tm.normals, tm.uvs, tm.indices, tm.material, T, instance_of=t))
+            continue
+        part = load_obj(path, scale=scale)
+        mat_base, tex_base, shape_base = len(mats), tex_count, len(meshes)
+        m2 = part.materials.copy()
+        for f in ("uber_normalMapId", "uber_diffuseTexId", "uber_glossyTexId", "uber_specReflectionTexId",
+                  "uber_transmissionTexId", "uber_opacityTexId", "uber_roughnessTexId", "uber_iorTexId"):
+            m2[f] = np.where(m2[f] >= 0, m2[f] + tex_base, m2[f])
+        mats.extend(m2[i:i + 1] for i in range(len(m2)))
+        if len(part.textures):
+            t2 = part.textures.copy()
+            t2["memOffset"] += tex_bytes
+            tex_chunks.append(t2)
+            texdata_chunks.append(part.texdata)
+            tex_bytes += part.texdata.size
+            tex_count += len(t2)
+        first_use[key] = []
+        for m in part.meshes:
+            first_use[key].append(len(meshes))
+            meshes.append(Mesh(m.name, m.positions, m.normals, m.uvs, m.indices,
+                               m.material + mat_base if m.material >= 0 else m.material, T))
+        for lt in part.lights:
+            l2 = lt.copy()
+            if int(l2["shapeId"]) >= 0:
+                l2["shapeId"] = int(l2["shapeId"]) + shape_base
+            lights.append(np.array([l2], dtype=L.LIGHT))
+    lights += list(extra_lights)
+    sc = Scene(name, meshes, np.concatenate(mats) if mats else np.zeros(0, dtype=L.MATERIAL),
+               np.concatenate(lights) if lights else np.zeros(0, dtype=L.LIGHT),
+               camera or CameraSpec(position=(0.0, 0.0, -5.0), euler_deg=(0.0, 0.0, 0.0)),
+               textures=np.concatenate(tex_chunks) if tex_chunks else np.zeros(0, dtype=L.TEXDESC),
+               texdata=np.concatenate(texdata_chunks) if texdata_chunks else np.zeros(0, dtype=np.uint8))
+    return sc.finalize()

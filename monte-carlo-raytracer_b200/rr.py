@@ -29,7 +29,9 @@ class RrbStats(ctypes.Structure):
     _fields_ = [("num_triangles", ctypes.c_int64), ("num_nodes", ctypes.c_int64), ("node_bytes", ctypes.c_int64),
                 ("triangle_bytes", ctypes.c_int64), ("build_seconds", ctypes.c_double), ("launches", ctypes.c_int64),
                 ("refits", ctypes.c_int64), ("last_commit_refit", ctypes.c_int64),
-                ("last_build_on_device", ctypes.c_int64), ("num_levels", ctypes.c_int64)]
+                ("last_build_on_device", ctypes.c_int64), ("num_levels", ctypes.c_int64),
+                ("two_level", ctypes.c_int64), ("num_instances", ctypes.c_int64), ("two_level_rebuilds", ctypes.c_int64),
+                ("top_level_updates", ctypes.c_int64)]
 
 
 def lib_path() -> str:
@@ -345,7 +347,10 @@ def attach_scene(api: IntersectionApi, scene):
     id = index into the RTShape array, world transform set on the shape."""
     shapes = []
     for i, m in enumerate(scene.meshes):
-        s = api.CreateMesh(m.positions, m.positions.shape[0], 12, m.indices, 0, None, m.indices.shape[0])
+        if getattr(m, "instance_of", None) is not None:      # RTScene.cpp:579: CreateInstance(instanceTemplateShape)
+            s = api.CreateInstance(shapes[int(m.instance_of)])
+        else:
+            s = api.CreateMesh(m.positions, m.positions.shape[0], 12, m.indices, 0, None, m.indices.shape[0])
         s.SetId(i)
         if m.transform is not None:
             s.SetTransform(m.transform)

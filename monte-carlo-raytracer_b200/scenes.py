@@ -88,6 +88,11 @@ class Mesh:
     indices: np.ndarray              # (T,3) int32, relative to this mesh's first vertex
     material: int = L.RT_INVALID_ID
     transform: Optional[np.ndarray] = None   # 4x4 row-major float32; None = identity
+    # Second and later uses of a mesh (RTScene::attachMesh, RTScene.cpp:575-598): index of the Mesh in Scene.meshes
+    # whose geometry this shape shares.  Its own RTShape has the template's startIdx / startVertex / numTriangles and
+    # its own transform; Radeon Rays gets CreateInstance(template) instead of a second CreateMesh.  The arrays above
+    # then ARE the template's (same objects), so code that flattens shapes keeps working.
+    instance_of: Optional[int] = None
 
 
 @dataclass
@@ -129,10 +134,16 @@ class Scene:
             T = np.eye(4, dtype=f4) if m.transform is None else np.asarray(m.transform, f4)
             shapes[i]["toWorldTransform"] = T
             shapes[i]["toWorldInverseTranspose"] = np.linalg.inv(T.astype(np.float64)).T.astype(f4)
+            shapes[i]["materialId"] = m.material
+            if m.instance_of is not None:       # shares the template's index / vertex ranges (RTScene.cpp:583-590)
+                t = int(m.instance_of)
+                assert t < i and self.meshes[t].instance_of is None, "an instance must follow its template mesh"
+                for k in ("startIdx", "startVertex", "numTriangles"):
+                    shapes[i][k] = shapes[t][k]
+                continue
             shapes[i]["startIdx"] = start_idx
             shapes[i]["startVertex"] = start_vtx
             shapes[i]["numTriangles"] = m.indices.shape[0]
-            shapes[i]["materialId"] = m.material
             idx_chunks.append(np.ascontiguousarray(m.indices, np.uint32).reshape(-1))
             pos_chunks.append(m.positions.astype(f4))
             uv_chunks.append(m.uvs.astype(f4))

@@ -89,6 +89,52 @@ def occluded(tris, rays, out=None):
     return out
 
 
+SHAPE2L = np.dtype([("minv", np.float32, 12), ("first_tri", np.int32), ("num_tris", np.int32), ("id", np.int32),
+                    ("pad", np.int32)])
+
+
+def two_level_world(shapes):
+    """shapes: iterable of (mesh_key, positions, indices, shape_id, minv 4x4 or None) -- one entry per ATTACHED shape;
+    entries with the same mesh_key share one set of object-space triangles (instances).  Returns (tris, table)."""
+    chunks, first, table, at = [], {}, [], 0
+    for key, pos, idx, sid, minv in shapes:
+        if key not in first:
+            t = mesh_triangles([(pos, idx, 0, None)])
+            first[key] = (at, t.shape[0])
+            chunks.append(t)
+            at += t.shape[0]
+        rec = np.zeros(1, dtype=SHAPE2L)
+        m = np.eye(4, dtype=np.float32) if minv is None else np.ascontiguousarray(minv, np.float32)
+        rec["minv"][0] = m[:3].reshape(-1)
+        rec["first_tri"], rec["num_tris"] = first[key]
+        rec["id"] = sid
+        table.append(rec)
+    return np.concatenate(chunks), np.concatenate(table)
+
+
+def intersect_2level(tris, table, rays, hits=None):
+    """Brute-force restatement of the reference's two-level kernel (intersect_bvh2level_skiplinks.cl:135-300)."""
+    lib = load()
+    lib.oracle_intersect_2level.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                            ctypes.c_longlong, ctypes.c_void_p]
+    if hits is None:
+        hits = np.zeros(rays.shape[0], dtype=L.INTERSECTION)
+        hits["shapeid"] = -1
+        hits["primid"] = -1
+    lib.oracle_intersect_2level(_p(tris), _p(table), table.shape[0], _p(rays), rays.shape[0], _p(hits))
+    return hits
+
+
+def occluded_2level(tris, table, rays, out=None):
+    lib = load()
+    lib.oracle_occluded_2level.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                           ctypes.c_longlong, ctypes.c_void_p]
+    if out is None:
+        out = np.zeros(rays.shape[0], np.int32)
+    lib.oracle_occluded_2level(_p(tris), _p(table), table.shape[0], _p(rays), rays.shape[0], _p(out))
+    return out
+
+
 def hit_in_tied_set(tris, ray, t, shape, prim) -> bool:
     lib = load()
     r = np.ascontiguousarray(ray)

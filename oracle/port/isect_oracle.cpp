@@ -198,6 +198,106 @@ void oracle_occluded(const void* tris_, long long ntris, const void* rays_, long
     }
 }
 
+// ---- two-level worlds (instances): intersect_bvh2level_skiplinks.cl
+// Every attached shape is visited; the ray is taken into the shape's object space with transform_point /
+// transform_vector on the rows of its world -> object matrix (:103-131, the direction is not re-normalised, so t is
+// shared by both spaces), tested there against the OBJECT-space triangles of its mesh with the same triangle test
+// (:205-222), the hit point and barycentrics taken in object space, and the shape's id reported (:213).  Brute
+// force over shapes x triangles; ties at equal t go to the smallest (shape id, prim), the CUDA path's rule.
+struct Shape2L {     // one attached shape
+    float minv[12];  // rows 0..2 of the world -> object matrix
+    int first_tri;   // its mesh's object-space triangles in `tris`
+    int num_tris;
+    int id;
+    int pad;
+};
+static inline Ray to_object(const Ray& r, const float* m) {
+    Ray o = r;
+    for (int k = 0; k < 3; ++k) {
+        const float* row = m + 4 * k;
+        o.o[k] = row[0] * r.o[0] + row[1] * r.o[1] + row[2] * r.o[2] + row[3];
+        o.d[k] = row[0] * r.d[0] + row[1] * r.d[1] + row[2] * r.d[2];
+    }
+    return o;
+}
+void oracle_intersect_2level(const void* tris_, const void* shapes_, int nshapes, const void* rays_, long long nrays,
+                             void* hits_) {
+    const Tri* tris = (const Tri*)tris_;
+    const Shape2L* shapes = (const Shape2L*)shapes_;
+    const Ray* rays = (const Ray*)rays_;
+    Isect* hits = (Isect*)hits_;
+#pragma omp parallel for schedule(dynamic, 64)
+    for (long long i = 0; i < nrays; ++i) {
+        const Ray& r = rays[i];
+        if (r.extra[1] == 0) continue;
+        float closest = r.o[3];
+        int best_shape = -1, best_id = 0, best_prim = 0;
+        long long best_tri = -1;
+        for (int s = 0; s < nshapes; ++s) {
+            const Shape2L& sh = shapes[s];
+            if (r.extra[0] == sh.id) continue;
+            const Ray o = to_object(r, sh.minv);
+            for (int k = 0; k < sh.num_tris; ++k) {
+                const Tri& t = tris[sh.first_tri + k];
+                float tt = intersect_triangle(o, t.v0, t.v1, t.v2, closest);
+                bool take = tt < closest;
+                if (!take && best_tri >= 0 && tt == closest &&
+                    intersect_triangle(o, t.v0, t.v1, t.v2, closest * 2.0f + 1.0f) == closest)
+                    take = sh.id < best_id || (sh.id == best_id && t.prim < best_prim);
+                if (take) {
+                    closest = tt;
+                    best_shape = s;
+                    best_id = sh.id;
+                    best_prim = t.prim;
+                    best_tri = sh.first_tri + k;
+                }
+            }
+        }
+        if (best_tri >= 0) {
+            const Ray o = to_object(r, shapes[best_shape].minv);
+            const Tri& t = tris[best_tri];
+            float p[3] = {o.o[0] + closest * o.d[0], o.o[1] + closest * o.d[1], o.o[2] + closest * o.d[2]};
+            float uv[2];
+            barycentrics(p, t.v0, t.v1, t.v2, uv);
+            hits[i].shapeid = best_id;
+            hits[i].primid = best_prim;
+            hits[i].uvwt[0] = uv[0];
+            hits[i].uvwt[1] = uv[1];
+            hits[i].uvwt[2] = 0.0f;
+            hits[i].uvwt[3] = closest;
+        } else {
+            hits[i].shapeid = -1;
+            hits[i].primid = -1;
+        }
+    }
+}
+void oracle_occluded_2level(const void* tris_, const void* shapes_, int nshapes, const void* rays_, long long nrays,
+                            int* out) {
+    const Tri* tris = (const Tri*)tris_;
+    const Shape2L* shapes = (const Shape2L*)shapes_;
+    const Ray* rays = (const Ray*)rays_;
+#pragma omp parallel for schedule(dynamic, 64)
+    for (long long i = 0; i < nrays; ++i) {
+        const Ray& r = rays[i];
+        if (r.extra[1] == 0) continue;
+        const float closest = r.o[3];
+        int res = -1;
+        for (int s = 0; s < nshapes && res < 0; ++s) {
+            const Shape2L& sh = shapes[s];
+            if (r.extra[0] == sh.id) continue;
+            const Ray o = to_object(r, sh.minv);
+            for (int k = 0; k < sh.num_tris; ++k) {
+                const Tri& t = tris[sh.first_tri + k];
+                if (intersect_triangle(o, t.v0, t.v1, t.v2, closest) < closest) {
+                    res = 1;
+                    break;
+                }
+            }
+        }
+        out[i] = res;
+    }
+}
+
 // ---- RNG / sampler restatement (assets/kernels/rng.cl:48-66,104-107; samplers.cl:83-84)
 uint32_t oracle_wang_hash(uint32_t seed) {
     seed = (seed ^ 61u) ^ (seed >> 16);

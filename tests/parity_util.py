@@ -164,8 +164,17 @@ def explain_divergences(scene, got_trace, want_trace, closest_rays, shadow_rays,
             out["reference_cull"] += int((g_ok & ~w_ok).sum())
             out["cuda_wrong"] += int((~g_ok & w_ok).sum())
             out["other"] += int((g_ok == w_ok).sum())
-            for i in np.nonzero(~(g_ok & ~w_ok))[0][:4]:
-                out["examples"].append({"pixel": int(px[i]), "bounce": int(b), "kind": name})
+            for i in np.nonzero(~(g_ok & ~w_ok))[0][:6]:
+                ex = {"pixel": int(px[i]), "bounce": int(b), "kind": name, "cuda": [int(x) for x in g[i]],
+                      "reference": [int(x) for x in w[i]], "ray_o": [float(x) for x in rays["o"][i]],
+                      "ray_d": [float(x) for x in rays["d"][i]], "ray_extra": [int(x) for x in rays["extra"][i]]}
+                if name == "closest":
+                    ex["brute_force"] = [int(bf["shapeid"][i]), int(bf["primid"][i]), float(bf["uvwt"][i, 3])]
+                else:
+                    ex["brute_force_occluded"] = bool(bf_occ[i])
+                    h = port.intersect(tris, rays[i:i + 1])
+                    ex["brute_force_closest"] = [int(h["shapeid"][0]), int(h["primid"][0]), float(h["uvwt"][0, 3])]
+                out["examples"].append(ex)
     rest = idx[(cls[idx] != CLASSES.index("closest_hit_flip")) & (cls[idx] != CLASSES.index("shadow_visibility_flip"))]
     out["other"] += int(rest.size)
     for i in rest[:4]:

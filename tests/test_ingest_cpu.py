@@ -106,3 +106,31 @@ def test_reference_cornell_obj_reproduces_the_builtin_scene():
     assert np.allclose(a.materials["uber_roughness"], b.materials["uber_roughness"])
     assert len(a.lights) == 1 and a.lights[0]["shapeId"] == b.lights[0]["shapeId"]
     assert np.allclose(a.lights[0]["intensity"], b.lights[0]["intensity"]) and np.isclose(a.lights[0]["area"], b.lights[0]["area"])
+
+
+def test_second_use_of_an_asset_becomes_an_instance(tiny, tmp_path):
+    """RTScene::attachMesh (RTScene.cpp:570-598): the second use of a mesh adds RTShapes that SHARE the template's
+    index / vertex ranges and material and carry their own transform; the Radeon Rays side gets CreateInstance.
+    Geometry, materials and textures are stored once."""
+    T1 = np.eye(4, dtype=np.float32)
+    T1[:3, 3] = (5.0, 0.0, 0.0)
+    T2 = np.eye(4, dtype=np.float32)
+    T2[:3, :3] *= 2.0
+    obj = str(tmp_path / "tiny.obj")
+    s = ingest.load_entities([(obj, None, 2.0), (obj, T1, 2.0), (obj, T2, 2.0)])
+    assert len(s.meshes) == 6 and len(s.shapes) == 6
+    assert [m.instance_of for m in s.meshes] == [None, None, 0, 1, 0, 1]
+    # geometry pooled once
+    assert s.indices.size == tiny.indices.size and s.positions.shape == tiny.positions.shape
+    assert len(s.materials) == len(tiny.materials) and len(s.textures) == len(tiny.textures)
+    for i, t in ((2, 0), (3, 1), (4, 0), (5, 1)):
+        for k in ("startIdx", "startVertex", "numTriangles", "materialId"):
+            assert s.shapes[i][k] == s.shapes[t][k]
+    assert np.array_equal(s.shapes[2]["toWorldTransform"], T1) and np.array_equal(s.shapes[4]["toWorldTransform"], T2)
+    assert np.allclose(s.shapes[4]["toWorldInverseTranspose"][:3, :3], np.eye(3) * 0.5)
+    # the emissive group is a light once per import, linked to the template's shape
+    assert len(s.lights) == 1 and int(s.lights[0]["shapeId"]) == 1 and s.shapes[1]["lightID"] == 0
+    # a different scale is a different asset, not an instance
+    s2 = ingest.load_entities([(obj, None, 2.0), (obj, None, 1.0)])
+    assert [m.instance_of for m in s2.meshes] == [None, None, None, None]
+    assert s2.indices.size == 2 * tiny.indices.size

@@ -417,11 +417,12 @@ def test_two_stream_half_frames_equal_single_wavefront_bitwise(api, cornell):
 @pytest.mark.parametrize("halves", [1, 2])
 def test_coherence_bucketed_queues_equal_push_order_bitwise(api, halves):
     """ptb_set_coherence: ordering the live-path queues by the sampler's coming light / lobe decisions changes which
-    lanes shade which path, not what any path computes -- radiance, image and counters are bit-identical."""
+    lanes shade which path, not what any path computes -- radiance, image and counters are bit-identical.  Mode 4 is
+    the consumer-side sort with the scene tables staged in shared memory by bulk copies (shade_sorted)."""
     scene = scene_library.sponza_class(64)     # three light types, textured two-lobe materials, alpha masks
     w, h, depth = 512, 320, 5
     res = []
-    for mode in (0, 1, 2, 3):
+    for mode in (0, 1, 2, 3, 4):
         a = api if mode == 0 else rr.IntersectionApi.Create(0)
         try:
             pl = pt.make_pt_pipeline(a, scene, w, h, depth)
@@ -440,7 +441,7 @@ def test_coherence_bucketed_queues_equal_push_order_bitwise(api, halves):
                 rr.IntersectionApi.Delete(a)
         res.append((frames, img, cnt))
     assert res[0][2]["shaded_vertices"] > 2 * w * h      # paths do go several bounces deep
-    for mode in (1, 2, 3):
+    for mode in (1, 2, 3, 4):
         for f in range(3):
             assert np.array_equal(res[0][0][f].view(np.uint32), res[mode][0][f].view(np.uint32)), (mode, f)
         assert np.array_equal(res[0][1].view(np.uint32), res[mode][1].view(np.uint32))
