@@ -10,6 +10,14 @@
 
 namespace mcrt {
 
+// Compile-time switch of the per-triangle shading records (Scene::triShade).  Measured on C3 (profiles/r02_shade.md):
+// neutral for the default shade kernel (1.991 vs 1.998 ms per step), +6 % for the sorted one, and the second code
+// path costs 1.5 K SASS instructions and registers in every kernel that shades -- so it is compiled out by default
+// (build with -DPT_TRI_RECORDS=1 and run with MCRT_TRI_RECORDS=1 to use it).
+#ifndef PT_TRI_RECORDS
+#define PT_TRI_RECORDS 0
+#endif
+
 struct RTShape {            // kernel_data.h:36-52
     float4 toWorld[4];
     float4 toWorldInvT[4];
@@ -107,7 +115,7 @@ HD void computeTrianglePartialDerivates(V2 uv0, V2 uv1, V2 uv2, V3 p0, V3 p1, V3
 
 HD void loadTrianglePositions(const Scene& sc, const RTShape* shape, int primIdx, V3* p0, V3* p1, V3* p2,
                               uint32_t* i0, uint32_t* i1, uint32_t* i2) {
-    if (sc.triShade) {      // world-space vertices straight from the per-triangle record (the indices are not needed)
+    if (PT_TRI_RECORDS && sc.triShade) {      // world-space vertices straight from the per-triangle record (the indices are not needed)
         const float4* r = sc.triShade + 9 * (size_t)(shape->startIdx / 3u + (uint32_t)primIdx);
         *p0 = v3(__ldg(r + 0));
         *p1 = v3(__ldg(r + 1));
@@ -188,7 +196,7 @@ HD TriShade loadTriShade(const float4* __restrict__ r) {
 // geometry.cl:177-215 computeSurfaceInteraction (wo / traceErrorOffset are set by the caller)
 HD RTInteraction computeSurfaceInteraction(const Scene& sc, int shapeId, int primIdx, float bu, float bv) {
     RTInteraction si;
-    if (sc.triShade) {      // the same arithmetic, its triangle-only half read back from the per-triangle record
+    if (PT_TRI_RECORDS && sc.triShade) {      // the same arithmetic, its triangle-only half read back from the per-triangle record
         const RTShape* shp = sc.shapes + shapeId;
         const TriShade t = loadTriShade(sc.triShade + 9 * (size_t)(shp->startIdx / 3u + (uint32_t)primIdx));
         const float w = 1.0f - bu - bv;

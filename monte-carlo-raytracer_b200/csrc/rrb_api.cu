@@ -426,6 +426,7 @@ bool wants_two_level(const rrb_api* api) {
     if (f2 != api->f32_options.end() && f2->second > 0.0f) return true;
     auto ff = api->f32_options.find("bvh.forceflat");
     if (ff != api->f32_options.end() && ff->second > 0.0f) return false;
+    if (refit_enabled(api)) return false;      // "bvh.refit" (this library's extension) refits the FLAT tree in place
     for (const rrb_shape* s : api->world)
         if (s->is_instance) return true;
     return false;

@@ -66,14 +66,15 @@ __device__ __forceinline__ uint32_t extract_byte(uint32_t x, uint32_t i) { retur
 // constant c = 1.0f, giving exactly 1 + b * 2^-15; the node's scale and offset absorb the affine map
 // (aix' = aix * 2^15, orx' = orx - aix').  Rounding orx' costs at most 2^-24 * 2^15 = 2^-9 quantisation step of
 // accuracy per plane on top of the errors proportional to t that the relative widening of the far side already
-// covers.  It is paid back by the constant: the bytes of a node's HIGH planes are converted with c = 1.0f + 2 ulp,
-// i.e. 2^-7 step further out.  For a positive direction component the high plane is the far one (t_far grows),
-// for a negative one it is the near one (t_near shrinks): either way the slab interval only widens.
+// covers.  It is paid back twice over: the bytes of a node's HIGH planes are converted with c = 1.0f + 4 ulp, i.e.
+// 2^-6 step further out, and the node offset is lowered by 2^-7 step (Traverser::run), so that LOW planes end up
+// 2^-7 step below and HIGH planes 2^-7 step above what the node stores: the slab interval only widens, on the near
+// side as well as on the far side, whatever the sign of the direction.
 #ifndef MCRT_QUANT_PRMT
 #define MCRT_QUANT_PRMT 1
 #endif
 #define MCRT_QUANT_C_LO 0x3F800000u
-#define MCRT_QUANT_C_HI 0x3F800002u
+#define MCRT_QUANT_C_HI 0x3F800004u
 template <int J>
 __device__ __forceinline__ float quant_byte_to_float(uint32_t x, uint32_t c) {
 #if MCRT_QUANT_PRMT
@@ -266,9 +267,17 @@ struct Traverser {
                 const float aix = mul_(__uint_as_float((extract_byte(n0.w, 0) + 15u) << 23), s.idx);
                 const float aiy = mul_(__uint_as_float((extract_byte(n0.w, 1) + 15u) << 23), s.idy);
                 const float aiz = mul_(__uint_as_float((extract_byte(n0.w, 2) + 15u) << 23), s.idz);
-                const float orx = sub_(mul_(sub_(__uint_as_float(n0.x), MCRT_RO(x)), s.idx), aix);
-                const float ory = sub_(mul_(sub_(__uint_as_float(n0.y), MCRT_RO(y)), s.idy), aiy);
-                const float orz = sub_(mul_(sub_(__uint_as_float(n0.z), MCRT_RO(z)), s.idz), aiz);
+                // ... and 2^-7 quantisation step less: every plane, LOW or HIGH, is thereby moved by -2^-7 step.  Together
+                // with the HIGH constant's +2^-6 step the LOW planes end up 2^-7 step below and the HIGH planes 2^-7 step
+                // above their stored position -- outward on BOTH sides, twice the rounding error of these offsets
+                // (2 x 2^-9 step: they are rounded at the magnitude of ai').  r01 biased the HIGH planes only, which
+                // keeps a box's own interval open but not the test against the ray's tmax: a shadow ray that ends on
+                // the emitter it was aimed at hits at t = tmax - a few ulp on the LOW face of the flat emitter's box,
+                // and a near plane that came out 2^-9 step late culled it (r02 parity report: 2-5 such rays per
+                // 512^2 Cornell frame disagreed with the brute-force oracle).
+                const float orx = __fmaf_rn(aix, -2.384185791015625e-07f, sub_(mul_(sub_(__uint_as_float(n0.x), MCRT_RO(x)), s.idx), aix));
+                const float ory = __fmaf_rn(aiy, -2.384185791015625e-07f, sub_(mul_(sub_(__uint_as_float(n0.y), MCRT_RO(y)), s.idy), aiy));
+                const float orz = __fmaf_rn(aiz, -2.384185791015625e-07f, sub_(mul_(sub_(__uint_as_float(n0.z), MCRT_RO(z)), s.idz), aiz));
 #else
                 const float aix = mul_(__uint_as_float(extract_byte(n0.w, 0) << 23), s.idx);
                 const float aiy = mul_(__uint_as_float(extract_byte(n0.w, 1) << 23), s.idy);
@@ -276,20 +285,6 @@ struct Traverser {
                 const float orx = mul_(sub_(__uint_as_float(n0.x), MCRT_RO(x)), s.idx);
                 const float ory = mul_(sub_(__uint_as_float(n0.y), MCRT_RO(y)), s.idy);
                 const float orz = mul_(sub_(__uint_as_float(n0.z), MCRT_RO(z)), s.idz);
-#endif
-#if MCRT_QUANT_PRMT
-                // The offset or' = (p - o) * idir - ai' is rounded at the magnitude of ai' = 2^(e + 15) * idir: an error of
-                // up to 2^-9 quantisation step in the position of every plane.  HIGH planes carry an outward bias of 2^-7
-                // step that covers it; LOW planes do not -- and for a positive direction component the LOW plane is the
-                // NEAR one, so t_near can come out late by |ai'| * 2^-24.  Harmless while the interval is closed by the
-                // (biased) far plane, not when it is closed by the ray's own tmax: a shadow ray that ends on the emitter
-                // it was aimed at hits at t = tmax - a few ulp, exactly on the flat emitter's low face, and was culled
-                // (r02 parity report: 2-5 shadow rays per 512^2 Cornell frame, against the brute-force oracle).  The
-                // far side is therefore widened by 2^-22 * max |ai'| = four times the error bound, folded into the
-                // multiply-add that applies the relative widening: no extra instruction per child.
-                const float slack = mul_(fmaxf(fmaxf(fabsf(aix), fabsf(aiy)), fabsf(aiz)), 2.384185791015625e-07f);
-#else
-                const float slack = 0.0f;
 #endif
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
@@ -305,9 +300,9 @@ struct Traverser {
                     const uint32_t ymin = s.idy < 0.f ? qhy : qly, ymax = s.idy < 0.f ? qly : qhy;
                     const uint32_t zmin = s.idz < 0.f ? qhz : qlz, zmax = s.idz < 0.f ? qlz : qhz;
                     // conversion constants travel with the words: HIGH planes get the outward bias
-                    const uint32_t cxmin = s.idx < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, cxmax = cxmin ^ 2u;
-                    const uint32_t cymin = s.idy < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, cymax = cymin ^ 2u;
-                    const uint32_t czmin = s.idz < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, czmax = czmin ^ 2u;
+                    const uint32_t cxmin = s.idx < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, cxmax = cxmin ^ 4u;
+                    const uint32_t cymin = s.idy < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, cymax = cymin ^ 4u;
+                    const uint32_t czmin = s.idz < 0.f ? MCRT_QUANT_C_HI : MCRT_QUANT_C_LO, czmax = czmin ^ 4u;
 #pragma unroll
 #define MCRT_CHILD_TEST(j)                                                                                      \
     {                                                                                                          \
@@ -319,7 +314,7 @@ struct Traverser {
         const float tmaxz = __fmaf_rn(quant_byte_to_float<j>(zmax, czmax), aiz, orz);                          \
         const float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, 0.f));                                      \
         /* 1 + 3 ulp widening keeps the quantised slab test conservative w.r.t. fp32 rounding */               \
-        const float cmax = __fmaf_rn(fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, s.closest)), 1.0000004f, slack);  \
+        const float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, s.closest)) * 1.0000004f;                   \
         if (cmin <= cmax) hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);              \
     }
                     MCRT_CHILD_TEST(0)
