@@ -1,7 +1,7 @@
 /* ptb.h -- C ABI of the B200 path-tracer stages (inside libmcrt_b200.so).
  *
  * Drop-in boundary, surface 2: what the engine's render passes call instead of compiling and
- * launching assets/kernels/*.cl through CLW (source/application/PathTracer/raytracing/renderPasses/
+ * launching the assets/kernels .cl files through CLW (source/application/PathTracer/raytracing/renderPasses/
  * RTPrimaryRaysPass.cpp:32-134, RTPathTracingPass.cpp:40-218, RTBDPTPass.cpp:67-511,
  * RTReconstructionPass.cpp:71-123) and instead of RTScene::setSceneArgs / upload*
  * (scene/RTScene.cpp:178-197,680-809).  Pass classes mirroring the reference's are in

@@ -153,6 +153,22 @@ def test_cpp_adaptor_compiles_against_reference_header_and_fails_loudly_without_
         assert "OK" in out.stdout
 
 
+def test_cpp_multi_gpu_host_loop_of_the_integration_guide_compiles_and_links():
+    """INTEGRATION.md section 3 shows a C++ host loop around ptb_set_partition / ptb_nccl_* / ptb_merge_accumulation;
+    tests/cpp/multi_gpu_host.cpp is that loop, compiled -Wall -Werror against include/ptb.h and linked against the
+    library.  Without a device it must report NO_DEVICE (no fallback)."""
+    import subprocess
+    import __graft_entry__ as g
+    exe = g.build_multi_gpu_host()
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    import torch
+    if not torch.cuda.is_available():
+        assert out.stdout.startswith("NO_DEVICE") and "no CPU fallback" in out.stdout
+    else:
+        assert out.stdout.startswith("OK")
+
+
 def test_refit_metadata_and_node_encoding_is_a_function_of_child_bounds():
     """What the device refit (csrc/refit_kernels.cu) relies on: (1) nodes are stored level by level and the
     builder reports where each level starts, (2) every emitted triangle knows the input mesh it came from,
