@@ -29,8 +29,9 @@ from oracle import ref
 
 pytestmark = pytest.mark.gpu
 
-# observed out-of-tolerance fractions (profiles/r02_parity.md: C1 4.8e-4 worst frame, C2 1.9e-6, C3 1.5e-4, C5 0) x 2
-MAX_OUT_FRAC = {"C1": 1.0e-3, "C2": 1.0e-5, "C3": 3.0e-4, "C5": 1.0e-5}
+# observed out-of-tolerance fractions (profiles/r02_parity.md: C1 5.0e-4 worst frame, C2 4.8e-7 = 1 pixel, C3 1.34e-4,
+# C5 0) x 2, rounded up; C2 / C5: a handful of pixels
+MAX_OUT_FRAC = {"C1": 1.0e-3, "C2": 2.0e-6, "C3": 3.0e-4, "C5": 1.0e-5}
 RMSE_BOUND = 1e-3          # x mean luminance of the oracle's image
 
 
