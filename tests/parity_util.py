@@ -202,9 +202,11 @@ def assert_parity(rep, max_out_frac, what=""):
 
 
 # ---------------------------------------------------------------------------------------------- drivers
-def cuda_frames(scene, w, h, depth, frames, part=None, device=0):
+def cuda_frames(scene, w, h, depth, frames, part=None, device=0, more_frames=(), images=None):
     """Fused wavefront through the C ABI with the diagnostic record on.  frames: iterable of frame indices.
-    Returns ([radiance (P,4)], [trace (D,P,4)], final image)."""
+    Returns ([radiance (P,4)], [trace (D,P,4)], final image).  `more_frames` are rendered and accumulated after
+    `frames` with the record off (nothing kept but the image); `images`, a dict, receives the accumulated image after
+    `frames` ("after_frames") and after `more_frames` ("final")."""
     from mcrt_b200 import rr, pt
     api = rr.IntersectionApi.Create(device)
     try:
@@ -221,6 +223,16 @@ def cuda_frames(scene, w, h, depth, frames, part=None, device=0):
             rad.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
             tr.append(pl.path_trace(depth).copy())
         img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+        if images is not None:
+            images["after_frames"] = img
+        if len(more_frames):
+            pl.set_path_trace(0)
+            for f in more_frames:
+                integ.m_frameIndex = f
+                pl.update()
+            img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+        if images is not None:
+            images["final"] = img
         pl.scene.destroy()
     finally:
         rr.IntersectionApi.Delete(api)
@@ -261,15 +273,20 @@ def config(name):
     raise KeyError(name)
 
 
-def run_config(name, device=0, keep=None):
+def run_config(name, device=0, keep=None, more_frames=()):
     """Per-frame parity reports of one config: CUDA fused wavefront vs oracle/_ref.  `keep`, a dict, receives the
-    CUDA path's accumulated image ("cuda_image") and the oracle's per-frame radiance ("oracle_radiance")."""
+    CUDA path's accumulated image after the config's frames ("cuda_image") and after `more_frames` as well
+    ("cuda_image_final"), the oracle's per-frame radiance of the config's frames ("oracle_radiance"), the mask of
+    pixels whose path diverged in any of them ("diverged_any") and the oracle renderer ("oracle_renderer")."""
     from mcrt_b200 import multi_gpu
     scene, w, h, depth, frames, part = config(name)
     pixels = None if part is None else multi_gpu.partition_pixels(w, h, part[0], part[1])
-    got, got_tr, img = cuda_frames(scene, w, h, depth, frames, part=part, device=device)
+    images = {}
+    got, got_tr, img = cuda_frames(scene, w, h, depth, frames, part=part, device=device, more_frames=more_frames,
+                                   images=images)
     if keep is not None:
-        keep["cuda_image"], keep["oracle_radiance"] = img, []
+        keep["cuda_image"], keep["cuda_image_final"], keep["oracle_radiance"] = images["after_frames"], images["final"], []
+        keep["diverged_any"] = np.zeros(w * h, bool)
     reps = []
     # the oracle one frame at a time: its per-bounce ray copies (for the brute-force arbitration) are large
     from mcrt_b200 import camera
@@ -282,6 +299,8 @@ def run_config(name, device=0, keep=None):
         want = rp.render_sample(cam, f, depth, trace=t, pixels=pixels)
         if keep is not None:
             keep["oracle_radiance"].append(want.copy())
+            keep["diverged_any"] |= first_divergence(got_tr[i], t["path_trace"], scene)[0] >= 0
+            keep["oracle_renderer"] = rp
         r = classify(got[i], want, got_tr[i], t["path_trace"], pixels=pixels, scene=scene)
         r["causes"] = explain_divergences(scene, got_tr[i], t["path_trace"], t["closest_rays"], t["shadow_rays"], pixels)
         r["config"], r["frame"] = name, f

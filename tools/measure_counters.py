@@ -41,6 +41,9 @@ def main():
     per = collections.OrderedDict()
     for r in csv.DictReader(rows):
         name = r["Kernel Name"].split("(")[0].split("::")[-1]
+        if name.startswith("void "):
+            name = name[5:]
+        name = name.split("<")[0]          # k_trace_mixed<0> / <1> (flat / two-level) -> k_trace_mixed
         name = ALIAS.get(name, name)
         try:
             v = float(r["Metric Value"].replace(",", ""))
@@ -48,7 +51,7 @@ def main():
             continue
         unit = r.get("Metric Unit", "")
         scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0, "usecond": 1e-6, "msecond": 1e-3, "nsecond": 1e-9,
-                 "second": 1.0}.get(unit, 1.0)
+                 "second": 1.0, "ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}.get(unit, 1.0)
         per.setdefault((name, r["ID"]), {})[r["Metric Name"]] = v * scale
     kernels = {}
     for (name, _), m in per.items():
