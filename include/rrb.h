@@ -113,6 +113,20 @@ int rrb_query_occlusion_indirect(rrb_api* api, const rrb_buffer* rays, const rrb
 int rrb_query_intersection_host(rrb_api* api, const void* host_rays, int numrays, void* host_hits);
 int rrb_query_occlusion_host(rrb_api* api, const void* host_rays, int numrays, int* host_results);
 
+/* ---- closest-hit query that allocates nothing.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same results as rrb_query_intersection, byte for byte (ray 48 B in, Intersection 32 B
+ * out, inactive rays and the uvwt of misses untouched), on raw DEVICE pointers the caller owns; asynchronous on the
+ * API's stream (rrb_get_stream), no event.  Its scratch -- the work counter of the persistent traversal kernel and
+ * a compacted list of the active rays' indices -- lives in one static device array of
+ * 256 + 4 * RRB_NOALLOC_MAX_RAYS bytes (4 MiB) that every GPU which loads the library holds until exit; the call
+ * makes no cudaMalloc / cudaFree and creates no stream or event.  numrays > RRB_NOALLOC_MAX_RAYS is rejected with
+ * RRB_ERROR_INVALID_ARGUMENT (split the batch).  All calls on a device share the array: calls whose kernels can
+ * overlap on the GPU (two streams or two API objects on one device) race; calls on one stream do not.
+ * (csrc/rrb_noalloc.cu) */
+#define RRB_NOALLOC_MAX_RAYS (1 << 20)
+int rrb_query_intersection_noalloc(rrb_api* api, const void* rays_device, int numrays, void* hits_device);
+
 /* ---- introspection for measurement (no reference counterpart) */
 typedef struct rrb_stats {
     int64_t num_triangles;

@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libmcrt_b200.so")
 STAMP_PATH = os.path.join(_HERE, ".libmcrt_b200.stamp")
 
 CUDA_SOURCES = ["rrb_api.cu", "rrb_kernels.cu", "ptb_api.cu", "pt_kernels.cu", "pt_stage_kernels.cu", "bdpt_kernels.cu",
-                "postfx_kernels.cu", "refit_kernels.cu", "lbvh_build.cu"]
+                "postfx_kernels.cu", "refit_kernels.cu", "lbvh_build.cu", "rrb_noalloc.cu"]
 CXX_SOURCES = ["bvh8_build.cpp"]
 
 # fp32 modes of the SHADING arithmetic.  The traversal, the triangle test and the hit
@@ -65,7 +65,7 @@ def _fingerprint():
     for f in files:
         p = f if os.path.isabs(f) else os.path.join(CSRC, f)
         if os.path.isfile(p):
-            h.update(p.encode())
+            h.update(os.path.basename(p).encode())      # names, not absolute paths: the same on every box
             with open(p, "rb") as fh:
                 h.update(fh.read())
     h.update(" ".join(NVCC_FLAGS).encode())

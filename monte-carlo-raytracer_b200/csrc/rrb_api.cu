@@ -269,6 +269,11 @@ int ensure_stage(rrb_api* api, size_t rays_bytes, size_t out_bytes) {
 
 }  // namespace
 
+namespace mcrt {
+// for the other translation units behind rrb.h (rrb_noalloc.cu): sets the text rrb_last_error() returns
+int rrb_fail(int code, const std::string& msg) { return fail(code, msg); }
+}  // namespace mcrt
+
 extern "C" {
 
 const char* rrb_last_error(void) { return g_last_error.c_str(); }

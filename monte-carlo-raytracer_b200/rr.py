@@ -15,6 +15,7 @@ import numpy as np
 
 from . import layouts as L
 
+NOALLOC_MAX_RAYS = 1 << 20
 K_NULL_ID = -1
 MAP_READ, MAP_WRITE = 1, 2
 
@@ -73,6 +74,7 @@ def load_library():
         "rrb_query_intersection_indirect": [vp, vp, vp, i, vp, vp, pp],
         "rrb_query_occlusion_indirect": [vp, vp, vp, i, vp, vp, pp],
         "rrb_query_intersection_host": [vp, vp, i, vp], "rrb_query_occlusion_host": [vp, vp, i, vp],
+        "rrb_query_intersection_noalloc": [vp, vp, i, vp],
         "rrb_get_stats": [vp, ctypes.POINTER(RrbStats)], "rrb_query_intersection_counted": [vp, vp, i, vp, vp],
         "rrb_get_bvh": [vp, pp, pp, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)],
         "rrb_get_stream": [vp, ctypes.POINTER(i), pp],
@@ -324,6 +326,13 @@ class IntersectionApi:
             results = np.zeros(rays.shape[0], dtype=np.int32)
         _check(self._lib.rrb_query_occlusion_host(self._h, _np_ptr(rays), rays.shape[0], _np_ptr(results)))
         return results
+
+    def QueryIntersectionNoAlloc(self, rays, numrays, hits):
+        """rrb_query_intersection_noalloc on the device pointers of two Buffers (or raw ints): no allocation inside,
+        asynchronous on the API's stream, at most RRB_NOALLOC_MAX_RAYS rays (include/rrb.h)."""
+        rp = rays.device_ptr if isinstance(rays, Buffer) else int(rays)
+        hp = hits.device_ptr if isinstance(hits, Buffer) else int(hits)
+        _check(self._lib.rrb_query_intersection_noalloc(self._h, rp, int(numrays), hp))
 
     # ---- measurement
     def GetStats(self):
