@@ -118,6 +118,20 @@ int ptb_bdpt_render_sample(ptb_context* ctx, int frame, int max_depth);
 /* RTBDPTPass::createBuffers (RTBDPTPass.cpp:451-478) alone: allocates the zero-filled BDPT buffers for `max_depth`
  * (ptb_bdpt_render_sample does it on first use), so that a checkpoint can be restored before the first frame. */
 int ptb_bdpt_reserve(ptb_context* ctx, int max_depth);
+/* Per-strategy records of the BDPT frame rendered last (diagnostic; the reference keeps the same information in its
+ * connection buffers: connectionRays / tempRadianceBuffer / connectionVisibilities, RTBDPTPass.cpp:451-478, written by
+ * PrepareConnections, BDPT.cl:460-652).  One record per (pixel, t, s) strategy whose unweighted contribution is not
+ * black -- compacted, in no particular order; N = element 6 of "BDPTCounters" (uint32[16]):
+ *   "BDPTConnectionContribution" float4[N]  xyz = unweighted contribution C (the reference's tempRadianceBuffer entry
+ *                                            before visibility and MIS weight), w = bits of the TARGET pixel index
+ *                                            (t = 1 strategies splat to the pixel the light vertex projects to)
+ *   "BDPTConnectionRayD"         float4[N]  xyz = connection ray direction, w = bits of  t | (s << 8)
+ *   "BDPTConnectionRayO"         float4[N]  xyz = connection ray origin, w = its length (s = 0: no ray, zeros)
+ *   "BDPTConnectionPixel"        int32[N]   the pixel whose subpaths are connected
+ *   "BDPTConnectionVisibility"   int32[N]   1 = unoccluded or no ray needed (s = 0), 0 = occluded
+ *   "BDPTConnectionWeight"       float[N]   the MIS weight the record was accumulated with (0 when occluded):
+ *                                            radiance[target] += C * weight
+ * Valid after ptb_bdpt_render_sample until the next BDPT frame or ptb_resize; capacity maxConnections * P records. */
 /* How ptb_pt_render_sample issues a frame: 2 (default) = the pixel set is split in two halves whose wavefronts run
  * on two streams, so that each kernel's drain-out tail is filled by the other half's kernels;
  * 1 = one wavefront on the context's stream.  Per-sample results are identical. */

@@ -751,7 +751,10 @@ k_bdpt_connect(PtState s, BdptState b) {
     const int P = s.width * s.height;
     const Scene sc = make_scene(s);
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        if (b.conn_vis[i] == 0) continue;
+        if (b.conn_vis[i] == 0) {
+            b.conn_w[i] = 0.0f;
+            continue;
+        }
         const float4 Cq = b.conn_C[i];
         const int ts = __float_as_int(b.conn_d[i].w);
         const int t = ts & 0xFF, st = ts >> 8;
@@ -759,6 +762,7 @@ k_bdpt_connect(PtState s, BdptState b) {
         const int target = __float_as_int(Cq.w);
         const V3 C = v3(Cq);
         const float w = isBlack(C) ? 0.0f : mis_weight(sc, b, P, px, t, st);
+        b.conn_w[i] = w;
         atomicAdd(b.splat + 3 * (size_t)target + 0, C.x * w);
         atomicAdd(b.splat + 3 * (size_t)target + 1, C.y * w);
         atomicAdd(b.splat + 3 * (size_t)target + 2, C.z * w);
@@ -780,7 +784,7 @@ const std::vector<const char*>& bdpt_buffer_names() {
         "bdpt_light_ray_o", "bdpt_light_ray_d", "bdpt_cam_hit", "bdpt_light_hit", "bdpt_cam_beta", "bdpt_light_beta",
         "bdpt_cam_count", "bdpt_light_count", "bdpt_cam_queue0", "bdpt_cam_queue1", "bdpt_light_queue0",
         "bdpt_light_queue1", "bdpt_conn_o", "bdpt_conn_d", "bdpt_conn_C", "bdpt_conn_src", "bdpt_conn_vis",
-        "bdpt_conn_rays", "bdpt_splat", "bdpt_cnt"};
+        "bdpt_conn_rays", "bdpt_conn_w", "bdpt_splat", "bdpt_cnt"};
     return names;
 }
 
@@ -812,6 +816,7 @@ std::vector<BdptBufferSpec> bdpt_buffer_specs(BdptState& b, int D) {
         {"bdpt_conn_src", maxConn * 4, (void**)&b.conn_src},
         {"bdpt_conn_vis", maxConn * 4, (void**)&b.conn_vis},
         {"bdpt_conn_rays", maxConn * 4, (void**)&b.conn_rays},
+        {"bdpt_conn_w", maxConn * 4, (void**)&b.conn_w},
         {"bdpt_splat", 12, (void**)&b.splat},
         {"bdpt_cnt", 0, (void**)&b.cnt},      // 0 = fixed 64-byte block, not per pixel
     };

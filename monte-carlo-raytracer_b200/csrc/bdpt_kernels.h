@@ -37,6 +37,7 @@ struct BdptState {
     float4* conn_C;          //   unweighted contribution rgb, w = target pixel bits
     int* conn_src;           //   pixel whose subpaths are connected
     int* conn_vis;           //   1 = unoccluded (or no ray needed)
+    float* conn_w;           //   MIS weight the record was accumulated with (0 when occluded), written by k_bdpt_connect
     uint32_t* conn_rays;     // indices of the records that need a shadow ray
     float* splat;            // float[3P] RGB accumulator (atomic adds; t = 1 strategies splat elsewhere)
     unsigned int* cnt;       // [0..1] cam queue counts, [2..3] light queue counts, [4] cam work, [5] light work,

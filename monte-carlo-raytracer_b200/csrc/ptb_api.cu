@@ -581,6 +581,9 @@ int ptb_resize(ptb_context* c, int width, int height) {
     c->path_trace_depth = 0;
     c->named.erase("PathTraceBuffer");
     c->named.erase("BDPTSampledLightBuffer");
+    for (const char* k : {"BDPTConnectionRayO", "BDPTConnectionRayD", "BDPTConnectionContribution", "BDPTConnectionPixel",
+                          "BDPTConnectionVisibility", "BDPTConnectionWeight", "BDPTCounters"})
+        c->named.erase(k);
     c->bdpt_depth = -1;
     std::memset(&c->bd, 0, sizeof(c->bd));
     c->width = width;
@@ -872,6 +875,18 @@ int ptb_bdpt_reserve(ptb_context* c, int max_depth) {
             v.bytes = bytes;
             c->named["BDPTSampledLightBuffer"] = v;
         }
+        // the per-strategy connection records of the frame rendered last (include/ptb.h)
+        static const char* const kPublic[][2] = {{"bdpt_conn_o", "BDPTConnectionRayO"}, {"bdpt_conn_d", "BDPTConnectionRayD"},
+                                                 {"bdpt_conn_C", "BDPTConnectionContribution"}, {"bdpt_conn_src", "BDPTConnectionPixel"},
+                                                 {"bdpt_conn_vis", "BDPTConnectionVisibility"}, {"bdpt_conn_w", "BDPTConnectionWeight"},
+                                                 {"bdpt_cnt", "BDPTCounters"}};
+        for (const auto& pub : kPublic)
+            if (std::string(sp.name) == pub[0]) {
+                DevBuf v;
+                v.p = p;
+                v.bytes = bytes;
+                c->named[pub[1]] = v;
+            }
     }
     c->bdpt_depth = max_depth;
     return 0;

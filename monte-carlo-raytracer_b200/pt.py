@@ -318,6 +318,25 @@ class RenderPipeline:
         w, h = self._size
         return self.read_buffer("PathTraceBuffer", np.int32).reshape(-1, w * h, 4)[:max_depth]
 
+    def bdpt_connections(self):
+        """Per-strategy records of the BDPT frame rendered last (include/ptb.h: "BDPTConnection*"): dict of arrays
+        over the N surviving (pixel, t, s) strategies -- pixel, t, s, target, C (N, 3), visible, weight, ray_o, ray_d."""
+        n = int(self.read_buffer("BDPTCounters", np.uint32)[6])
+
+        def head(name, dtype, width):
+            out = np.empty(n * width, dtype=dtype)
+            if n:
+                _check(_lib().ptb_read_buffer(self.scene._h, name.encode(), _ptr(out), out.nbytes))
+            return out.reshape(n, width) if width > 1 else out
+        C = head("BDPTConnectionContribution", np.float32, 4)
+        d = head("BDPTConnectionRayD", np.float32, 4)
+        o = head("BDPTConnectionRayO", np.float32, 4)
+        ts = d[:, 3].copy().view(np.int32)
+        return {"pixel": head("BDPTConnectionPixel", np.int32, 1), "t": ts & 0xFF, "s": ts >> 8,
+                "target": C[:, 3].copy().view(np.int32), "C": C[:, :3].copy(),
+                "visible": head("BDPTConnectionVisibility", np.int32, 1) != 0,
+                "weight": head("BDPTConnectionWeight", np.float32, 1), "ray_o": o, "ray_d": d[:, :3].copy()}
+
     def merge_accumulation(self, comm=None, root=0):
         """The one collective of the multi-GPU path (ptb_merge_accumulation): NCCL reduce of the accumulation
         buffers to `root` (all-reduce when root < 0) + the division, on the context's stream."""

@@ -300,5 +300,7 @@ class RefBDPT:
                                       _ptr(self.sampled_cam), _ptr(self.sampled_light), _ptr(self.conn_rays),
                                       _ptr(self.conn_vis), _ptr(self.cam_counts), _ptr(self.light_counts),
                                       _ptr(self.temp_radiance), _ptr(self.final))
+        if trace is not None:      # ConnectVertices multiplied by the visibility and filled in the s = 0 slots (:722-737)
+            trace["connected"] = self.temp_radiance.copy()
         lib.ref_bdpt_copy_buffer(w, h, _ptr(self.final), _ptr(self.radiance))
         return self.radiance
