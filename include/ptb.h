@@ -141,7 +141,7 @@ int ptb_set_overlap(ptb_context* ctx, int halves);
  * traversal launch ends with the few rays that graze the mesh -- is filled by the work of the following frames.
  * ptb_accumulate consumes the frames in the order they were rendered, on the context's stream; every other entry
  * point first waits for the frames in flight, so the call sequence of the render passes and every per-sample value
- * are unchanged.  "RadianceBufferCL" names the buffer of the frame rendered last.  Costs 184 B per pixel of device
+ * are unchanged.  "RadianceBufferCL" names the buffer of the frame rendered last.  Costs 296 B per pixel of device
  * memory per extra frame. */
 int ptb_set_frames_in_flight(ptb_context* ctx, int depth);
 /* Order of the live-path queues of ptb_pt_render_sample.  The reference's sampler is a pure function of (pixel, frame,
@@ -163,6 +163,14 @@ int ptb_set_frames_in_flight(ptb_context* ctx, int depth);
 #define PTB_EST_NEE_MIS 2
 int ptb_set_estimator(ptb_context* ctx, int flags);
 int ptb_set_coherence(ptb_context* ctx, int mode);
+/* The shade stage of ptb_pt_render_sample as ONE kernel per bounce (0) or as TWO (1): k_shade_surface -- surface
+ * interaction, normal map, emission, material textures; drops the rays that missed; writes a 112-byte record per live
+ * vertex -- and k_shade_scatter -- light sampling, BSDF evaluation, lobe sampling on dense records (csrc/pt_kernels.cu,
+ * pt_shade.cuh).  Same expressions on the same values: per-sample results are identical.  Used for the reference's
+ * estimator only, and only while no material binds a specular-reflection / transmission / ior / roughness texture
+ * (the second kernel re-reads those properties from the material table); otherwise the single kernel runs. */
+#define PTB_DEFAULT_SHADE_SPLIT 0
+int ptb_set_shade_split(ptb_context* ctx, int on);
 
 /* Diagnostic record of ptb_pt_render_sample (no reference counterpart; parity evidence only).  With max_depth > 0 a
  * buffer "PathTraceBuffer" of int4[max_depth][P] is kept: entry [bounce * P + pixel] = {shape id, prim id, flags,

@@ -23,6 +23,7 @@ namespace mcrt {
 // cnt: [0],[1] live-path queue sizes (ping-pong)  [3],[4] work counters of the persistent kernels
 //      [5],[6] shadow-ray counts by bounce parity (the shadow rays of bounce b are traced together with the
 //      closest-hit rays of bounce b + 1, while nothing writes either set)
+//      [7] vertex records written by k_shade_surface for k_shade_scatter (split shade stage)
 //      [8..15] coherence-bucket counts of the queue being filled, [16..24] prefix sums of the queue about to be read
 __global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int cur, int bounce, int n_first, int bucketed) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -49,6 +50,7 @@ __global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int c
     cnt[5 + (bounce & 1)] = 0;
     cnt[3] = 0;
     cnt[4] = 0;
+    cnt[7] = 0;      // vertex records of the split shade stage
 }
 __global__ void k_sample_end(unsigned int* cnt, unsigned long long* stats, int last_bounce) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -247,6 +249,62 @@ k_trace_mixed(PtState s, int cur, int sh, int sh_bounce) {
 #ifndef PT_SHADE_MIN_BLOCKS
 #define PT_SHADE_MIN_BLOCKS 1      // register cap = 64K / (PT_SHADE_BLOCK * PT_SHADE_MIN_BLOCKS)
 #endif
+// What a shaded vertex leaves behind: the diagnostic record, the shadow-queue entry, the entry of the next live queue
+// (ordered per `s.coherence`) and the path state of the pixel.  Called by every thread of the CTA (barriers / ballots).
+template <bool EST>
+__device__ __forceinline__ void push_vertex_results(const PtState& s, int cur, int frame, int bounce, int cap, uint32_t px,
+                                                    bool in_range, bool active, bool pushShadow, bool pushNext,
+                                                    const ShadeOut& out) {
+    if (s.path_trace && in_range) {
+        const int4 h = s.hit[px];
+        const int flags = (active ? 1 : 0) | (pushShadow ? 2 : 0) | (active && out.hasEmission ? 4 : 0) |
+                          (pushNext ? 8 : 0) | (active ? (out.bsdfFlags << 8) : 0);
+        s.path_trace[(size_t)bounce * ((size_t)s.width * s.height) + px] = make_int4(h.x, h.y, flags, 0);
+    }
+    const unsigned si = warp_push(pushShadow, s.cnt + 5 + (bounce & 1));
+    if (pushShadow) {
+        s.sh_o[si] = make_float4(out.shadow.o.x, out.shadow.o.y, out.shadow.o.z, out.shadow.tmax);
+        s.sh_d[si] = make_float4(out.shadow.d.x, out.shadow.d.y, out.shadow.d.z, __int_as_float((int)px));
+        s.sh_L[si] = make_float4(out.direct.x, out.direct.y, out.direct.z, 0.0f);
+    }
+    if (s.coherence == 3) {
+        // CTA-local bucketing: the survivors of this CTA's chunk of the queue go to ONE contiguous chunk of the
+        // next queue, ordered by coherence key inside it.  Neighbouring pixels stay neighbours (texture and
+        // geometry locality of the next bounce), warps of the next shade launch still see runs of equal keys.
+        __shared__ unsigned s_cnt[PT_NUM_BUCKETS], s_pre[PT_NUM_BUCKETS], s_base;
+        if (threadIdx.x < PT_NUM_BUCKETS) s_cnt[threadIdx.x] = 0;
+        __syncthreads();
+        const unsigned key = pushNext ? coherence_key(s, px, frame, bounce + 1) : 0u;
+        const unsigned rank = warp_push_keyed(pushNext, key, s_cnt);      // shared-memory atomics
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned sum = 0;
+            for (int k = 0; k < PT_NUM_BUCKETS; ++k) {
+                s_pre[k] = sum;
+                sum += s_cnt[k];
+            }
+            s_base = sum ? atomicAdd(s.cnt + (1 - cur), sum) : 0u;
+        }
+        __syncthreads();
+        if (pushNext) s.queue[1 - cur][s_base + s_pre[key] + rank] = px;
+    } else if (s.coherence >= 1) {   // next bounce's queue goes to the staging regions, by coherence key
+        const unsigned key = pushNext ? coherence_key(s, px, frame, bounce + 1) : 0u;
+        const unsigned slot = warp_push_keyed(pushNext, key, s.cnt + 8);
+        if (pushNext) s.bucket[(size_t)key * (size_t)cap + slot] = px;
+    } else {
+        const unsigned ni = warp_push(pushNext, s.cnt + (1 - cur));
+        if (pushNext) s.queue[1 - cur][ni] = px;
+    }
+    if (pushNext) {
+        s.ray_o[px] = make_float4(out.nextO.x, out.nextO.y, out.nextO.z, RT_MAX_TRACE_DISTANCE);
+        s.ray_d[px] = make_float4(out.nextD.x, out.nextD.y, out.nextD.z, EST ? out.nextPdf : 0.0f);
+        if (EST && out.nextPdf > 0.0f)
+            s.direct_weight[px] = make_float4(out.nextDirectWeight.x, out.nextDirectWeight.y, out.nextDirectWeight.z, 0.0f);
+        s.throughput[px] = make_float4(out.throughput.x, out.throughput.y, out.throughput.z,
+                                       __int_as_float(out.bsdfFlags));
+    }
+}
+
 template <bool EST>
 __device__ __forceinline__ void shade_queue(const PtState& s, int cur, int frame, int bounce, int maxDepth, int cap,
                                             int estimator) {
@@ -310,54 +368,7 @@ __device__ __forceinline__ void shade_queue(const PtState& s, int cur, int frame
                 pushNext = out.continues;
             }
         }
-        if (s.path_trace && i < count) {
-            const int4 h = s.hit[px];
-            const int flags = (active ? 1 : 0) | (pushShadow ? 2 : 0) | (active && out.hasEmission ? 4 : 0) |
-                              (pushNext ? 8 : 0) | (active ? (out.bsdfFlags << 8) : 0);
-            s.path_trace[(size_t)bounce * ((size_t)s.width * s.height) + px] = make_int4(h.x, h.y, flags, 0);
-        }
-        const unsigned si = warp_push(pushShadow, s.cnt + 5 + (bounce & 1));
-        if (pushShadow) {
-            s.sh_o[si] = make_float4(out.shadow.o.x, out.shadow.o.y, out.shadow.o.z, out.shadow.tmax);
-            s.sh_d[si] = make_float4(out.shadow.d.x, out.shadow.d.y, out.shadow.d.z, __int_as_float((int)px));
-            s.sh_L[si] = make_float4(out.direct.x, out.direct.y, out.direct.z, 0.0f);
-        }
-        if (s.coherence == 3) {
-            // CTA-local bucketing: the survivors of this CTA's chunk of the queue go to ONE contiguous chunk of the
-            // next queue, ordered by coherence key inside it.  Neighbouring pixels stay neighbours (texture and
-            // geometry locality of the next bounce), warps of the next shade launch still see runs of equal keys.
-            __shared__ unsigned s_cnt[PT_NUM_BUCKETS], s_pre[PT_NUM_BUCKETS], s_base;
-            if (threadIdx.x < PT_NUM_BUCKETS) s_cnt[threadIdx.x] = 0;
-            __syncthreads();
-            const unsigned key = pushNext ? coherence_key(s, px, frame, bounce + 1) : 0u;
-            const unsigned rank = warp_push_keyed(pushNext, key, s_cnt);      // shared-memory atomics
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                unsigned sum = 0;
-                for (int k = 0; k < PT_NUM_BUCKETS; ++k) {
-                    s_pre[k] = sum;
-                    sum += s_cnt[k];
-                }
-                s_base = sum ? atomicAdd(s.cnt + (1 - cur), sum) : 0u;
-            }
-            __syncthreads();
-            if (pushNext) s.queue[1 - cur][s_base + s_pre[key] + rank] = px;
-        } else if (s.coherence >= 1) {   // next bounce's queue goes to the staging regions, by coherence key
-            const unsigned key = pushNext ? coherence_key(s, px, frame, bounce + 1) : 0u;
-            const unsigned slot = warp_push_keyed(pushNext, key, s.cnt + 8);
-            if (pushNext) s.bucket[(size_t)key * (size_t)cap + slot] = px;
-        } else {
-            const unsigned ni = warp_push(pushNext, s.cnt + (1 - cur));
-            if (pushNext) s.queue[1 - cur][ni] = px;
-        }
-        if (pushNext) {
-            s.ray_o[px] = make_float4(out.nextO.x, out.nextO.y, out.nextO.z, RT_MAX_TRACE_DISTANCE);
-            s.ray_d[px] = make_float4(out.nextD.x, out.nextD.y, out.nextD.z, EST ? out.nextPdf : 0.0f);
-            if (EST && out.nextPdf > 0.0f)
-                s.direct_weight[px] = make_float4(out.nextDirectWeight.x, out.nextDirectWeight.y, out.nextDirectWeight.z, 0.0f);
-            s.throughput[px] = make_float4(out.throughput.x, out.throughput.y, out.throughput.z,
-                                           __int_as_float(out.bsdfFlags));
-        }
+        push_vertex_results<EST>(s, cur, frame, bounce, cap, px, i < count, active, pushShadow, pushNext, out);
     }
 }
 
@@ -369,6 +380,132 @@ k_shade(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
 __global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
 k_shade_est(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
     shade_queue<true>(s, cur, frame, bounce, maxDepth, cap, s.estimator);
+}
+
+// ---------------------------------------------------------------------------------------------
+// shade in two stages (ptb_set_shade_split; pt_shade.cuh: shade_surface / shade_scatter)
+// ---------------------------------------------------------------------------------------------
+// k_shade_surface: one thread per queue entry -- drops the rays that missed, ends the paths that hit an emitter
+// (radiance += throughput * Le), and for every other vertex does the gather-heavy half (geometry, normal map, material
+// textures) and writes a 112-byte record.  A CTA's records go to ONE contiguous run of the record array in queue
+// order (warp ballots + one atomic per CTA and iteration), so the second stage reads them coalesced and the next
+// queue keeps neighbouring pixels together.  Record layout: 7 float4 planes of `vtx_stride` entries,
+//   0: p | pixel   1: gn | flags   2: sn | opacity.x   3: sdpdu | opacity.y   4: sdpdv | opacity.z   5: Kd | -   6: Ks | -
+#ifndef PT_SURF_BLOCK
+#define PT_SURF_BLOCK 256
+#endif
+#ifndef PT_SURF_MIN_BLOCKS
+#define PT_SURF_MIN_BLOCKS 3       // register cap 85: 24 warps per SM
+#endif
+__global__ void __launch_bounds__(PT_SURF_BLOCK, PT_SURF_MIN_BLOCKS)
+k_shade_surface(PtState s, int cur, int bounce) {
+    const unsigned count = s.cnt[cur];
+    const Scene sc = make_scene(s);
+    __shared__ unsigned s_warp[PT_SURF_BLOCK / 32], s_base;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const size_t P = (size_t)s.width * s.height;
+    const size_t stride = (size_t)s.vtx_stride;
+    for (unsigned cta_base = blockIdx.x * blockDim.x; cta_base < count; cta_base += gridDim.x * blockDim.x) {
+        const unsigned i = cta_base + threadIdx.x;
+        int kind = SURF_DEAD;
+        VertexRecord rec;
+        uint32_t px = 0;
+        if (i < count) {
+            px = s.queue[cur][i];
+            const int4 h = s.hit[px];
+            int trace_flags = 0;
+            if (h.x != -1 && h.y != -1) {
+                const float4 d = s.ray_d[px];
+                // the throughput and the previous lobe flags matter here only when the shape is an emitter
+                float4 tp = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+                const bool emitter = sc.shapes[h.x].lightID != RT_INVALID_ID;
+                if (emitter) tp = s.throughput[px];
+                V3 Le;
+                kind = shade_surface(sc, h.x, h.y, __int_as_float(h.z), __int_as_float(h.w), v3(d.x, d.y, d.z),
+                                     __float_as_int(tp.w), bounce, &Le, &rec);
+                rec.px = px;
+                if (kind == SURF_EMITTED) {
+                    const V3 t = bounce == 0 ? v3(1.0f) : v3(tp.x, tp.y, tp.z);
+                    const V3 e = t * Le;
+                    float4 r = s.radiance[px];
+                    r.x += e.x;
+                    r.y += e.y;
+                    r.z += e.z;
+                    s.radiance[px] = r;
+                    trace_flags = 1 | 4 | (__float_as_int(tp.w) << 8);
+                }
+            }
+            if (s.path_trace && kind != SURF_RECORD)
+                s.path_trace[(size_t)bounce * P + px] = make_int4(h.x, h.y, trace_flags, 0);
+        }
+        const bool has = kind == SURF_RECORD;
+        const unsigned m = __ballot_sync(0xffffffffu, has);
+        if (lane == 0) s_warp[warp] = (unsigned)__popc(m);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned sum = 0;
+            for (int w = 0; w < PT_SURF_BLOCK / 32; ++w) {
+                const unsigned t = s_warp[w];
+                s_warp[w] = sum;
+                sum += t;
+            }
+            s_base = sum ? atomicAdd(s.cnt + 7, sum) : 0u;
+        }
+        __syncthreads();
+        if (has) {
+            float4* v = s.vtx + (s_base + s_warp[warp] + (unsigned)__popc(m & ((1u << lane) - 1u)));
+            v[0 * stride] = make_float4(rec.p.x, rec.p.y, rec.p.z, __int_as_float((int)rec.px));
+            v[1 * stride] = make_float4(rec.gn.x, rec.gn.y, rec.gn.z, __int_as_float(rec.flags));
+            v[2 * stride] = make_float4(rec.sn.x, rec.sn.y, rec.sn.z, rec.opacity.x);
+            v[3 * stride] = make_float4(rec.sdpdu.x, rec.sdpdu.y, rec.sdpdu.z, rec.opacity.y);
+            v[4 * stride] = make_float4(rec.sdpdv.x, rec.sdpdv.y, rec.sdpdv.z, rec.opacity.z);
+            v[5 * stride] = make_float4(rec.Kd.x, rec.Kd.y, rec.Kd.z, 0.0f);
+            v[6 * stride] = make_float4(rec.Ks.x, rec.Ks.y, rec.Ks.z, 0.0f);
+        }
+        __syncthreads();      // s_warp / s_base are rewritten by the next iteration
+    }
+}
+
+// k_shade_scatter: one thread per record -- light sampling, BSDF evaluation, lobe sampling, the pushes of k_shade.
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
+k_shade_scatter(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
+    const unsigned count = s.cnt[7];
+    const Scene sc = make_scene(s);
+    const size_t stride = (size_t)s.vtx_stride;
+    for (unsigned cta_base = blockIdx.x * blockDim.x; cta_base < count; cta_base += gridDim.x * blockDim.x) {
+        const unsigned i = cta_base + threadIdx.x;
+        const bool active = i < count;
+        bool pushNext = false, pushShadow = false;
+        ShadeOut out;
+        out.hasEmission = false;
+        out.bsdfFlags = 0;
+        uint32_t px = 0;
+        if (active) {
+            const float4* v = s.vtx + i;
+            const float4 r0 = v[0 * stride], r1 = v[1 * stride], r2 = v[2 * stride], r3 = v[3 * stride],
+                         r4 = v[4 * stride], r5 = v[5 * stride], r6 = v[6 * stride];
+            VertexRecord rec;
+            rec.p = v3(r0.x, r0.y, r0.z);
+            rec.px = (uint32_t)__float_as_int(r0.w);
+            rec.gn = v3(r1.x, r1.y, r1.z);
+            rec.flags = __float_as_int(r1.w);
+            rec.sn = v3(r2.x, r2.y, r2.z);
+            rec.sdpdu = v3(r3.x, r3.y, r3.z);
+            rec.sdpdv = v3(r4.x, r4.y, r4.z);
+            rec.opacity = v3(r2.w, r3.w, r4.w);
+            rec.Kd = v3(r5.x, r5.y, r5.z);
+            rec.Ks = v3(r6.x, r6.y, r6.z);
+            px = rec.px;
+            const float4 d = s.ray_d[px];
+            const float4 tp = s.throughput[px];
+            shade_scatter(sc, rec, v3(d.x, d.y, d.z), v3(tp.x, tp.y, tp.z), __float_as_int(tp.w), frame, s.width, s.height,
+                          bounce, maxDepth, &out);
+            // a zero contribution adds nothing whatever the visibility: no shadow ray needed
+            pushShadow = out.shadow.written && !(out.direct.x == 0.0f && out.direct.y == 0.0f && out.direct.z == 0.0f);
+            pushNext = out.continues;
+        }
+        push_vertex_results<false>(s, cur, frame, bounce, cap, px, active, active, pushShadow, pushNext, out);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -650,6 +787,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
     // and are read once.
     static const int trace_per_sm = env_int("MCRT_TRACE_CTAS_PER_SM", 8);
     static const int shade_per_sm = env_int("MCRT_SHADE_CTAS_PER_SM", PT_SHADE_CTAS_PER_SM);
+    static const int surf_per_sm = env_int("MCRT_SURF_CTAS_PER_SM", PT_SURF_MIN_BLOCKS);
     static const int stagger = env_int("MCRT_OVERLAP_STAGGER", 0);   // measured: no gain from starting the halves a stage apart
 
     // the frame as one wavefront, or as two half-frame wavefronts on two streams (PtOverlap)
@@ -670,6 +808,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         t.sh_L += nA;
         t.cnt += PT_CNT_STRIDE;
         t.bucket += (size_t)PT_NUM_BUCKETS * nA;
+        if (t.vtx) t.vtx += nA;      // record planes keep the full-frame stride
         half[1] = {t, nA, n_pixels - nA, overlap->stream};
         cudaEventRecord(overlap->fork, stream);
         cudaStreamWaitEvent(overlap->stream, overlap->fork, 0);
@@ -723,6 +862,11 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                         k_shade_sorted_est<<<nb, PT_SHADE_BLOCK, sorted_smem, H.stream>>>(H.s, cur[h], frame, b, max_depth, stage_tables);
                     else
                         k_shade_sorted<<<nb, PT_SHADE_BLOCK, sorted_smem, H.stream>>>(H.s, cur[h], frame, b, max_depth, stage_tables);
+                } else if (s.shade_split && !s.estimator && s.vtx) {
+                    const int nb = min(sms * surf_per_sm, (H.n + PT_SURF_BLOCK - 1) / PT_SURF_BLOCK);
+                    k_shade_surface<<<nb, PT_SURF_BLOCK, 0, H.stream>>>(H.s, cur[h], b);
+                    k_shade_scatter<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
+                    ++launches;
                 } else if (s.estimator)
                     k_shade_est<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
                 else

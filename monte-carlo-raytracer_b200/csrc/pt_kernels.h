@@ -51,6 +51,9 @@ struct PtState {
     unsigned int* cnt;    // [0],[1] queue counts, [3],[4] work counters, [5],[6] shadow counts by bounce parity,
                           // [8..15] coherence-bucket counts, [16..24] their prefix sums (PT_CNT_STRIDE per half frame)
     uint32_t* bucket;     // coherence staging: PT_NUM_BUCKETS regions per half frame (pt_kernels.cu)
+    float4* vtx;          // split shade stage (ptb_set_shade_split): 7 planes of vtx_stride vertex records (pt_kernels.cu)
+    int vtx_stride;       // = pixels of the frame
+    int shade_split;      // 1 = k_shade_surface + k_shade_scatter instead of k_shade (reference estimator only)
     int estimator;        // PT_EST_* flags of the opt-in estimator switches (pt_shade.cuh); 0 = the reference's estimator
     int coherence;        // 0 = queues in push order, 1 = bounces >= 1 bucketed by sampler decisions, 2 = bounce 0 too
     unsigned long long* stats;  // [0] closest rays, [1] shadow rays, [2] shaded vertices, [3] samples

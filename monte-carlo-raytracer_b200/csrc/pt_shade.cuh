@@ -197,6 +197,151 @@ HD void shade_vertex(const Scene& sc, const ShadeIn& in, bool active, int frame,
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// The same vertex in TWO stages (ptb_set_shade_split; the reference's estimator only).  shade_vertex above needs
+// ~119 registers and 13,000 SASS instructions, so the shade kernel runs 16 warps per SM and waits: on the dependent
+// gathers of the surface half (hit -> shape -> indices -> vertices -> uv -> texture descriptors -> texels) and on
+// instruction fetch.  Split, the gather-heavy half (surface interaction, normal map, emission, material textures)
+// runs at a higher occupancy and drops the rays that missed; the arithmetic half (light sampling, BSDF evaluation,
+// lobe sampling) reads a dense 112-byte record per live vertex and keeps no lane idle.  Every expression is the one
+// shade_vertex evaluates, on the same values, so per-sample results are bit-identical (tests: the coherence /
+// split equality test and the full-size parity tests run either way).
+//
+// Which material properties travel in the record: those a texture can change here -- Kd, Ks and the opacity
+// (diffuse, glossy and opacity textures, the diffuse texture's alpha).  Kr, Kt, eta and the roughness are
+// re-read from the material table by the second stage, which is exact when the material binds no specular-
+// reflection / transmission / ior / roughness texture; the host uses the split only for scenes where none does
+// (split_supported in ptb_upload_scene).
+struct VertexRecord {
+    V3 p, gn, sn, sdpdu, sdpdv, Kd, Ks, opacity;
+    uint32_t px;
+    int flags;      // bit 0: traceErrorOffset is negative (back face), bit 1: the shape has a material, bits 8..: material id
+};
+enum { SURF_DEAD = 0, SURF_EMITTED = 1, SURF_RECORD = 2 };
+
+// first stage.  SURF_EMITTED: the path ends on an emitter, *Le is its radiance towards the ray origin.
+HD int shade_surface(const Scene& sc, int shapeId, int primId, float bu, float bv, V3 rayDir, int prevBsdfFlags,
+                     int bounce, V3* Le, VertexRecord* rec) {
+    RTInteraction si = computeSurfaceInteraction(sc, shapeId, primId, bu, bv);
+    si.wo = -rayDir;
+    const bool isBackfacing = dot(si.gn, si.wo) < 0.0f;
+    si.traceErrorOffset = isBackfacing ? -RT_TRACE_OFFSET : RT_TRACE_OFFSET;
+    const RTShape* shape = sc.shapes + shapeId;
+    const int materialId = shape->materialId;
+    const int lightID = shape->lightID;
+    applyNormalMapping(sc, materialId, &si);
+    const bool isEmitter = lightID != RT_INVALID_ID;
+    const bool sampledSpecular = (BSDF_SPECULAR & prevBsdfFlags) == BSDF_SPECULAR;
+    if (isEmitter && (bounce == 0 || sampledSpecular)) {
+        *Le = evalLightLe(sc.lights + lightID, si.gn, si.wo);
+        return SURF_EMITTED;
+    }
+    const bool hasMaterial = materialId != RT_INVALID_ID;
+    UberProps um;
+    um.Kd = um.Ks = um.opacity = v3(0.0f);
+    if (hasMaterial) getUberMaterialProperties(sc, materialId, &si, &um);
+    rec->p = si.p;
+    rec->gn = si.gn;
+    rec->sn = si.sn;
+    rec->sdpdu = si.sdpdu;
+    rec->sdpdv = si.sdpdv;
+    rec->Kd = um.Kd;
+    rec->Ks = um.Ks;
+    rec->opacity = um.opacity;
+    rec->flags = (isBackfacing ? 1 : 0) | (hasMaterial ? 2 : 0) | (hasMaterial ? (materialId << 8) : 0);
+    return SURF_RECORD;
+}
+
+// the properties getUberMaterialProperties takes from the material table alone (no texture bound)
+HD void untexturedUberProperties(const Scene& sc, int materialIdx, UberProps* p) {
+    const RTMaterial* m = sc.materials + materialIdx;
+    p->Kr = v3(1.0f) * v3(m->kr);
+    p->Kt = v3(1.0f) * v3(m->kt);
+    p->KtW = m->kt.w;
+    p->eta = m->eta;
+    if (sc.materialAlpha) {
+        const float2 a = sc.staged ? sc.materialAlpha[materialIdx] : __ldg(sc.materialAlpha + materialIdx);
+        p->roughness = v2(a.x, a.y);
+    } else {
+        p->roughness = v2(roughnessToAlpha(m->roughness.x), roughnessToAlpha(m->roughness.y));
+    }
+}
+
+// second stage: shade_vertex from the sampler on, for a vertex that is alive (not an emitter hit that ended the path)
+HD void shade_scatter(const Scene& sc, const VertexRecord& rec, V3 rayDir, V3 throughput, int prevBsdfFlags, int frame,
+                      int width, int height, int bounce, int maxDepth, ShadeOut* out) {
+    out->hasEmission = false;
+    out->nextPdf = 0.0f;
+    out->emitted = v3(0.0f);
+    out->direct = v3(0.0f);
+    out->shadow.written = false;
+    out->continues = false;
+    out->bsdfFlags = prevBsdfFlags;
+    if (bounce == 0) throughput = v3(1.0f);
+    out->throughput = throughput;
+
+    RTInteraction si;
+    si.p = rec.p;
+    si.gn = rec.gn;
+    si.sn = rec.sn;
+    si.sdpdu = rec.sdpdu;
+    si.sdpdv = rec.sdpdv;
+    si.wo = -rayDir;
+    si.traceErrorOffset = (rec.flags & 1) ? -RT_TRACE_OFFSET : RT_TRACE_OFFSET;
+    const bool hasMaterial = (rec.flags & 2) != 0;
+    UberProps um;
+    if (hasMaterial) {
+        um.Kd = rec.Kd;
+        um.Ks = rec.Ks;
+        um.opacity = rec.opacity;
+        untexturedUberProperties(sc, rec.flags >> 8, &um);
+    }
+
+    Sampler sampler = makeSampler(sc.sobolMatrices, (int)rec.px, frame, width, height, bounce);
+    // direct lighting: one light, one sample (PathTracing.cl:106-134)
+    float lightPdf = 0.0f;
+    V3 wiL = v3(0.0f), Li = v3(0.0f);
+    {
+        uint32_t lightIdx = ((uint32_t)floorf(getSample1D(&sampler) * sc.numLights));
+        lightIdx %= (uint32_t)sc.numLights;
+        V2 u = getSample2D(&sampler);
+        V3 unusedN, unusedP;
+        Li = sampleLightLi((int)lightIdx, sc, &si, u, &unusedP, &unusedN, &wiL, &lightPdf, &out->shadow);
+        lightPdf *= sc.lights[lightIdx].choicePdf;
+    }
+    {
+        V3 L = v3(0.0f);
+        if (hasMaterial) {
+            V3 bsdf = evaluateUberBSDF(um, &si, si.wo, wiL, TRANSPORT_MODE_RADIANCE);
+            bsdf *= absDot(wiL, si.sn);
+            if (!isNearZero(lightPdf)) L = Li * bsdf / lightPdf;
+        }
+        out->direct = throughput * L;
+    }
+    if (bounce + 1 < maxDepth) {   // extend the path (PathTracing.cl:137-172)
+        V2 bsdfSample = getSample2D(&sampler);
+        if (hasMaterial) {
+            float pdf = 0.0f;
+            int sampledType, unused;
+            V3 wi = v3(0.0f);
+            V3 f = sampleUberBSDF(um, &si, bsdfSample, TRANSPORT_MODE_RADIANCE, BSDF_ALL, si.wo, &wi, &pdf, &unused,
+                                  &sampledType);
+            out->bsdfFlags = sampledType;
+            if (!(isNearZero(pdf) || isBlack(f))) {
+                f /= pdf;
+                V3 tp = f * absDot(wi, si.sn);
+                out->throughput = throughput * tp;
+                float traceErrorOffset = si.traceErrorOffset;
+                if ((sampledType & BSDF_TRANSMISSION) != 0 && dot(si.gn, wi) * signf(traceErrorOffset) < 0.0f)
+                    traceErrorOffset *= -1.0f;
+                out->nextO = si.p + si.gn * traceErrorOffset;
+                out->nextD = wi;
+                out->continues = true;
+            }
+        }
+    }
+}
+
 // PathTracing.cl:13-35 GeneratePerspectiveRays: pixel CORNER uv, no +0.5 (E15)
 HD V3 primary_ray_dir(const RTPinholeCamera* cam, int x, int y) {
     const float rx = 1.0f / cam->width, ry = 1.0f / cam->height;

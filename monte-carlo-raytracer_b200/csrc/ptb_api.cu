@@ -77,6 +77,8 @@ struct ptb_context {
     int snap_next = 0;
     int halves = 2;
     int num_materials = 0;
+    int shade_split_wanted = 0;        // ptb_set_shade_split / MCRT_SHADE_SPLIT
+    bool split_supported = false;      // no material binds a texture the record of the split stage does not carry
     int num_scene_tris = 0;                       // triangles covered by the per-triangle shading records (0 = none)
     const int* d_tri_shape = nullptr;
     // Frames in flight (ptb_set_frames_in_flight): with D > 1 consecutive ptb_pt_render_sample calls run on D side
@@ -191,6 +193,19 @@ int ready(ptb_context* c) {
 }
 
 // ---- frames in flight
+// The split shade stage re-reads Kr, Kt, eta and the roughness from the material table in its second kernel
+// (pt_shade.cuh: untexturedUberProperties): exact unless a material binds a texture for one of them.
+bool materials_allow_split(const void* materials, int n) {
+    const unsigned char* m = (const unsigned char*)materials;
+    for (int i = 0; i < n; ++i) {
+        int ids[8];      // normalMap, diffuse, glossy, specReflection, transmission, opacity, roughness, ior (kernel_data.h:87-113)
+        std::memcpy(ids, m + (size_t)i * 128 + 96, sizeof(ids));
+        if (ids[3] != -1 || ids[4] != -1 || ids[6] != -1 || ids[7] != -1) return false;
+    }
+    return true;
+}
+void apply_shade_split(ptb_context* c) { c->st.shade_split = (c->shade_split_wanted && c->split_supported) ? 1 : 0; }
+
 bool pipelined(const ptb_context* c) { return c->slots.size() > 1 && !c->profiling && !c->st.path_trace; }
 
 // the context's stream waits (on the device) for every frame rendered on a side stream
@@ -273,6 +288,7 @@ int alloc_slots(ptb_context* c, int depth) {
             {"radiance", 16, (void**)&s.st.radiance}, {"direct_weight", 16, (void**)&s.st.direct_weight},
             {"queue0", 4, (void**)&s.st.queue[0]}, {"queue1", 4, (void**)&s.st.queue[1]},
             {"bucket", 4 * mcrt::PT_NUM_BUCKETS, (void**)&s.st.bucket},
+            {"vtx", 7 * 16, (void**)&s.st.vtx},
             {"sh_o", 16, (void**)&s.st.sh_o},     {"sh_d", 16, (void**)&s.st.sh_d},
             {"sh_L", 16, (void**)&s.st.sh_L},
         };
@@ -301,6 +317,7 @@ mcrt::PtState slot_state(const ptb_context* c, int k) {
         st.queue[0] = s.st.queue[0];
         st.queue[1] = s.st.queue[1];
         st.bucket = s.st.bucket;
+        st.vtx = s.st.vtx;
         st.sh_o = s.st.sh_o;
         st.sh_d = s.st.sh_d;
         st.sh_L = s.st.sh_L;
@@ -369,6 +386,8 @@ int ptb_create(rrb_api* api, ptb_context** out) {
     if (const char* v = getenv("MCRT_OVERLAP_HALVES")) c->halves = atoi(v) == 1 ? 1 : 2;   // profiling aid
     c->st.coherence = PTB_DEFAULT_COHERENCE;
     if (const char* v = getenv("MCRT_COHERENCE")) c->st.coherence = std::max(0, std::min(4, atoi(v)));   // variant runs
+    c->shade_split_wanted = PTB_DEFAULT_SHADE_SPLIT;
+    if (const char* v = getenv("MCRT_SHADE_SPLIT")) c->shade_split_wanted = atoi(v) ? 1 : 0;                  // variant runs
     PTB_CUDA(cudaStreamCreateWithFlags(&c->overlap.stream, cudaStreamNonBlocking));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.fork, cudaEventDisableTiming));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.join, cudaEventDisableTiming));
@@ -405,6 +424,17 @@ int ptb_set_coherence(ptb_context* c, int mode) {
     if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->st.coherence = mode;
+    return 0;
+}
+
+int ptb_set_shade_split(ptb_context* c, int on) {
+    if (!c || (on != 0 && on != 1)) return pfail(RRB_ERROR_INVALID_ARGUMENT, "shade split must be 0 or 1");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    c->shade_split_wanted = on;
+    apply_shade_split(c);
     return 0;
 }
 
@@ -478,6 +508,8 @@ int ptb_upload_scene(ptb_context* c, const ptb_scene_desc* d) {
         c->st.material_alpha = (const float2*)a;
         c->num_materials = d->num_materials;
         PTB_CUDA(mcrt::launch_material_alpha(c->st.materials, (float2*)a, d->num_materials, c->stream));
+        c->split_supported = materials_allow_split(d->materials, d->num_materials);
+        apply_shade_split(c);
     }
     // per-triangle shading records: index-array order, so a hit's (shape, prim) addresses startIdx / 3 + prim
     c->st.tri_shade = nullptr;
@@ -546,8 +578,11 @@ int ptb_update_scene_array(ptb_context* c, const char* array, const void* data, 
     PTB_CUDA(cudaMemcpyAsync(it->second.p, data, bytes, cudaMemcpyHostToDevice, c->stream));
     if (name == "shapes" && c->st.tri_shade)      // transforms changed: the per-triangle records follow
         PTB_CUDA(mcrt::launch_build_tri_shade(c->st, c->d_tri_shape, (float4*)c->st.tri_shade, c->num_scene_tris, c->stream));
-    if (name == "materials")
+    if (name == "materials") {
         PTB_CUDA(mcrt::launch_material_alpha(c->st.materials, (float2*)c->st.material_alpha, c->num_materials, c->stream));
+        c->split_supported = materials_allow_split(data, c->num_materials);
+        apply_shade_split(c);
+    }
     if (!c->slots.empty()) PTB_CUDA(cudaStreamSynchronize(c->stream));   // frames on side streams must see the update
     return 0;
 }
@@ -590,6 +625,7 @@ int ptb_resize(ptb_context* c, int width, int height) {
     c->height = height;
     c->st.width = width;
     c->st.height = height;
+    c->st.vtx_stride = width * height;
     const size_t P = (size_t)width * height;
     struct Spec {
         const char* name;
@@ -608,6 +644,7 @@ int ptb_resize(ptb_context* c, int width, int height) {
         {"queue0", 4, (void**)&s.queue[0], nullptr},
         {"queue1", 4, (void**)&s.queue[1], nullptr},
         {"bucket", 4 * mcrt::PT_NUM_BUCKETS, (void**)&s.bucket, nullptr},
+        {"vtx", 7 * 16, (void**)&s.vtx, nullptr},
         {"sh_o", 16, (void**)&s.sh_o, nullptr},
         {"sh_d", 16, (void**)&s.sh_d, nullptr},
         {"sh_L", 16, (void**)&s.sh_L, nullptr},

@@ -68,6 +68,7 @@ def _lib():
             "ptb_tonemap": [vp, ctypes.c_char_p, ctypes.c_float],
             "ptb_profile_enable": [vp, ctypes.c_int], "ptb_set_overlap": [vp, ctypes.c_int],
             "ptb_set_coherence": [vp, ctypes.c_int], "ptb_set_estimator": [vp, ctypes.c_int],
+            "ptb_set_shade_split": [vp, ctypes.c_int],
             "ptb_set_frames_in_flight": [vp, ctypes.c_int],
             "ptb_selftest_fdiv": [vp, vp, vp, vp, vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
@@ -298,6 +299,11 @@ class RenderPipeline:
         """Queue order of the fused wavefront: 0 push order, 1 bounces >= 1 bucketed by the sampler's light / lobe
         decisions, 2 bounce 0 too (include/ptb.h)."""
         _check(_lib().ptb_set_coherence(self.scene._h, int(mode)))
+
+    def set_shade_split(self, on):
+        """The shade stage as one kernel per bounce (False) or as surface + scatter kernels (True); identical results
+        (include/ptb.h: ptb_set_shade_split)."""
+        _check(_lib().ptb_set_shade_split(self.scene._h, 1 if on else 0))
 
     def set_estimator(self, russian_roulette=False, nee_mis=False):
         """Opt-in estimator switches (include/ptb.h PTB_EST_*); both off = the reference's estimator."""

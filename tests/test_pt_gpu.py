@@ -449,6 +449,54 @@ def test_coherence_bucketed_queues_equal_push_order_bitwise(api, halves):
             assert res[0][2][k] == res[mode][2][k], (mode, k)
 
 
+@pytest.mark.parametrize("coherence", [0, 3])
+def test_split_shade_stage_equals_the_single_kernel_bitwise(coherence):
+    """ptb_set_shade_split: the shade stage as k_shade_surface (geometry, normal map, emission, material textures,
+    a 112-byte record per live vertex) + k_shade_scatter (light sampling, BSDF evaluation, lobe sampling) evaluates
+    the expressions of the single kernel on the same values: radiance, accumulated image, counters and the
+    per-bounce path record are bit-identical -- on textured two-lobe materials with alpha masks and three light
+    types, on the glass / mirror Cornell box (specular chains: emission after a specular bounce ends the path in the
+    first kernel), with half-frame wavefronts, frames in flight and a tile partition."""
+    cases = [(scene_library.sponza_class(64), 512, 320, 5, {}),
+             (scene_library.cornell_box(True), 256, 256, 6, {}),
+             (scene_library.sponza_class(64), 512, 320, 4, {"in_flight": 3, "partition": (1, 3)})]
+    for scene, w, h, depth, opt in cases:
+        res = []
+        for split in (False, True):
+            a = rr.IntersectionApi.Create(0)
+            try:
+                pl = pt.make_pt_pipeline(a, scene, w, h, depth)
+                pl.ensure_size()
+                pl.set_coherence(coherence)
+                pl.set_shade_split(split)
+                if "partition" in opt:
+                    pl.set_partition(*opt["partition"])
+                if "in_flight" in opt:
+                    pl.set_frames_in_flight(opt["in_flight"])
+                else:
+                    pl.set_path_trace(depth)
+                frames, traces = [], []
+                for _ in range(4):
+                    pl.update()
+                    if "in_flight" not in opt:
+                        frames.append(pl.read_buffer("RadianceBufferCL").reshape(-1, 4).copy())
+                        traces.append(pl.path_trace(depth).copy())
+                img = pl.read_buffer("NextFrameImageCL").reshape(-1, 4).copy()
+                cnt = pl.counters()
+                pl.scene.destroy()
+            finally:
+                rr.IntersectionApi.Delete(a)
+            res.append((frames, traces, img, cnt))
+        one, two = res
+        assert one[3]["shaded_vertices"] > w * h // 4
+        for f in range(len(one[0])):
+            assert np.array_equal(one[0][f].view(np.uint32), two[0][f].view(np.uint32)), f
+            assert np.array_equal(one[1][f], two[1][f]), f
+        assert np.array_equal(one[2].view(np.uint32), two[2].view(np.uint32))
+        for k in ("samples", "closest_rays", "shadow_rays", "shaded_vertices"):
+            assert one[3][k] == two[3][k], k
+
+
 @pytest.mark.parametrize("depth_in_flight", [2, 4])
 def test_frames_in_flight_equal_one_at_a_time_bitwise(api, depth_in_flight):
     """ptb_set_frames_in_flight: consecutive frames rendered concurrently on side streams (own wavefront state and
