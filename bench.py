@@ -358,7 +358,11 @@ def own_arm(args):
         ev1.record(stream)
         barrier()
         ms_single = max_over_ranks(ev0.elapsed_time(ev1))
-        prof = pl.profile_collect()
+        kern = pl.profile_collect_kernels()
+        split = kern["k_shade_scatter"][1] > 0       # the shade stage ran as surface + scatter kernels
+        prof = {k: kern[k] for k in pl.STAGES}
+        if split:                                     # the stage as a whole: one "launch" = one bounce = two kernels
+            prof["k_shade"] = (kern["k_shade"][0] + kern["k_shade_scatter"][0], kern["k_shade"][1])
         pl.profile_enable(False)
         pl.set_overlap(timed_halves)
 
@@ -418,10 +422,13 @@ def own_arm(args):
         nb = max(nb, 1)
         achieved = top_bytes / max(top_ms * 1e-3, 1e-12) / 1e9
         traffic = None      # measured per build: run_extras() fills it from profiles/kernel_counters.json
-        roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
+        shade_name = "k_shade_surface+k_shade_scatter" if split else "k_shade"
+        roofline = {"bound": "hbm", "kernel": shade_name if top == "k_shade" else top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                     "launches": nb, "avg_launch_ms": top_ms / nb, "algorithmic_bytes_per_launch": top_bytes / nb,
-                    "stage_ms_per_step": {k: v[0] / K for k, v in stages.items()},
+                    "stage_ms_per_step": dict({k: v[0] / K for k, v in stages.items()},
+                                              **({"k_shade_surface": kern["k_shade"][0] / K, "k_shade_scatter": kern["k_shade_scatter"][0] / K}
+                                                 if split else {})),
                     "stage_share_of_step": {k: v[0] / max(ms_single, 1e-9) for k, v in stages.items()},
                     "stage_timing": "separate %d-step loop, one frame at a time, one wavefront per frame (%.3f ms/step); the timed region %s"
                                     % (K, ms_single / K, ("keeps %d frames in flight on side streams" % fif) if fif > 1 else

@@ -153,7 +153,7 @@ int ptb_set_frames_in_flight(ptb_context* ctx, int depth);
  * memory by (light type, lobe half, material id), drops the rays that missed, and stages the scene's small tables in
  * shared memory with bulk asynchronous copies (csrc/pt_kernels.cu: shade_sorted; measured slower than 3 on the
  * benchmark scene, profiles/r02_shade.md).  Per-sample results are identical in all modes. */
-#define PTB_DEFAULT_COHERENCE 3
+#define PTB_DEFAULT_COHERENCE 0      /* push order: fastest with the split shade stage (r02q); 3 was r01's default for the single kernel */
 /* Opt-in estimator switches of ptb_pt_render_sample (default 0 = the reference's estimator, PathTracing.cl:52-184,
  * which has neither): Russian roulette from the third vertex on, and power-heuristic MIS between next-event
  * estimation and BSDF sampling for triangle-mesh area lights.  Both keep the expectation of the reference's
@@ -169,7 +169,7 @@ int ptb_set_coherence(ptb_context* ctx, int mode);
  * pt_shade.cuh).  Same expressions on the same values: per-sample results are identical.  Used for the reference's
  * estimator only, and only while no material binds a specular-reflection / transmission / ior / roughness texture
  * (the second kernel re-reads those properties from the material table); otherwise the single kernel runs. */
-#define PTB_DEFAULT_SHADE_SPLIT 0
+#define PTB_DEFAULT_SHADE_SPLIT 1
 int ptb_set_shade_split(ptb_context* ctx, int on);
 
 /* Diagnostic record of ptb_pt_render_sample (no reference counterpart; parity evidence only).  With max_depth > 0 a
@@ -188,10 +188,15 @@ enum ptb_stage {
     PTB_STAGE_TRACE_CLOSEST = 0,   /* closest-hit rays of bounce 0 */
     PTB_STAGE_TRACE_MIXED = 1,     /* closest-hit rays of bounce b + shadow rays of bounce b - 1, one launch */
     PTB_STAGE_TRACE_SHADOW = 2,    /* shadow rays of the last bounce */
-    PTB_STAGE_SHADE = 3
+    PTB_STAGE_SHADE = 3,           /* the shade stage: k_shade, or k_shade_surface + k_shade_scatter (ptb_set_shade_split) */
+    PTB_STAGE_SHADE_SCATTER = 4,   /* ptb_profile_collect_kernels only: the scatter kernel; [3] is then the surface kernel */
+    PTB_NUM_STAGES = 5
 };
 int ptb_profile_enable(ptb_context* ctx, int on);
 int ptb_profile_collect(ptb_context* ctx, double ms[4], int64_t launches[4]);
+/* The same per KERNEL: with the split shade stage, entry PTB_STAGE_SHADE holds the surface kernel alone and entry
+ * PTB_STAGE_SHADE_SCATTER the scatter kernel (0 for the single kernel). */
+int ptb_profile_collect_kernels(ptb_context* ctx, double ms[PTB_NUM_STAGES], int64_t launches[PTB_NUM_STAGES]);
 
 /* ReconstructionPass (reconstruction.cl:6-60): clamp, filter weight of the frame's pixel offset,
  * running weighted mean into "NextFrameImageCL"; frame 0 restarts the mean (reconstruction.cl:47-57). */

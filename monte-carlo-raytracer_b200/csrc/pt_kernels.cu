@@ -390,7 +390,7 @@ k_shade_est(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
 // textures) and writes a 112-byte record.  A CTA's records go to ONE contiguous run of the record array in queue
 // order (warp ballots + one atomic per CTA and iteration), so the second stage reads them coalesced and the next
 // queue keeps neighbouring pixels together.  Record layout: 7 float4 planes of `vtx_stride` entries,
-//   0: p | pixel   1: gn | flags   2: sn | opacity.x   3: sdpdu | opacity.y   4: sdpdv | opacity.z   5: Kd | -   6: Ks | -
+//   0: p | pixel   1: gn | flags   2: sn | opacity.x   3: sdpdu | opacity.y   4: sdpdv | opacity.z   5: Kd | key   6: Ks | -
 #ifndef PT_SURF_BLOCK
 #define PT_SURF_BLOCK 256
 #endif
@@ -398,7 +398,7 @@ k_shade_est(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
 #define PT_SURF_MIN_BLOCKS 3       // register cap 85: 24 warps per SM
 #endif
 __global__ void __launch_bounds__(PT_SURF_BLOCK, PT_SURF_MIN_BLOCKS)
-k_shade_surface(PtState s, int cur, int bounce) {
+k_shade_surface(PtState s, int cur, int frame, int bounce) {
     const unsigned count = s.cnt[cur];
     const Scene sc = make_scene(s);
     __shared__ unsigned s_warp[PT_SURF_BLOCK / 32], s_base;
@@ -422,8 +422,7 @@ k_shade_surface(PtState s, int cur, int bounce) {
                 if (emitter) tp = s.throughput[px];
                 V3 Le;
                 kind = shade_surface(sc, h.x, h.y, __int_as_float(h.z), __int_as_float(h.w), v3(d.x, d.y, d.z),
-                                     __float_as_int(tp.w), bounce, &Le, &rec);
-                rec.px = px;
+                                     __float_as_int(tp.w), bounce, px, frame, s.width, s.height, &Le, &rec);
                 if (kind == SURF_EMITTED) {
                     const V3 t = bounce == 0 ? v3(1.0f) : v3(tp.x, tp.y, tp.z);
                     const V3 e = t * Le;
@@ -459,7 +458,7 @@ k_shade_surface(PtState s, int cur, int bounce) {
             v[2 * stride] = make_float4(rec.sn.x, rec.sn.y, rec.sn.z, rec.opacity.x);
             v[3 * stride] = make_float4(rec.sdpdu.x, rec.sdpdu.y, rec.sdpdu.z, rec.opacity.y);
             v[4 * stride] = make_float4(rec.sdpdv.x, rec.sdpdv.y, rec.sdpdv.z, rec.opacity.z);
-            v[5 * stride] = make_float4(rec.Kd.x, rec.Kd.y, rec.Kd.z, 0.0f);
+            v[5 * stride] = make_float4(rec.Kd.x, rec.Kd.y, rec.Kd.z, __int_as_float(rec.key));
             v[6 * stride] = make_float4(rec.Ks.x, rec.Ks.y, rec.Ks.z, 0.0f);
         }
         __syncthreads();      // s_warp / s_base are rewritten by the next iteration
@@ -467,7 +466,17 @@ k_shade_surface(PtState s, int cur, int bounce) {
 }
 
 // k_shade_scatter: one thread per record -- light sampling, BSDF evaluation, lobe sampling, the pushes of k_shade.
-__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
+// This half gathers nothing but its record and the pixel's ray / throughput and is bound by dependent arithmetic
+// (ncu r02l: stall `wait` 30 %, 4 warps per scheduler at 121 registers), so -- unlike the single kernel, where a lower
+// register cap only added spills to a kernel that waits for memory -- it gains from more resident warps: capped at
+// 85 registers (3 x 256 threads per SM, 24 warps) it is 3 % faster than at 121 (profiles/r02_full_frame.md).
+#ifndef PT_SCAT_BLOCK
+#define PT_SCAT_BLOCK 256
+#endif
+#ifndef PT_SCAT_MIN_BLOCKS
+#define PT_SCAT_MIN_BLOCKS 3
+#endif
+__global__ void __launch_bounds__(PT_SCAT_BLOCK, PT_SCAT_MIN_BLOCKS)
 k_shade_scatter(PtState s, int cur, int frame, int bounce, int maxDepth, int cap) {
     const unsigned count = s.cnt[7];
     const Scene sc = make_scene(s);
@@ -505,6 +514,202 @@ k_shade_scatter(PtState s, int cur, int frame, int bounce, int maxDepth, int cap
             pushNext = out.continues;
         }
         push_vertex_results<false>(s, cur, frame, bounce, cap, px, active, active, pushShadow, pushNext, out);
+    }
+}
+
+// k_shade_scatter_sorted: the same work in an order that keeps a warp's lanes together.  With dense records the
+// second stage is bound by its instruction stream, and ncu counts 16 of 32 lanes active per instruction (r02l): the
+// lanes of a warp sample different light types and different lobes.  This stage gathers nothing but its own records
+// and the pixel's ray / throughput, so -- unlike the single kernel's consumer-side sort (mode 4), which lost more to
+// texture / geometry locality than it won -- the order of the ARITHMETIC is free, as long as the MEMORY traffic keeps
+// the record order (a first version that also gathered and scattered in sorted order was slower: 25 of 32 lanes,
+// 33 % fewer warp instructions, +15 % time).  So a CTA
+//   1. brings a CHUNK of consecutive records into shared memory with one bulk asynchronous copy per record plane
+//      (cp.async.bulk, completion on an mbarrier), and the pixels' ray directions / throughputs beside them;
+//   2. counting-sorts the chunk's record indices by the 7-bit key the first stage left in the record (scatter_key);
+//   3. shades in sorted order out of shared memory, leaving the next ray and throughput in the record's own slot;
+//   4. writes the survivors' path state and the next queue's entries in RECORD order -- one contiguous run per chunk,
+//      neighbouring pixels stay neighbours for the next bounce's surface stage.
+#define PT_SCAT_CHUNK 1024
+#define PT_SCAT_PER_THREAD (PT_SCAT_CHUNK / PT_SHADE_BLOCK)
+#define PT_SCAT_KEYS 128
+#define PT_SCAT_PLANES 9        // 7 record planes + ray direction + throughput
+static_assert(PT_SCAT_CHUNK % PT_SHADE_BLOCK == 0 && PT_SCAT_KEYS <= PT_SHADE_BLOCK && PT_SCAT_CHUNK <= 65536, "scatter sort geometry");
+static size_t scatter_sorted_smem() {
+    return (size_t)PT_SCAT_PLANES * PT_SCAT_CHUNK * 16 + PT_SCAT_CHUNK * 2 + PT_SCAT_CHUNK + PT_SCAT_KEYS * 4 +
+           (4 + PT_SHADE_BLOCK / 32) * 4 + 8;
+}
+__global__ void __launch_bounds__(PT_SHADE_BLOCK, PT_SHADE_MIN_BLOCKS)
+k_shade_scatter_sorted(PtState s, int cur, int frame, int bounce, int maxDepth) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    float4* s_rec = (float4*)smem;                                            // [PLANES][CHUNK]
+    unsigned short* s_idx = (unsigned short*)(s_rec + PT_SCAT_PLANES * PT_SCAT_CHUNK);   // sorted position -> record offset
+    unsigned char* s_next = (unsigned char*)(s_idx + PT_SCAT_CHUNK);          // record offset -> the path goes on
+    unsigned* s_bin = (unsigned*)(s_next + PT_SCAT_CHUNK);
+    unsigned* s_misc = s_bin + PT_SCAT_KEYS;                                  // [0] queue base, [1] run counter, [4..] warp sums
+    uint64_t* s_bar = (uint64_t*)(s_misc + 4 + PT_SHADE_BLOCK / 32);
+    const unsigned count = s.cnt[7];
+    const Scene sc = make_scene(s);
+    const size_t stride = (size_t)s.vtx_stride;
+    const size_t P = (size_t)s.width * s.height;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    unsigned chunk = PT_SCAT_CHUNK;
+    const unsigned per_cta = (count + gridDim.x - 1) / gridDim.x;
+    if (per_cta < PT_SCAT_CHUNK) chunk = max((unsigned)PT_SHADE_BLOCK, (per_cta + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK * PT_SHADE_BLOCK);
+    const unsigned nchunks = (count + chunk - 1) / chunk;
+    if (threadIdx.x == 0) mbar_init(s_bar, 1);
+    __syncthreads();
+    unsigned parity = 0;
+    for (unsigned c = blockIdx.x; c < nchunks; c += gridDim.x) {
+        const unsigned base = c * chunk;
+        const unsigned n = min(chunk, count - base);
+        // ---- 1. the chunk's records: one bulk copy per plane
+        if (threadIdx.x == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the slots were written by the last chunk
+            mbar_expect_tx(s_bar, 7u * n * 16u);
+            for (int f = 0; f < 7; ++f)
+                bulk_copy_g2s(s_rec + f * PT_SCAT_CHUNK, s.vtx + f * stride + base, n * 16u, s_bar);
+        }
+        if (threadIdx.x < PT_SCAT_KEYS) s_bin[threadIdx.x] = 0;
+        if (threadIdx.x == 0) s_misc[1] = 0;      // run counter of step 3
+        __syncthreads();
+        mbar_wait(s_bar, parity);
+        parity ^= 1u;
+        // ---- 2. keys and ranks; the pixels' ray directions and throughputs (record order: neighbouring pixels)
+        unsigned e_key[PT_SCAT_PER_THREAD], e_rank[PT_SCAT_PER_THREAD];
+#pragma unroll
+        for (int j = 0; j < PT_SCAT_PER_THREAD; ++j) {
+            const unsigned e = threadIdx.x + j * PT_SHADE_BLOCK;
+            e_key[j] = 0xffffffffu;
+            if (e < n) {
+                const uint32_t px = (uint32_t)__float_as_int(s_rec[0 * PT_SCAT_CHUNK + e].w);
+                s_rec[7 * PT_SCAT_CHUNK + e] = s.ray_d[px];
+                s_rec[8 * PT_SCAT_CHUNK + e] = s.throughput[px];
+                s_next[e] = 0;
+                e_key[j] = (unsigned)__float_as_int(s_rec[5 * PT_SCAT_CHUNK + e].w) & (PT_SCAT_KEYS - 1);
+                e_rank[j] = atomicAdd(s_bin + e_key[j], 1u);
+            }
+        }
+        __syncthreads();
+        {   // exclusive scan of the bins
+            unsigned v = threadIdx.x < PT_SCAT_KEYS ? s_bin[threadIdx.x] : 0u;
+            unsigned incl = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned t = __shfl_up_sync(0xffffffffu, incl, d);
+                if ((int)lane >= d) incl += t;
+            }
+            if (lane == 31 && warp < PT_SCAT_KEYS / 32) s_misc[4 + warp] = incl;
+            __syncthreads();
+            if (threadIdx.x < PT_SCAT_KEYS) {
+                unsigned before = 0;
+                for (unsigned w = 0; w < warp; ++w) before += s_misc[4 + w];
+                s_bin[threadIdx.x] = before + incl - v;
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int j = 0; j < PT_SCAT_PER_THREAD; ++j)
+            if (e_key[j] != 0xffffffffu) s_idx[s_bin[e_key[j]] + e_rank[j]] = (unsigned short)(threadIdx.x + j * PT_SHADE_BLOCK);
+        __syncthreads();
+        // ---- 3. shade in sorted order.  Warps PULL runs of 32 sorted records from a shared counter: the cost of a run
+        // depends on its key (a microfacet lobe costs several Lambertian ones), a static assignment leaves the CTA
+        // waiting at the barrier below for its slowest warp.
+        for (;;) {
+            unsigned r = 0;
+            if (lane == 0) r = atomicAdd(s_misc + 1, 32u);
+            r = __shfl_sync(0xffffffffu, r, 0);
+            if (r >= n) break;
+            const unsigned j = r + lane;
+            const bool active = j < n;
+            bool pushNext = false, pushShadow = false;
+            ShadeOut out;
+            out.hasEmission = false;
+            out.bsdfFlags = 0;
+            uint32_t px = 0;
+            unsigned e = 0;
+            if (active) {
+                e = s_idx[j];
+                const float4* v = s_rec + e;
+                const float4 r0 = v[0 * PT_SCAT_CHUNK], r1 = v[1 * PT_SCAT_CHUNK], r2 = v[2 * PT_SCAT_CHUNK],
+                             r3 = v[3 * PT_SCAT_CHUNK], r4 = v[4 * PT_SCAT_CHUNK], r5 = v[5 * PT_SCAT_CHUNK],
+                             r6 = v[6 * PT_SCAT_CHUNK], d = v[7 * PT_SCAT_CHUNK], tp = v[8 * PT_SCAT_CHUNK];
+                VertexRecord rec;
+                rec.p = v3(r0.x, r0.y, r0.z);
+                rec.px = (uint32_t)__float_as_int(r0.w);
+                rec.gn = v3(r1.x, r1.y, r1.z);
+                rec.flags = __float_as_int(r1.w);
+                rec.sn = v3(r2.x, r2.y, r2.z);
+                rec.sdpdu = v3(r3.x, r3.y, r3.z);
+                rec.sdpdv = v3(r4.x, r4.y, r4.z);
+                rec.opacity = v3(r2.w, r3.w, r4.w);
+                rec.Kd = v3(r5.x, r5.y, r5.z);
+                rec.Ks = v3(r6.x, r6.y, r6.z);
+                rec.key = 0;
+                px = rec.px;
+                shade_scatter(sc, rec, v3(d.x, d.y, d.z), v3(tp.x, tp.y, tp.z), __float_as_int(tp.w), frame, s.width, s.height,
+                              bounce, maxDepth, &out);
+                pushShadow = out.shadow.written && !(out.direct.x == 0.0f && out.direct.y == 0.0f && out.direct.z == 0.0f);
+                pushNext = out.continues;
+                if (s.path_trace) {
+                    const int4 h = s.hit[px];
+                    const int flags = 1 | (pushShadow ? 2 : 0) | (pushNext ? 8 : 0) | (out.bsdfFlags << 8);
+                    s.path_trace[(size_t)bounce * P + px] = make_int4(h.x, h.y, flags, 0);
+                }
+            }
+            const unsigned si = warp_push(pushShadow, s.cnt + 5 + (bounce & 1));
+            if (pushShadow) {
+                s.sh_o[si] = make_float4(out.shadow.o.x, out.shadow.o.y, out.shadow.o.z, out.shadow.tmax);
+                s.sh_d[si] = make_float4(out.shadow.d.x, out.shadow.d.y, out.shadow.d.z, __int_as_float((int)px));
+                s.sh_L[si] = make_float4(out.direct.x, out.direct.y, out.direct.z, 0.0f);
+            }
+            if (pushNext) {      // the next path state waits in the record's own slot (plane 0 keeps the pixel)
+                s_next[e] = 1;
+                s_rec[1 * PT_SCAT_CHUNK + e] = make_float4(out.nextO.x, out.nextO.y, out.nextO.z, RT_MAX_TRACE_DISTANCE);
+                s_rec[2 * PT_SCAT_CHUNK + e] = make_float4(out.nextD.x, out.nextD.y, out.nextD.z, 0.0f);
+                s_rec[3 * PT_SCAT_CHUNK + e] = make_float4(out.throughput.x, out.throughput.y, out.throughput.z,
+                                                           __int_as_float(out.bsdfFlags));
+            }
+        }
+        __syncthreads();
+        // ---- 4. survivors in record order: thread t owns PER_THREAD consecutive records
+        {
+            const unsigned first = threadIdx.x * PT_SCAT_PER_THREAD;
+            unsigned mine = 0;
+#pragma unroll
+            for (int j = 0; j < PT_SCAT_PER_THREAD; ++j) mine += (first + j < n && s_next[first + j]) ? 1u : 0u;
+            unsigned incl = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned t = __shfl_up_sync(0xffffffffu, incl, d);
+                if ((int)lane >= d) incl += t;
+            }
+            if (lane == 31) s_misc[4 + warp] = incl;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                unsigned sum = 0;
+                for (int w = 0; w < PT_SHADE_BLOCK / 32; ++w) {
+                    const unsigned t = s_misc[4 + w];
+                    s_misc[4 + w] = sum;
+                    sum += t;
+                }
+                s_misc[0] = sum ? atomicAdd(s.cnt + (1 - cur), sum) : 0u;
+            }
+            __syncthreads();
+            unsigned at = s_misc[0] + s_misc[4 + warp] + incl - mine;
+#pragma unroll
+            for (int j = 0; j < PT_SCAT_PER_THREAD; ++j) {
+                const unsigned e = first + j;
+                if (e < n && s_next[e]) {
+                    const uint32_t px = (uint32_t)__float_as_int(s_rec[0 * PT_SCAT_CHUNK + e].w);
+                    s.queue[1 - cur][at++] = px;
+                    s.ray_o[px] = s_rec[1 * PT_SCAT_CHUNK + e];
+                    s.ray_d[px] = s_rec[2 * PT_SCAT_CHUNK + e];
+                    s.throughput[px] = s_rec[3 * PT_SCAT_CHUNK + e];
+                }
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -788,6 +993,11 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
     static const int trace_per_sm = env_int("MCRT_TRACE_CTAS_PER_SM", 8);
     static const int shade_per_sm = env_int("MCRT_SHADE_CTAS_PER_SM", PT_SHADE_CTAS_PER_SM);
     static const int surf_per_sm = env_int("MCRT_SURF_CTAS_PER_SM", PT_SURF_MIN_BLOCKS);
+    static const int scat_per_sm = env_int("MCRT_SCAT_CTAS_PER_SM", PT_SCAT_MIN_BLOCKS);
+    // 1 = k_shade_scatter_sorted (25 of 32 lanes active instead of 16, a third fewer warp instructions, 2 % faster than
+    // record order at the same occupancy -- and 3 % slower than record order at 24 warps per SM, which its 151 KB of
+    // shared memory rules out: profiles/r02_full_frame.md)
+    static const int scatter_sort = env_int("MCRT_SCATTER_SORT", 0);
     static const int stagger = env_int("MCRT_OVERLAP_STAGGER", 0);   // measured: no gain from starting the halves a stage apart
 
     // the frame as one wavefront, or as two half-frame wavefronts on two streams (PtOverlap)
@@ -825,6 +1035,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         const int max_smem = (int)shade_sorted_smem(PT_STAGE_MAX_BYTES);
         cudaFuncSetAttribute(k_shade_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         cudaFuncSetAttribute(k_shade_sorted_est, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        cudaFuncSetAttribute(k_shade_scatter_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scatter_sorted_smem());
         smem_attr_set = true;
     }
     auto blocks_trace = [&](int n) { return min(sms * trace_per_sm, (n + 127) / 128); };
@@ -864,14 +1075,20 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                         k_shade_sorted<<<nb, PT_SHADE_BLOCK, sorted_smem, H.stream>>>(H.s, cur[h], frame, b, max_depth, stage_tables);
                 } else if (s.shade_split && !s.estimator && s.vtx) {
                     const int nb = min(sms * surf_per_sm, (H.n + PT_SURF_BLOCK - 1) / PT_SURF_BLOCK);
-                    k_shade_surface<<<nb, PT_SURF_BLOCK, 0, H.stream>>>(H.s, cur[h], b);
-                    k_shade_scatter<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
+                    k_shade_surface<<<nb, PT_SURF_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b);
+                    if (timer) timer->mark(h, H.stream, StageTimer::SHADE);
+                    if (scatter_sort)
+                        k_shade_scatter_sorted<<<min(sms, (H.n + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK), PT_SHADE_BLOCK, scatter_sorted_smem(), H.stream>>>(
+                            H.s, cur[h], frame, b, max_depth);
+                    else
+                        k_shade_scatter<<<min(sms * scat_per_sm, (H.n + PT_SCAT_BLOCK - 1) / PT_SCAT_BLOCK), PT_SCAT_BLOCK, 0, H.stream>>>(
+                            H.s, cur[h], frame, b, max_depth, H.n);
                     ++launches;
                 } else if (s.estimator)
                     k_shade_est<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
                 else
                     k_shade<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
-                if (timer) timer->mark(h, H.stream, StageTimer::SHADE);
+                if (timer) timer->mark(h, H.stream, (s.shade_split && !s.estimator && s.vtx && s.coherence != 4) ? StageTimer::SHADE_SCATTER : StageTimer::SHADE);
                 launches += 3;
                 cur[h] = 1 - cur[h];
             }

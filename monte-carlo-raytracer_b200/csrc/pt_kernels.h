@@ -80,7 +80,8 @@ struct PtState {
 // caller reads the gaps after a synchronise (ptb_profile_collect).  Marks per bounce: before the
 // closest-hit trace, before shade, before the shadow trace, after the shadow trace.
 struct StageTimer {
-    enum { NONE = -1, TRACE_CLOSEST = 0, TRACE_MIXED = 1, TRACE_SHADOW = 2, SHADE = 3, NUM_STAGES = 4 };   // = ptb_stage
+    // = ptb_stage.  SHADE: the single shade kernel, or the surface kernel of the split stage; SHADE_SCATTER: its scatter kernel
+    enum { NONE = -1, TRACE_CLOSEST = 0, TRACE_MIXED = 1, TRACE_SHADOW = 2, SHADE = 3, SHADE_SCATTER = 4, NUM_STAGES = 5 };
     // one sequence of marks per stream ("lane") the frame is issued on; intervals are taken between consecutive
     // marks of a lane, so kernels of the two lanes that overlap on the device are each timed as they ran
     struct Lane {

@@ -216,12 +216,47 @@ struct VertexRecord {
     V3 p, gn, sn, sdpdu, sdpdv, Kd, Ks, opacity;
     uint32_t px;
     int flags;      // bit 0: traceErrorOffset is negative (back face), bit 1: the shape has a material, bits 8..: material id
+    int key;        // what the lanes of the second stage would diverge on (scatter_key); a scheduling hint only
 };
+
+// Divergence key of the second stage, 7 bits: the TYPE of the light the vertex will sample (2 bits), the lobe its
+// BSDF sample will pick (3 bits: the walk of sampleUberBSDF over the material's components with the sampler's
+// fourth draw of the bounce) and whether the Lambertian / microfacet-reflection components exist (2 bits: they are
+// evaluated for the other lobe's direction).  The sampler is a pure function of (pixel, frame, bounce)
+// (samplers.cl:75-84), so all of it is known here.  The second stage may order its records by this key; no result
+// depends on it.
+HD int scatter_key(const Scene& sc, const UberProps& um, bool hasMaterial, uint32_t px, int frame, int width, int height,
+                   int bounce) {
+    Sampler sp = makeSampler(sc.sobolMatrices, (int)px, frame, width, height, bounce);
+    uint32_t lightIdx = ((uint32_t)floorf(getSample1D(&sp) * sc.numLights));
+    lightIdx %= (uint32_t)sc.numLights;
+    const int ltype = sc.lights[lightIdx].type & 3;
+    if (!hasMaterial) return ltype;
+    skipSamples(&sp, 2);
+    const float ux = getSample1D(&sp);
+    const V3 t = v3(1.0f) - um.opacity;
+    const V3 kd = um.Kd * um.opacity, ks = um.Ks * um.opacity, kt = um.Kt * um.opacity, kr = um.Kr * um.opacity;
+    const bool perfectT = um.KtW < 0.5f;
+    // component order of the walk: T, perfect-specular Kt, Kr, microfacet Kt, Kd, Ks
+    const bool has[6] = {isNotBlack(t), perfectT && isNotBlack(kt), isNotBlack(kr), isNotBlack(kt) && !perfectT,
+                         isNotBlack(kd), isNotBlack(ks)};
+    int n = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) n += has[i] ? 1 : 0;
+    int lobe = 7;
+    if (n > 0) {
+        int chosen = min((int)floorf(ux * n), n - 1);
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            if (has[i] && chosen-- == 0) lobe = i;
+    }
+    return ltype | (lobe << 2) | (has[4] ? 32 : 0) | (has[5] ? 64 : 0);
+}
 enum { SURF_DEAD = 0, SURF_EMITTED = 1, SURF_RECORD = 2 };
 
 // first stage.  SURF_EMITTED: the path ends on an emitter, *Le is its radiance towards the ray origin.
 HD int shade_surface(const Scene& sc, int shapeId, int primId, float bu, float bv, V3 rayDir, int prevBsdfFlags,
-                     int bounce, V3* Le, VertexRecord* rec) {
+                     int bounce, uint32_t px, int frame, int width, int height, V3* Le, VertexRecord* rec) {
     RTInteraction si = computeSurfaceInteraction(sc, shapeId, primId, bu, bv);
     si.wo = -rayDir;
     const bool isBackfacing = dot(si.gn, si.wo) < 0.0f;
@@ -238,7 +273,8 @@ HD int shade_surface(const Scene& sc, int shapeId, int primId, float bu, float b
     }
     const bool hasMaterial = materialId != RT_INVALID_ID;
     UberProps um;
-    um.Kd = um.Ks = um.opacity = v3(0.0f);
+    um.Kd = um.Ks = um.opacity = um.Kr = um.Kt = v3(0.0f);
+    um.KtW = 0.0f;
     if (hasMaterial) getUberMaterialProperties(sc, materialId, &si, &um);
     rec->p = si.p;
     rec->gn = si.gn;
@@ -249,6 +285,8 @@ HD int shade_surface(const Scene& sc, int shapeId, int primId, float bu, float b
     rec->Ks = um.Ks;
     rec->opacity = um.opacity;
     rec->flags = (isBackfacing ? 1 : 0) | (hasMaterial ? 2 : 0) | (hasMaterial ? (materialId << 8) : 0);
+    rec->px = px;
+    rec->key = scatter_key(sc, um, hasMaterial, px, frame, width, height, bounce);
     return SURF_RECORD;
 }
 

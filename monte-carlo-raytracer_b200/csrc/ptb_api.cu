@@ -857,14 +857,16 @@ int ptb_profile_enable(ptb_context* c, int on) {
     return 0;
 }
 
-int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
+static int profile_collect(ptb_context* c, double* acc, int64_t* n) {
     if (!c) return pfail(RRB_ERROR_INVALID_ARGUMENT, "null context");
     int rc = set_dev(c);
     if (rc) return rc;
     if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
-    double acc[mcrt::StageTimer::NUM_STAGES] = {0.0, 0.0, 0.0, 0.0};
-    int64_t n[mcrt::StageTimer::NUM_STAGES] = {0, 0, 0, 0};
+    for (int k = 0; k < mcrt::StageTimer::NUM_STAGES; ++k) {
+        acc[k] = 0.0;
+        n[k] = 0;
+    }
     for (const mcrt::StageTimer::Lane& l : c->timer.lanes)
         for (size_t i = 1; i < l.used; ++i) {
             const int tag = l.tags[i];
@@ -874,11 +876,32 @@ int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
             acc[tag] += t;
             n[tag] += 1;
         }
-    for (int k = 0; k < mcrt::StageTimer::NUM_STAGES; ++k) {
+    c->timer.reset();
+    return 0;
+}
+
+int ptb_profile_collect(ptb_context* c, double ms[4], int64_t launches[4]) {
+    double acc[mcrt::StageTimer::NUM_STAGES];
+    int64_t n[mcrt::StageTimer::NUM_STAGES];
+    int rc = profile_collect(c, acc, n);
+    if (rc) return rc;
+    acc[PTB_STAGE_SHADE] += acc[PTB_STAGE_SHADE_SCATTER];      // the shade stage as a whole; one launch = one bounce
+    for (int k = 0; k < 4; ++k) {
         if (ms) ms[k] = acc[k];
         if (launches) launches[k] = n[k];
     }
-    c->timer.reset();
+    return 0;
+}
+
+int ptb_profile_collect_kernels(ptb_context* c, double ms[PTB_NUM_STAGES], int64_t launches[PTB_NUM_STAGES]) {
+    double acc[mcrt::StageTimer::NUM_STAGES];
+    int64_t n[mcrt::StageTimer::NUM_STAGES];
+    int rc = profile_collect(c, acc, n);
+    if (rc) return rc;
+    for (int k = 0; k < PTB_NUM_STAGES; ++k) {
+        if (ms) ms[k] = acc[k];
+        if (launches) launches[k] = n[k];
+    }
     return 0;
 }
 

@@ -73,6 +73,7 @@ def _lib():
             "ptb_selftest_fdiv": [vp, vp, vp, vp, vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
             "ptb_profile_collect": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
+            "ptb_profile_collect_kernels": [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
             "ptb_selftest_libm": [vp, i, vp, vp, i],
             "ptb_set_path_trace": [vp, i], "ptb_write_buffer": [vp, ctypes.c_char_p, vp, sz],
             "ptb_bdpt_reserve": [vp, i], "ptb_merge_accumulation": [vp, vp, i],
@@ -287,6 +288,15 @@ class RenderPipeline:
         ms, n = (ctypes.c_double * 4)(), (ctypes.c_int64 * 4)()
         _check(_lib().ptb_profile_collect(self.scene._h, ms, n))
         return {k: (ms[i], n[i]) for i, k in enumerate(self.STAGES)}
+
+    KERNELS = STAGES + ("k_shade_scatter",)     # ptb_profile_collect_kernels: [3] is the surface kernel when [4] ran
+
+    def profile_collect_kernels(self):
+        """Like profile_collect, per kernel: with the split shade stage "k_shade" is the surface kernel alone and
+        "k_shade_scatter" the scatter kernel (zero launches for the single shade kernel)."""
+        ms, n = (ctypes.c_double * 5)(), (ctypes.c_int64 * 5)()
+        _check(_lib().ptb_profile_collect_kernels(self.scene._h, ms, n))
+        return {k: (ms[i], n[i]) for i, k in enumerate(self.KERNELS)}
 
     def set_overlap(self, halves):
         _check(_lib().ptb_set_overlap(self.scene._h, int(halves)))

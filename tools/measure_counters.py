@@ -30,10 +30,12 @@ def main():
     os.makedirs(out_dir, exist_ok=True)
     log = os.path.join(out_dir, "kernel_counters.csv")
     env = dict(os.environ, MCRT_OVERLAP_HALVES="1")
+    split = os.environ.get("MCRT_SHADE_SPLIT", "1") != "0"      # PTB_DEFAULT_SHADE_SPLIT = 1
+    per_frame = 16 if split else 11      # trace / shade launches of one frame: closest, 4 x mixed, shadow, 5 x (1 or 2) shade
     # warm-up 3 steps (the bench's minimum) + 1 timed + 1 profiled-stage step + e2e: skip the warm-up's launches and
     # capture the launches of the first timed frame: raygen, closest, 5 x shade, 4 x mixed, shadow, control kernels
     cmd = ["ncu", "--metrics", ",".join(METRICS), "--clock-control", "none", "--csv", "--log-file", log,
-           "-k", "regex:k_trace|k_shade", "-s", "33", "-c", "11",
+           "-k", "regex:k_trace|k_shade", "-s", str(3 * per_frame), "-c", str(per_frame),
            sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "3", "--frames-in-flight", "1",
            "--halves", "1", "--no-cpu-baseline", "--no-extras"]
     subprocess.run(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, check=True)
@@ -66,9 +68,21 @@ def main():
                          "warp_insts_per_launch": mean("smsp__inst_executed.sum"),
                          "threads_per_inst": mean("smsp__thread_inst_executed.sum") / max(mean("smsp__inst_executed.sum"), 1.0),
                          "ncu_time_per_launch_s": mean("gpu__time_duration.sum")}
+    if "k_shade_surface" in summary and "k_shade_scatter" in summary:
+        # the shade STAGE of the split build: one "launch" = one bounce = the two kernels, as bench.py's stage timer counts
+        a, b = summary["k_shade_surface"], summary["k_shade_scatter"]
+        n = max(a["launches"], 1)
+        tot = lambda k: a[k] * a["launches"] + b[k] * b["launches"]
+        wi = tot("warp_insts_per_launch")
+        summary["k_shade"] = {"launches": n, "dram_bytes_per_launch": tot("dram_bytes_per_launch") / n,
+                              "l2_bytes_per_launch": tot("l2_bytes_per_launch") / n, "warp_insts_per_launch": wi / n,
+                              "threads_per_inst": (a["threads_per_inst"] * a["warp_insts_per_launch"] * a["launches"] +
+                                                   b["threads_per_inst"] * b["warp_insts_per_launch"] * b["launches"]) / max(wi, 1.0),
+                              "ncu_time_per_launch_s": tot("ncu_time_per_launch_s") / n,
+                              "note": "k_shade_surface + k_shade_scatter per bounce"}
     doc = {"build_fingerprint": build._fingerprint()[:16], "when": datetime.datetime.utcnow().strftime("%Y-%m-%dT%H:%MZ"),
            "workload": "bench.py default (sponza_class 1920x1080 depth 5), one frame as one wavefront",
-           "how": "ncu --metrics %s --clock-control none, launches 33..43 of k_trace*/k_shade* (the first timed frame)" % ",".join(METRICS),
+           "how": "ncu --metrics %s --clock-control none, the trace / shade launches of the first timed frame" % ",".join(METRICS),
            "kernels": summary}
     with open(os.path.join(out_dir, "kernel_counters.json"), "w") as f:
         json.dump(doc, f, indent=1)
