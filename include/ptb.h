@@ -141,7 +141,7 @@ int ptb_set_overlap(ptb_context* ctx, int halves);
  * traversal launch ends with the few rays that graze the mesh -- is filled by the work of the following frames.
  * ptb_accumulate consumes the frames in the order they were rendered, on the context's stream; every other entry
  * point first waits for the frames in flight, so the call sequence of the render passes and every per-sample value
- * are unchanged.  "RadianceBufferCL" names the buffer of the frame rendered last.  Costs 296 B per pixel of device
+ * are unchanged.  "RadianceBufferCL" names the buffer of the frame rendered last.  Costs 304 B per pixel of device
  * memory per extra frame. */
 int ptb_set_frames_in_flight(ptb_context* ctx, int depth);
 /* Order of the live-path queues of ptb_pt_render_sample.  The reference's sampler is a pure function of (pixel, frame,
@@ -171,6 +171,14 @@ int ptb_set_coherence(ptb_context* ctx, int mode);
  * (the second kernel re-reads those properties from the material table); otherwise the single kernel runs. */
 #define PTB_DEFAULT_SHADE_SPLIT 1
 int ptb_set_shade_split(ptb_context* ctx, int on);
+/* Cooperative tail of the traversal kernels of ptb_pt_render_sample (flat trees; no reference counterpart).  A ray that
+ * is still being walked `min_iters` rounds after its launch's queue ran dry is put on a list of stragglers; every warp
+ * that is out of work pulls rays off that list and walks each with all 32 lanes, lane k restricted to the k-th of 32
+ * intervals of t (same origin and direction, so every t is the value the single walk computes); the warp's smallest
+ * (t, shape id, prim id) is the single walk's answer, tie rule included (csrc/pt_wavefront.cuh).  It shortens the tail a
+ * few slow rays put on every launch (profiles/r02_tail.md).  0 = off.  Per-sample results are identical. */
+#define PTB_DEFAULT_COOPERATIVE_TAIL 0
+int ptb_set_cooperative_tail(ptb_context* ctx, int min_iters);
 
 /* Diagnostic record of ptb_pt_render_sample (no reference counterpart; parity evidence only).  With max_depth > 0 a
  * buffer "PathTraceBuffer" of int4[max_depth][P] is kept: entry [bounce * P + pixel] = {shape id, prim id, flags,

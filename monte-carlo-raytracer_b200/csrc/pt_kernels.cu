@@ -24,6 +24,7 @@ namespace mcrt {
 //      [5],[6] shadow-ray counts by bounce parity (the shadow rays of bounce b are traced together with the
 //      closest-hit rays of bounce b + 1, while nothing writes either set)
 //      [7] vertex records written by k_shade_surface for k_shade_scatter (split shade stage)
+//      [25],[26] stragglers of the running traversal launch: listed, taken (cooperative tail, pt_wavefront.cuh)
 //      [8..15] coherence-bucket counts of the queue being filled, [16..24] prefix sums of the queue about to be read
 __global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int cur, int bounce, int n_first, int bucketed) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -51,11 +52,15 @@ __global__ void k_bounce_ctl(unsigned int* cnt, unsigned long long* stats, int c
     cnt[3] = 0;
     cnt[4] = 0;
     cnt[7] = 0;      // vertex records of the split shade stage
+    cnt[25] = 0;     // stragglers of the traversal launch about to start (cooperative tail): listed, taken
+    cnt[26] = 0;
 }
 __global__ void k_sample_end(unsigned int* cnt, unsigned long long* stats, int last_bounce) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     atomicAdd(stats + 1, (unsigned long long)cnt[5 + (last_bounce & 1)]);
     cnt[4] = 0;
+    cnt[25] = 0;
+    cnt[26] = 0;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -124,6 +129,11 @@ k_queue_gather(PtState s, int cur, int cap) {
     }
 }
 
+// the cooperative tail of a traversal launch (pt_wavefront.cuh): straggler list and its two counters
+__device__ __forceinline__ CoopTail coop_tail(const PtState& s) {
+    return CoopTail{s.strag ? s.coopIters : 0, s.strag, s.cnt + 25};
+}
+
 // closest-hit ray of queue entry idx / its result
 __device__ __forceinline__ void fetch_closest_ray(const PtState& s, const uint32_t* __restrict__ queue, unsigned idx, Ray& r) {
     const uint32_t px = queue[idx];
@@ -174,45 +184,45 @@ __device__ __forceinline__ void resolve_shadow(const PtState& s, unsigned idx, c
 
 // TWO_LEVEL: the world is a top-level tree over shapes with per-mesh bottom-level trees (rrb_commit with instances);
 // separate instantiations, so the flat kernels keep their 64 registers / 8 CTAs per SM.
-template <bool TWO_LEVEL>
+template <bool TWO_LEVEL, bool COOP = false>
 __global__ void __launch_bounds__(128, TWO_LEVEL ? 6 : 8)
 k_trace_closest(PtState s, int cur) {
     const unsigned count = s.cnt[cur];
     const uint32_t* __restrict__ queue = s.queue[cur];
-    persistent_trace<false, false, TWO_LEVEL>(
+    persistent_trace<false, false, TWO_LEVEL, COOP>(
         s.nodes, s.tris, count, s.cnt + 3,
         [&](unsigned idx, Ray& r) {
             fetch_closest_ray(s, queue, idx, r);
             return false;
         },
         [&](unsigned idx, const Ray& r, const TravState& st) { store_closest_hit<TWO_LEVEL>(s, queue, idx, r, st); },
-        s.numNodes, s.stageTop, s.instances);
+        s.numNodes, s.stageTop, s.instances, coop_tail(s));
 }
 
 // any-hit traversal fused with the reference's ShadowPass; shadow rays of bounce parity `sh`
-template <bool TWO_LEVEL>
+template <bool TWO_LEVEL, bool COOP = false>
 __global__ void __launch_bounds__(128, TWO_LEVEL ? 6 : 8)
 k_trace_shadow(PtState s, int sh, int bounce) {
     const unsigned count = s.cnt[5 + sh];
-    persistent_trace<true, false, TWO_LEVEL>(
+    persistent_trace<true, false, TWO_LEVEL, COOP>(
         s.nodes, s.tris, count, s.cnt + 4,
         [&](unsigned idx, Ray& r) {
             fetch_shadow_ray(s, idx, r);
             return true;
         },
         [&](unsigned idx, const Ray&, const TravState& st) { resolve_shadow(s, idx, st, bounce); }, s.numNodes, s.stageTop,
-        s.instances);
+        s.instances, coop_tail(s));
 }
 
 // One launch for the two ray sets that are ready after a shade stage: the closest-hit rays of the next bounce
 // (queue `cur`) and the shadow rays of the bounce just shaded (parity `sh`).  They are independent of each other, so
 // sharing the persistent warps removes one drain-out tail and one launch per bounce.  Long rays first.
-template <bool TWO_LEVEL>
+template <bool TWO_LEVEL, bool COOP = false>
 __global__ void __launch_bounds__(128, TWO_LEVEL ? 6 : 8)
 k_trace_mixed(PtState s, int cur, int sh, int sh_bounce) {
     const unsigned n_closest = s.cnt[cur], n_shadow = s.cnt[5 + sh];
     const uint32_t* __restrict__ queue = s.queue[cur];
-    persistent_trace<false, true, TWO_LEVEL>(
+    persistent_trace<false, true, TWO_LEVEL, COOP>(
         s.nodes, s.tris, n_closest + n_shadow, s.cnt + 3,
         [&](unsigned idx, Ray& r) {
             if (idx < n_closest) {
@@ -226,7 +236,7 @@ k_trace_mixed(PtState s, int cur, int sh, int sh_bounce) {
             if (idx < n_closest) store_closest_hit<TWO_LEVEL>(s, queue, idx, r, st);
             else resolve_shadow(s, idx - n_closest, st, sh_bounce);
         },
-        s.numNodes, s.stageTop, s.instances);
+        s.numNodes, s.stageTop, s.instances, coop_tail(s));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1019,12 +1029,14 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         t.cnt += PT_CNT_STRIDE;
         t.bucket += (size_t)PT_NUM_BUCKETS * nA;
         if (t.vtx) t.vtx += nA;      // record planes keep the full-frame stride
+        if (t.strag) t.strag += 2 * (size_t)nA;      // a mixed launch serves up to 2 rays per pixel
         half[1] = {t, nA, n_pixels - nA, overlap->stream};
         cudaEventRecord(overlap->fork, stream);
         cudaStreamWaitEvent(overlap->stream, overlap->fork, 0);
     }
     int cur[2] = {0, 0};
     const bool two_level = s.instances != nullptr;
+    const bool coop = !two_level && s.coopIters > 0 && s.strag != nullptr;      // kernels with the cooperative tail compiled in
     // the sorted shade kernel stages the small scene tables in shared memory when they fit
     const unsigned table_bytes = staged_tables(s).total();
     static const int stage_enabled = env_int("MCRT_STAGE_TABLES", 1);
@@ -1060,10 +1072,12 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                     // experiment knob: start the second half one stage behind the first
                     if (h == 1 && stagger) cudaStreamWaitEvent(H.stream, overlap->stagger, 0);
                     if (two_level) k_trace_closest<true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h]);
+                    else if (coop) k_trace_closest<false, true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h]);
                     else k_trace_closest<false><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h]);
                     if (h == 0 && nh == 2 && stagger) cudaEventRecord(overlap->stagger, H.stream);
                 } else {
                     if (two_level) k_trace_mixed<true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1, b - 1);
+                    else if (coop) k_trace_mixed<false, true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1, b - 1);
                     else k_trace_mixed<false><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, cur[h], (b - 1) & 1, b - 1);
                 }
                 if (timer) timer->mark(h, H.stream, b == 0 ? StageTimer::TRACE_CLOSEST : StageTimer::TRACE_MIXED);
@@ -1098,6 +1112,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
             k_sample_end<<<1, 32, 0, H.stream>>>(H.s.cnt, H.s.stats, max_depth - 1);
             if (timer) timer->mark(h, H.stream);
             if (two_level) k_trace_shadow<true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1, max_depth - 1);
+            else if (coop) k_trace_shadow<false, true><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1, max_depth - 1);
             else k_trace_shadow<false><<<blocks_trace(H.n), 128, 0, H.stream>>>(H.s, (max_depth - 1) & 1, max_depth - 1);
             if (timer) timer->mark(h, H.stream, StageTimer::TRACE_SHADOW);
             launches += 2;

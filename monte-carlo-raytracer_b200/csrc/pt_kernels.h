@@ -37,6 +37,9 @@ struct PtState {
     const float4* instances;   // two-level world (rrb_commit with instances): the shape table, 4 float4 per shape; else NULL
     int numNodes;         // nodes in the tree; the first MCRT_TOP_NODES are staged in shared memory by the traversal CTAs
     int stageTop;         // 0 = every node from global memory (experiment switch MCRT_STAGE_TOP=0)
+    int coopIters;        // > 0: cooperative tail of the traversal kernels (pt_wavefront.cuh): a ray still walked this many
+                          // rounds after the queue ran dry goes to the straggler list; 0 = off.  Flat trees only.
+    unsigned int* strag;  // straggler list of the running traversal launch, 2 entries per pixel (or NULL)
     // SoA wavefront state
     float4* ray_o;        // xyz origin, w tmax
     float4* ray_d;        // xyz direction

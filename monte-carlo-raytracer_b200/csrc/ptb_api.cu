@@ -289,6 +289,7 @@ int alloc_slots(ptb_context* c, int depth) {
             {"queue0", 4, (void**)&s.st.queue[0]}, {"queue1", 4, (void**)&s.st.queue[1]},
             {"bucket", 4 * mcrt::PT_NUM_BUCKETS, (void**)&s.st.bucket},
             {"vtx", 7 * 16, (void**)&s.st.vtx},
+            {"strag", 8, (void**)&s.st.strag},
             {"sh_o", 16, (void**)&s.st.sh_o},     {"sh_d", 16, (void**)&s.st.sh_d},
             {"sh_L", 16, (void**)&s.st.sh_L},
         };
@@ -318,6 +319,7 @@ mcrt::PtState slot_state(const ptb_context* c, int k) {
         st.queue[1] = s.st.queue[1];
         st.bucket = s.st.bucket;
         st.vtx = s.st.vtx;
+        st.strag = s.st.strag;
         st.sh_o = s.st.sh_o;
         st.sh_d = s.st.sh_d;
         st.sh_L = s.st.sh_L;
@@ -386,6 +388,8 @@ int ptb_create(rrb_api* api, ptb_context** out) {
     if (const char* v = getenv("MCRT_OVERLAP_HALVES")) c->halves = atoi(v) == 1 ? 1 : 2;   // profiling aid
     c->st.coherence = PTB_DEFAULT_COHERENCE;
     if (const char* v = getenv("MCRT_COHERENCE")) c->st.coherence = std::max(0, std::min(4, atoi(v)));   // variant runs
+    c->st.coopIters = PTB_DEFAULT_COOPERATIVE_TAIL;
+    if (const char* v = getenv("MCRT_COOP_ITERS")) c->st.coopIters = std::max(0, atoi(v));                      // variant runs
     c->shade_split_wanted = PTB_DEFAULT_SHADE_SPLIT;
     if (const char* v = getenv("MCRT_SHADE_SPLIT")) c->shade_split_wanted = atoi(v) ? 1 : 0;                  // variant runs
     PTB_CUDA(cudaStreamCreateWithFlags(&c->overlap.stream, cudaStreamNonBlocking));
@@ -424,6 +428,16 @@ int ptb_set_coherence(ptb_context* c, int mode) {
     if ((rc = join_and_drop_frames(c))) return rc;
     PTB_CUDA(cudaStreamSynchronize(c->stream));
     c->st.coherence = mode;
+    return 0;
+}
+
+int ptb_set_cooperative_tail(ptb_context* c, int min_iters) {
+    if (!c || min_iters < 0) return pfail(RRB_ERROR_INVALID_ARGUMENT, "min_iters must be >= 0");
+    int rc = set_dev(c);
+    if (rc) return rc;
+    if ((rc = join_and_drop_frames(c))) return rc;
+    PTB_CUDA(cudaStreamSynchronize(c->stream));
+    c->st.coopIters = min_iters;
     return 0;
 }
 
@@ -645,6 +659,7 @@ int ptb_resize(ptb_context* c, int width, int height) {
         {"queue1", 4, (void**)&s.queue[1], nullptr},
         {"bucket", 4 * mcrt::PT_NUM_BUCKETS, (void**)&s.bucket, nullptr},
         {"vtx", 7 * 16, (void**)&s.vtx, nullptr},
+        {"strag", 8, (void**)&s.strag, nullptr},
         {"sh_o", 16, (void**)&s.sh_o, nullptr},
         {"sh_d", 16, (void**)&s.sh_d, nullptr},
         {"sh_L", 16, (void**)&s.sh_L, nullptr},

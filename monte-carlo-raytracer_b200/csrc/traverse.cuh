@@ -158,6 +158,9 @@ struct TravState {
     // (-1 = at the top level), the instance being walked and the one that owns the best hit
     float cox, coy, coz, cdx, cdy, cdz;
     int inst_sp, cur_inst, cur_sid, best_inst;
+    // run<SPLIT = true> only (the cooperative tail of persistent_trace): this lane walks the ray restricted to
+    // tlo < t <= closest; tlo_box is tlo rounded down for the slab test.  Not touched by init().
+    float tlo, tlo_box;
 };
 
 // ray.o / ray.d through rows 0..2 of a world -> object matrix: transform_point / transform_vector of the reference's
@@ -219,6 +222,10 @@ struct Traverser {
 
     // Runs until the ray is finished (returns true) or the warp's active-lane count drops under
     // the dynamic-fetch threshold (returns false: caller refills idle lanes and calls again).
+    // SPLIT: the lane is one of several that share ONE ray, each restricted to its own interval (s.tlo, s.closest] of
+    // t -- same origin and direction, so every t is the number the unrestricted walk computes; boxes that end before
+    // tlo are culled, triangles are accepted only for t > tlo.
+    template <bool SPLIT = false>
     __device__ __forceinline__ bool run(TravState& s, const Ray& r, uint2* stack, int* counters) const {
         uint2 ngroup = s.ngroup, tgroup = s.tgroup;
         int sp = s.sp;
@@ -312,7 +319,7 @@ struct Traverser {
         const float tmaxx = __fmaf_rn(quant_byte_to_float<j>(xmax, cxmax), aix, orx);                          \
         const float tmaxy = __fmaf_rn(quant_byte_to_float<j>(ymax, cymax), aiy, ory);                          \
         const float tmaxz = __fmaf_rn(quant_byte_to_float<j>(zmax, czmax), aiz, orz);                          \
-        const float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, 0.f));                                      \
+        const float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, SPLIT ? s.tlo_box : 0.f));                  \
         /* 1 + 3 ulp widening keeps the quantised slab test conservative w.r.t. fp32 rounding */               \
         const float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, s.closest)) * 1.0000004f;                   \
         if (cmin <= cmax) hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);              \
@@ -393,7 +400,7 @@ struct Traverser {
                     cr.ox = s.cox; cr.oy = s.coy; cr.oz = s.coz;
                     cr.dx = s.cdx; cr.dy = s.cdy; cr.dz = s.cdz;
                 }
-                if (intersect_triangle_ref(cr, v0, v1, v2, s.closest, t)) {
+                if (intersect_triangle_ref(cr, v0, v1, v2, s.closest, t) && (!SPLIT || t > s.tlo)) {
                     if (ANY_HIT || (MIXED && s.any_hit)) {
                         if (t < s.closest) {
                             s.best_tri = (int)ta;

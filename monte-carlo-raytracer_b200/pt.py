@@ -69,6 +69,7 @@ def _lib():
             "ptb_profile_enable": [vp, ctypes.c_int], "ptb_set_overlap": [vp, ctypes.c_int],
             "ptb_set_coherence": [vp, ctypes.c_int], "ptb_set_estimator": [vp, ctypes.c_int],
             "ptb_set_shade_split": [vp, ctypes.c_int],
+            "ptb_set_cooperative_tail": [vp, ctypes.c_int],
             "ptb_set_frames_in_flight": [vp, ctypes.c_int],
             "ptb_selftest_fdiv": [vp, vp, vp, vp, vp, ctypes.c_int],
             "ptb_read_buffer_async": [vp, ctypes.c_char_p, vp, sz], "ptb_read_wait": [vp],
@@ -314,6 +315,11 @@ class RenderPipeline:
         """The shade stage as one kernel per bounce (False) or as surface + scatter kernels (True); identical results
         (include/ptb.h: ptb_set_shade_split)."""
         _check(_lib().ptb_set_shade_split(self.scene._h, 1 if on else 0))
+
+    def set_cooperative_tail(self, min_iters):
+        """Cooperative tail of the traversal kernels: split a ray walked `min_iters` rounds after the queue ran dry
+        over the warp's idle lanes (include/ptb.h); 0 = off; identical results."""
+        _check(_lib().ptb_set_cooperative_tail(self.scene._h, int(min_iters)))
 
     def set_estimator(self, russian_roulette=False, nee_mis=False):
         """Opt-in estimator switches (include/ptb.h PTB_EST_*); both off = the reference's estimator."""

@@ -47,6 +47,7 @@ def main():
     ap.add_argument("--partition", default="tiles", choices=["tiles", "samples"],
                     help="tiles: every rank renders its 64x64 tiles of every sample (strong scaling, BASELINE configs[4]); "
                          "samples: rank r renders whole frames r, r+N, ... (weak scaling, like bench.py)")
+    ap.add_argument("--parts", type=int, default=0, help="single GPU only: render part 0 of this many tile partitions (what one of N GPUs does)")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -65,7 +66,7 @@ def main():
     pl.ensure_size()
     by_tiles = a.partition == "tiles"
     if by_tiles:
-        pl.set_partition(rank, world)
+        pl.set_partition(rank, a.parts if (a.parts > 0 and world == 1) else world)
     pl.set_frames_in_flight(a.frames_in_flight)
     lib, h = pt._lib(), pl.scene._h
     fprops = pl.GI.filter_props()
