@@ -1050,6 +1050,10 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
         cudaFuncSetAttribute(k_shade_scatter_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scatter_sorted_smem());
         smem_attr_set = true;
     }
+    // The split shade stage pays for its second launch and its record traffic only on large wavefronts: 1 M entries
+    // (a 1080p half frame) +4.4 % paths/s, 131 K entries (a 512^2 half frame) -12 % (profiles/r02_full_frame.md).
+    static const int split_min = env_int("MCRT_SPLIT_MIN_ENTRIES", 393216);
+    auto use_split = [&](int n) { return s.shade_split && !s.estimator && s.vtx != nullptr && (s.shade_split == 2 || n >= split_min); };
     auto blocks_trace = [&](int n) { return min(sms * trace_per_sm, (n + 127) / 128); };
     auto blocks_shade = [&](int n) { return min(sms * shade_per_sm, (n + PT_SHADE_BLOCK - 1) / PT_SHADE_BLOCK); };
     for (int h = 0; h < nh; ++h) {
@@ -1087,7 +1091,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                         k_shade_sorted_est<<<nb, PT_SHADE_BLOCK, sorted_smem, H.stream>>>(H.s, cur[h], frame, b, max_depth, stage_tables);
                     else
                         k_shade_sorted<<<nb, PT_SHADE_BLOCK, sorted_smem, H.stream>>>(H.s, cur[h], frame, b, max_depth, stage_tables);
-                } else if (s.shade_split && !s.estimator && s.vtx) {
+                } else if (use_split(H.n)) {
                     const int nb = min(sms * surf_per_sm, (H.n + PT_SURF_BLOCK - 1) / PT_SURF_BLOCK);
                     k_shade_surface<<<nb, PT_SURF_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b);
                     if (timer) timer->mark(h, H.stream, StageTimer::SHADE);
@@ -1102,7 +1106,7 @@ int launch_pt_sample(const PtState& s, const uint32_t* pixels, int n_pixels, int
                     k_shade_est<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
                 else
                     k_shade<<<blocks_shade(H.n), PT_SHADE_BLOCK, 0, H.stream>>>(H.s, cur[h], frame, b, max_depth, H.n);
-                if (timer) timer->mark(h, H.stream, (s.shade_split && !s.estimator && s.vtx && s.coherence != 4) ? StageTimer::SHADE_SCATTER : StageTimer::SHADE);
+                if (timer) timer->mark(h, H.stream, (s.coherence != 4 && use_split(H.n)) ? StageTimer::SHADE_SCATTER : StageTimer::SHADE);
                 launches += 3;
                 cur[h] = 1 - cur[h];
             }

@@ -56,7 +56,8 @@ struct PtState {
     uint32_t* bucket;     // coherence staging: PT_NUM_BUCKETS regions per half frame (pt_kernels.cu)
     float4* vtx;          // split shade stage (ptb_set_shade_split): 7 planes of vtx_stride vertex records (pt_kernels.cu)
     int vtx_stride;       // = pixels of the frame
-    int shade_split;      // 1 = k_shade_surface + k_shade_scatter instead of k_shade (reference estimator only)
+    int shade_split;      // k_shade_surface + k_shade_scatter instead of k_shade (reference estimator only): 0 never,
+                          // 1 on wavefronts of at least 393,216 entries, 2 always
     int estimator;        // PT_EST_* flags of the opt-in estimator switches (pt_shade.cuh); 0 = the reference's estimator
     int coherence;        // 0 = queues in push order, 1 = bounces >= 1 bucketed by sampler decisions, 2 = bounce 0 too
     unsigned long long* stats;  // [0] closest rays, [1] shadow rays, [2] shaded vertices, [3] samples

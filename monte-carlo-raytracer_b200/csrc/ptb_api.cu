@@ -204,7 +204,7 @@ bool materials_allow_split(const void* materials, int n) {
     }
     return true;
 }
-void apply_shade_split(ptb_context* c) { c->st.shade_split = (c->shade_split_wanted && c->split_supported) ? 1 : 0; }
+void apply_shade_split(ptb_context* c) { c->st.shade_split = c->split_supported ? c->shade_split_wanted : 0; }
 
 bool pipelined(const ptb_context* c) { return c->slots.size() > 1 && !c->profiling && !c->st.path_trace; }
 
@@ -391,7 +391,7 @@ int ptb_create(rrb_api* api, ptb_context** out) {
     c->st.coopIters = PTB_DEFAULT_COOPERATIVE_TAIL;
     if (const char* v = getenv("MCRT_COOP_ITERS")) c->st.coopIters = std::max(0, atoi(v));                      // variant runs
     c->shade_split_wanted = PTB_DEFAULT_SHADE_SPLIT;
-    if (const char* v = getenv("MCRT_SHADE_SPLIT")) c->shade_split_wanted = atoi(v) ? 1 : 0;                  // variant runs
+    if (const char* v = getenv("MCRT_SHADE_SPLIT")) c->shade_split_wanted = std::max(0, std::min(2, atoi(v)));                  // variant runs
     PTB_CUDA(cudaStreamCreateWithFlags(&c->overlap.stream, cudaStreamNonBlocking));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.fork, cudaEventDisableTiming));
     PTB_CUDA(cudaEventCreateWithFlags(&c->overlap.join, cudaEventDisableTiming));
@@ -442,7 +442,7 @@ int ptb_set_cooperative_tail(ptb_context* c, int min_iters) {
 }
 
 int ptb_set_shade_split(ptb_context* c, int on) {
-    if (!c || (on != 0 && on != 1)) return pfail(RRB_ERROR_INVALID_ARGUMENT, "shade split must be 0 or 1");
+    if (!c || on < 0 || on > 2) return pfail(RRB_ERROR_INVALID_ARGUMENT, "shade split must be 0, 1 or 2");
     int rc = set_dev(c);
     if (rc) return rc;
     if ((rc = join_and_drop_frames(c))) return rc;

@@ -312,9 +312,11 @@ class RenderPipeline:
         _check(_lib().ptb_set_coherence(self.scene._h, int(mode)))
 
     def set_shade_split(self, on):
-        """The shade stage as one kernel per bounce (False) or as surface + scatter kernels (True); identical results
+        """The shade stage as one kernel per bounce (False), as surface + scatter kernels always (True) or on large
+        wavefronts only ("auto", the default); identical results
         (include/ptb.h: ptb_set_shade_split)."""
-        _check(_lib().ptb_set_shade_split(self.scene._h, 1 if on else 0))
+        mode = {False: 0, True: 2, "auto": 1}.get(on, on)       # True = always (tests), "auto" = the library's default
+        _check(_lib().ptb_set_shade_split(self.scene._h, int(mode)))
 
     def set_cooperative_tail(self, min_iters):
         """Cooperative tail of the traversal kernels: split a ray walked `min_iters` rounds after the queue ran dry
