@@ -30,6 +30,10 @@ def main(path):
                     f = float(v)
                     if u in ("ns", "nsecond"):
                         f /= 1e3
+                    if u in ("ms", "msecond") and "us" in label:
+                        f *= 1e3
+                    if u in ("s", "second") and "us" in label:
+                        f *= 1e6
                     if u == "byte" and "MB" in label:
                         f /= 1e6
                     if u == "Kbyte" and "MB" in label:
