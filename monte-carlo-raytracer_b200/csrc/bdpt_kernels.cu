@@ -514,6 +514,13 @@ HD void strategy_of(int k, int D, int* t, int* s) {
     *s = k;
 }
 
+// Strategy classes: 0 = s == 0 (a camera vertex on a light), 1 = t == 1 (light tracing), 2 = s == 1 (next-event
+// estimation), 3 = full connection.  k_bdpt_prepare and k_bdpt_connect are instantiated per class and launched four
+// times over the same items: each instance carries one class's code only (ncu r02: the all-in-one kernels waited for
+// instruction fetch 33 % / 58 % of the time), and the records of a class end up next to each other.
+HD int strategy_class(int t, int st) { return st == 0 ? 0 : (t == 1 ? 1 : (st == 1 ? 2 : 3)); }
+
+template <int CLS>
 __global__ void __launch_bounds__(128)
 k_bdpt_prepare(PtState s, BdptState b, const uint32_t* __restrict__ pixels, int n, int frame) {
     const int D = b.max_depth;
@@ -533,9 +540,9 @@ k_bdpt_prepare(PtState s, BdptState b, const uint32_t* __restrict__ pixels, int 
             px = pixels ? pixels[i] : (uint32_t)i;
             strategy_of(k, D, &t, &st);
             target = (int)px;
-            const bool valid = t <= b.cam_count[px] && st <= b.light_count[px];
+            const bool valid = strategy_class(t, st) == CLS && t <= b.cam_count[px] && st <= b.light_count[px];
             const Scene sc = make_scene(s);
-            if (valid && st == 0) {
+            if (CLS == 0 && valid) {
                 // emitted radiance of a camera vertex that lies on a light (ConnectVertices, BDPT.cl:722-730)
                 const BVertex cv = load_vertex<3>(vptr(b.cam_vertices, P, t - 1, px));
                 if (vIsLight(cv)) {
@@ -543,7 +550,7 @@ k_bdpt_prepare(PtState s, BdptState b, const uint32_t* __restrict__ pixels, int 
                     C = Le * cv.beta;
                 }
                 push = !isBlack(C);
-            } else if (valid && t == 1) {
+            } else if (CLS == 1 && valid) {
                 // light tracing: project light vertex s-1 to the camera (:517-561)
                 const BVertex lv = load_vertex<3>(vptr(b.light_vertices, P, st - 1, px));
                 if (vConnectible(lv)) {
@@ -568,7 +575,7 @@ k_bdpt_prepare(PtState s, BdptState b, const uint32_t* __restrict__ pixels, int 
                         push = isNotBlack(C);
                     }
                 }
-            } else if (valid && st == 1) {
+            } else if (CLS == 2 && valid) {
                 // next-event estimation at camera vertex t-1 with a fresh light sample (:563-597)
                 const BVertex cv = load_vertex<3>(vptr(b.cam_vertices, P, t - 1, px));
                 if (vConnectible(cv)) {
@@ -606,7 +613,7 @@ k_bdpt_prepare(PtState s, BdptState b, const uint32_t* __restrict__ pixels, int 
                         push = sr.written && !isBlack(C);
                     }
                 }
-            } else if (valid) {
+            } else if (CLS == 3 && valid) {
                 // full connection of camera vertex t-1 and light vertex s-1 (:599-632)
                 const BVertex cv = load_vertex<3>(vptr(b.cam_vertices, P, t - 1, px));
                 const BVertex lv = load_vertex<3>(vptr(b.light_vertices, P, st - 1, px));
@@ -667,7 +674,15 @@ k_bdpt_trace_conn(PtState s, BdptState b) {
 // ---------------------------------------------------------------------------------------------
 HD float remap0(float f) { return f == 0.0f ? 1.0f : f; }
 
+template <int CLS>
 HD float mis_weight(const Scene& sc, const BdptState& b, int P, uint32_t px, int t, int s) {
+    // what the class says about (t, s), for the compiler: the branches below that cannot be taken disappear
+    if (CLS == 0) s = 0;
+    if (CLS == 1) t = 1;
+    if (CLS == 2) s = 1;
+    __builtin_assume(t >= 1 && s >= 0);
+    if (CLS != 1) __builtin_assume(t >= 2);
+    if (CLS == 1 || CLS == 3) __builtin_assume(s >= 2);
     if (s + t == 2) return 1.0f;
     BVertex pt, qs, ptPrev, qsPrev;
     if (t == 1) {      // the sampled camera vertex (createCameraVertex at the camera position, BDPT.cl:159-174)
@@ -745,23 +760,25 @@ HD float mis_weight(const Scene& sc, const BdptState& b, int P, uint32_t px, int
     return 1.0f / (1.0f + sumRi);
 }
 
+template <int CLS>
 __global__ void __launch_bounds__(128)
 k_bdpt_connect(PtState s, BdptState b) {
     const unsigned count = b.cnt[6];
     const int P = s.width * s.height;
     const Scene sc = make_scene(s);
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int ts = __float_as_int(b.conn_d[i].w);
+        const int t = ts & 0xFF, st = ts >> 8;
+        if (strategy_class(t, st) != CLS) continue;
         if (b.conn_vis[i] == 0) {
             b.conn_w[i] = 0.0f;
             continue;
         }
         const float4 Cq = b.conn_C[i];
-        const int ts = __float_as_int(b.conn_d[i].w);
-        const int t = ts & 0xFF, st = ts >> 8;
         const uint32_t px = (uint32_t)b.conn_src[i];
         const int target = __float_as_int(Cq.w);
         const V3 C = v3(Cq);
-        const float w = isBlack(C) ? 0.0f : mis_weight(sc, b, P, px, t, st);
+        const float w = isBlack(C) ? 0.0f : mis_weight<CLS>(sc, b, P, px, t, st);
         b.conn_w[i] = w;
         atomicAdd(b.splat + 3 * (size_t)target + 0, C.x * w);
         atomicAdd(b.splat + 3 * (size_t)target + 1, C.y * w);
@@ -869,12 +886,18 @@ int launch_bdpt_sample(const PtState& s, const BdptState& b, const uint32_t* pix
     }
     const unsigned long long total = (unsigned long long)n_pixels * (unsigned)b.max_conn;
     const int prep_blocks = (int)std::min<unsigned long long>((total + 127) / 128, (unsigned long long)sms * 32);
-    k_bdpt_prepare<<<prep_blocks, 128, 0, stream>>>(s, b, pixels, n_pixels, frame);
+    k_bdpt_prepare<0><<<prep_blocks, 128, 0, stream>>>(s, b, pixels, n_pixels, frame);
+    k_bdpt_prepare<1><<<prep_blocks, 128, 0, stream>>>(s, b, pixels, n_pixels, frame);
+    k_bdpt_prepare<2><<<prep_blocks, 128, 0, stream>>>(s, b, pixels, n_pixels, frame);
+    k_bdpt_prepare<3><<<prep_blocks, 128, 0, stream>>>(s, b, pixels, n_pixels, frame);
     k_bdpt_conn_stats<<<1, 32, 0, stream>>>(b.cnt, s.stats);
     k_bdpt_trace_conn<<<sms * 8, 128, 0, stream>>>(s, b);
-    k_bdpt_connect<<<sms * 16, 128, 0, stream>>>(s, b);
+    k_bdpt_connect<0><<<sms * 16, 128, 0, stream>>>(s, b);
+    k_bdpt_connect<1><<<sms * 16, 128, 0, stream>>>(s, b);
+    k_bdpt_connect<2><<<sms * 16, 128, 0, stream>>>(s, b);
+    k_bdpt_connect<3><<<sms * 16, 128, 0, stream>>>(s, b);
     k_bdpt_finish<<<(P + 255) / 256, 256, 0, stream>>>(b.splat, s.radiance, P);
-    launches += 5;
+    launches += 11;
     *err = cudaGetLastError();
     return launches;
 }
