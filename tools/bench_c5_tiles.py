@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """BASELINE.json configs[4]: the 10 M-triangle scene, regular PT 3840x2160, depth 5, image-TILE partitioned across
-N GPUs (ptb_set_partition: 64x64 tiles dealt round-robin), one NCCL all-reduce of the accumulation buffers.
+N GPUs (ptb_set_partition: 64x64 tiles dealt round-robin), one NCCL all-reduce of the accumulation buffer behind the C ABI
+(ptb_merge_accumulation).
 
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
       tools/bench_c5_tiles.py --steps K [--reduce-every 1]
@@ -88,8 +89,11 @@ def main():
         pt._check(lib.ptb_pt_render_sample(h, f, depth))
         pt._check(lib.ptb_accumulate(h, f, ctypes.byref(fprops)))
 
+    # the one collective of the path, behind the C ABI: NCCL all-reduce of the 20 B/pixel accumulation buffer + the division
+    comm = multi_gpu.create_comm(pl, rank, world) if world > 1 else None
+
     def merge():
-        multi_gpu.merge_accumulation(t_wr.view(P, 4), t_fw, stage=stage, image=t_img.view(P, 4))
+        pt._check(lib.ptb_merge_accumulation(h, comm, -1))
 
     def barrier():
         if world > 1:
@@ -145,6 +149,8 @@ def main():
             "frames_in_flight": a.frames_in_flight, "allreduce_bytes": 20 * P, "acc_type": a.acc_type, "bvh_on_device": st["last_build_on_device"],
             "setup_s": setup_s, "commit_s": st["build_seconds"], "image_mean": float(img[:, :3].mean()),
             "finite": bool(np.isfinite(img).all()), "bit_identical_to_one_gpu": verified}), flush=True)
+    if comm is not None:
+        multi_gpu.destroy_comm(comm)
     if world > 1:
         dist.destroy_process_group()
 
