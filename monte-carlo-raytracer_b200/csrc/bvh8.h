@@ -67,6 +67,13 @@ struct BuildOptions {
     float traversal_cost = 1.2f;  // relative to one triangle test, for the BVH2 leaf decision
     int num_threads = 0;          // 0 = hardware concurrency
     bool depth_guard = true;      // rebuild with balanced splits when the tree is deeper than the traversal stack allows
+    // Collapse of the binary tree into 8-wide nodes: SAH-optimal forest per node by dynamic programming (Ylitie et al.
+    // 2017, section 3.1), which also forms the leaves (at most 3 triangles); false = greedy largest-area-first.
+    // MCRT_BVH_COLLAPSE=greedy|optimal, MCRT_BVH_COST=node:prim override (development switches).
+    bool optimal_collapse = true;
+    bool optimal_slots = true;         // child -> slot assignment with the largest total score instead of greedy (MCRT_BVH_SLOTS)
+    float collapse_node_cost = 1.0f;   // cost of fetching + testing one 80-byte node ...
+    float collapse_prim_cost = 0.6f;   // ... relative to one 48-byte triangle
     int max_levels = 19;          // ... i.e. than this many levels (two stack entries per level, 40-entry stack)
 };
 

@@ -12,6 +12,8 @@
 #include <atomic>
 #include <climits>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <future>
 #include <limits>
@@ -52,6 +54,7 @@ struct Node2 {
     Box box;
     int left = -1, right = -1;  // children (internal)
     int first = 0, count = 0;   // primitive range (leaf when count > 0)
+    int pfirst = 0, pcount = 0; // primitive range of the whole subtree (every node)
 };
 
 struct Builder {
@@ -82,6 +85,8 @@ struct Builder {
             cb.grow(&pcent[3 * (size_t)prim[(size_t)i]]);
         }
         n.box = b;
+        n.pfirst = first;
+        n.pcount = count;
         if (count == 1) {
             n.first = first;
             n.count = count;
@@ -93,7 +98,7 @@ struct Builder {
         const int NB = std::max(4, std::min(opt.num_bins, 64));
         const bool forced = depth >= sah_depth_cap;
         if (forced) {
-            if (count <= 3) {
+            if (count <= 3 && !opt.optimal_collapse) {
                 n.first = first;
                 n.count = count;
                 return;
@@ -140,8 +145,9 @@ struct Builder {
                     }
                 }
             }
-            // Leaf decision (leaves hold at most 3 triangles, the wide node's per-child maximum).
-            if (count <= 3) {
+            // Leaf decision (leaves hold at most 3 triangles, the wide node's per-child maximum).  With the optimal
+            // collapse the binary tree goes down to single triangles and the collapse forms the leaves.
+            if (count <= 3 && !opt.optimal_collapse) {
                 float leaf_cost = (float)count * b.half_area();
                 float split_cost = opt.traversal_cost * b.half_area() + best_cost;
                 if (best_axis < 0 || leaf_cost <= split_cost) {
@@ -150,7 +156,7 @@ struct Builder {
                     return;
                 }
             }
-        } else if (count <= 2) {
+        } else if (count <= 2 && !opt.optimal_collapse) {
             n.first = first;
             n.count = count;
             return;
@@ -188,7 +194,7 @@ struct Builder {
             mid = (int)(m - beg);
         }
         if (mid <= 0 || mid >= count) {
-            if (count <= 3) {
+            if (count <= 3 && !opt.optimal_collapse) {
                 n.first = first;
                 n.count = count;
                 return;
@@ -232,12 +238,28 @@ struct WideNode {
     int nchild = 0;
 };
 
+// development switches (see bvh8.h)
+BuildOptions with_env_overrides(BuildOptions o) {
+    if (const char* c = std::getenv("MCRT_BVH_COLLAPSE")) o.optimal_collapse = std::strcmp(c, "greedy") != 0;
+    if (const char* c = std::getenv("MCRT_BVH_SLOTS")) o.optimal_slots = std::strcmp(c, "greedy") != 0;
+    if (const char* c = std::getenv("MCRT_BVH_BINS")) o.num_bins = std::atoi(c);
+    if (const char* c = std::getenv("MCRT_BVH_COST")) {
+        float a = 0.f, b = 0.f;
+        if (std::sscanf(c, "%f:%f", &a, &b) == 2 && a > 0.f && b > 0.f) {
+            o.collapse_node_cost = a;
+            o.collapse_prim_cost = b;
+        }
+    }
+    return o;
+}
+
 }  // namespace
 
 static void build_core(Builder& B, const std::vector<float>& tri, const std::vector<int32_t>& tri_mesh_in, size_t N,
                        const BuildOptions& opt, Bvh8& out);
 
-void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& opt, Bvh8& out) {
+void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& opt_in, Bvh8& out) {
+    const BuildOptions opt = with_env_overrides(opt_in);
     // ---- 1. gather world-space triangles
     int64_t total = 0;
     for (const auto& m : meshes) total += m.numfaces;
@@ -288,7 +310,8 @@ void build_bvh8(const std::vector<BuildInputMesh>& meshes, const BuildOptions& o
 // Top level of the two-level structure: a tree over `n` boxes (lo.xyz, hi.xyz each).  The leaf "triangle" records of
 // the result carry, in the int bits of word 3, the index of the box they stand for, in emission order: the caller
 // lays its instance table out in that order, so a leaf's record index IS the instance index.
-void build_bvh8_boxes(const float* boxes, int n, const BuildOptions& opt, Bvh8& out) {
+void build_bvh8_boxes(const float* boxes, int n, const BuildOptions& opt_in, Bvh8& out) {
+    const BuildOptions opt = with_env_overrides(opt_in);
     if (n <= 0) throw std::runtime_error("Scene is empty.");
     const size_t N = (size_t)n;
     std::vector<float> rec(12 * N, 0.0f);
@@ -348,12 +371,90 @@ static void build_core(Builder& B, const std::vector<float>& tri, const std::vec
     out.triangles.reserve(12 * N);
     std::vector<uint32_t>& W = out.nodes;
 
+    // Optimal collapse (Ylitie, Karras, Laine 2017, section 3.1): cost[n][i] = the smallest SAH cost of representing
+    // binary subtree n by at most i children of one wide node, i = 1..7; a subtree of at most 3 triangles may become
+    // one leaf child, any subtree may become an internal child whose own 8 slots are distributed over its two sides.
+    // Children have larger indices than their parents (alloc_node), so one descending sweep is a post-order.
+    struct Dp {
+        float c[8];      // c[i], i = 1..7
+        uint8_t k[9];    // k[i], i = 2..7: 0 = same forest as i - 1, else slots given to the left side; k[8]: root split
+        uint8_t leaf;    // c[1] is the leaf alternative
+    };
+    std::vector<Dp> dp;
+    const int num_n2 = B.next_node.load();
+    if (opt.optimal_collapse) {
+        dp.resize((size_t)num_n2);
+        const float c_node = opt.collapse_node_cost, c_prim = opt.collapse_prim_cost;
+        for (int ni = num_n2 - 1; ni >= 0; --ni) {
+            const Node2& n = n2[(size_t)ni];
+            Dp& d = dp[(size_t)ni];
+            const float area = n.box.half_area();
+            std::memset(d.k, 0, sizeof(d.k));
+            if (n.count > 0) {
+                for (int i = 1; i < 8; ++i) d.c[i] = area * (float)n.pcount * c_prim;
+                d.leaf = 1;
+                continue;
+            }
+            const Dp& l = dp[(size_t)n.left];
+            const Dp& r = dp[(size_t)n.right];
+            float dist[9];
+            uint8_t dk[9];
+            for (int j = 2; j <= 8; ++j) {
+                dist[j] = std::numeric_limits<float>::infinity();
+                dk[j] = 1;
+                for (int k = std::max(1, j - 7); k <= std::min(7, j - 1); ++k) {
+                    const float c = l.c[k] + r.c[j - k];
+                    if (c < dist[j]) {
+                        dist[j] = c;
+                        dk[j] = (uint8_t)k;
+                    }
+                }
+            }
+            const float c_int = dist[8] + area * c_node;
+            const float c_leaf = n.pcount <= 3 ? area * (float)n.pcount * c_prim : std::numeric_limits<float>::infinity();
+            d.leaf = c_leaf <= c_int;
+            d.c[1] = d.leaf ? c_leaf : c_int;
+            d.k[8] = dk[8];
+            for (int i = 2; i < 8; ++i) {
+                if (dist[i] < d.c[i - 1]) {
+                    d.c[i] = dist[i];
+                    d.k[i] = dk[i];
+                } else {
+                    d.c[i] = d.c[i - 1];
+                    d.k[i] = 0;
+                }
+            }
+        }
+    }
+    std::vector<uint8_t> leaf_child((size_t)num_n2, 0);   // binary node emitted as ONE leaf child (its whole range)
+    for (int ni = 0; ni < num_n2; ++ni) leaf_child[(size_t)ni] = n2[(size_t)ni].count > 0;
+    std::vector<std::pair<int, int>> todo;                // (binary node, slots) during the expansion of one wide node
+
     for (size_t wi = 0; wi < wide_src.size(); ++wi) {
         const int src = wide_src[wi];
         int ch[8];
         int nch = 0;
-        if (n2[(size_t)src].count > 0) {
+        if (n2[(size_t)src].count > 0 || (opt.optimal_collapse && wi == 0 && n2[(size_t)src].pcount <= 3)) {
             ch[nch++] = src;  // degenerate: the whole scene is one leaf
+            leaf_child[(size_t)src] = 1;
+        } else if (opt.optimal_collapse) {
+            todo.clear();
+            const int k8 = dp[(size_t)src].k[8];
+            todo.emplace_back(n2[(size_t)src].right, 8 - k8);
+            todo.emplace_back(n2[(size_t)src].left, k8);
+            while (!todo.empty()) {
+                int m = todo.back().first, j = todo.back().second;
+                todo.pop_back();
+                const Dp& d = dp[(size_t)m];
+                while (j > 1 && d.k[j] == 0) --j;
+                if (j == 1 || n2[(size_t)m].count > 0) {
+                    leaf_child[(size_t)m] = d.leaf;
+                    ch[nch++] = m;
+                } else {
+                    todo.emplace_back(n2[(size_t)m].right, j - d.k[j]);
+                    todo.emplace_back(n2[(size_t)m].left, (int)d.k[j]);
+                }
+            }
         } else {
             ch[nch++] = n2[(size_t)src].left;
             ch[nch++] = n2[(size_t)src].right;
@@ -395,6 +496,38 @@ static void build_core(Builder& B, const std::vector<float>& tri, const std::vec
                 score[i][s] = -proj;  // nearer along the slot's direction = better
             }
         }
+        // the assignment with the largest total score (subset DP over the 8 slots: child i takes a free slot of every
+        // set of i occupied slots); the greedy loop below then only fills in what a NaN score left open
+        if (opt.optimal_slots) {
+            float best[256];
+            int8_t from[256];
+            for (int m = 0; m < 256; ++m) {
+                best[m] = -std::numeric_limits<float>::infinity();
+                from[m] = -1;
+            }
+            best[0] = 0.f;
+            for (int m = 0; m < 256; ++m) {
+                const int i = __builtin_popcount((unsigned)m);
+                if (i >= nch || !(best[m] > -std::numeric_limits<float>::infinity())) continue;
+                for (int sl = 0; sl < 8; ++sl) {
+                    if (m & (1 << sl)) continue;
+                    const float v = best[m] + score[i][sl];
+                    if (v > best[m | (1 << sl)]) {
+                        best[m | (1 << sl)] = v;
+                        from[m | (1 << sl)] = (int8_t)sl;
+                    }
+                }
+            }
+            int bm = -1;
+            for (int m = 0; m < 256; ++m)
+                if (__builtin_popcount((unsigned)m) == nch && from[m] >= 0 && (bm < 0 || best[m] > best[bm])) bm = m;
+            for (int i = nch - 1; i >= 0 && bm > 0; --i) {
+                const int sl = from[bm];
+                slot_of[i] = sl;
+                child_in_slot[sl] = i;
+                bm &= ~(1 << sl);
+            }
+        }
         for (int k = 0; k < nch; ++k) {
             int bi = -1, bs = -1;
             float bv = -std::numeric_limits<float>::infinity();
@@ -412,6 +545,7 @@ static void build_core(Builder& B, const std::vector<float>& tri, const std::vec
             if (bi < 0) {      // NaN scores (non-finite boxes): first free child into the first free slot
                 for (int i = 0; i < nch && bi < 0; ++i)
                     if (slot_of[i] < 0) bi = i;
+                if (bi < 0) break;   // every child has its slot
                 for (int s = 0; s < 8 && bs < 0; ++s)
                     if (child_in_slot[s] < 0) bs = s;
             }
@@ -458,20 +592,20 @@ static void build_core(Builder& B, const std::vector<float>& tri, const std::vec
                 q[a][s] = (uint8_t)qlo;
                 q[3 + a][s] = (uint8_t)qhi;
             }
-            if (c.count == 0) {
+            if (!leaf_child[(size_t)ch[i]]) {
                 imask |= (uint8_t)(1u << s);
                 meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
                 wide_src.push_back(ch[i]);
                 wide_depth.push_back(wide_depth[wi] + 1);
             } else {
                 static const uint8_t unary[4] = {0, 1, 3, 7};
-                meta[s] = (uint8_t)((unary[c.count] << 5) | (uint32_t)tri_off);
-                for (int k = 0; k < c.count; ++k) {
-                    const float* src_tri = &tri[12 * (size_t)B.prim[(size_t)(c.first + k)]];
+                meta[s] = (uint8_t)((unary[c.pcount] << 5) | (uint32_t)tri_off);
+                for (int k = 0; k < c.pcount; ++k) {
+                    const float* src_tri = &tri[12 * (size_t)B.prim[(size_t)(c.pfirst + k)]];
                     out.triangles.insert(out.triangles.end(), src_tri, src_tri + 12);
-                    out.tri_mesh.push_back(tri_mesh_in[(size_t)B.prim[(size_t)(c.first + k)]]);
+                    out.tri_mesh.push_back(tri_mesh_in[(size_t)B.prim[(size_t)(c.pfirst + k)]]);
                 }
-                tri_off += c.count;
+                tri_off += c.pcount;
             }
         }
         std::memcpy(&words[0], &nb.lo[0], 4);

@@ -136,6 +136,46 @@ def test_emulated_walk_matches_bruteforce_on_soup_and_is_ordered():
     assert visited < 0.25 * nodes.shape[0], visited
 
 
+def _wide_sah(nodes, tris):
+    """SAH cost of the wide tree (node visit 1, triangle test 0.6, areas relative to the root's)."""
+    bounds = bvh8_emul.subtree_bounds(nodes, tris)
+
+    def area(lo, hi):
+        d = np.maximum(hi - lo, 0.0)
+        return d[0] * d[1] + d[1] * d[2] + d[2] * d[0]
+
+    root = area(*bounds[0])
+    cost = 1.0
+    for ni, s, leaf, lo, hi, ref in bvh8_emul.walk_tree(nodes, tris):
+        cost += area(lo, hi) / root * (0.6 * len(ref) if leaf else 1.0)
+    return cost
+
+
+def test_optimal_collapse_and_greedy_collapse_find_the_same_hits_and_optimal_is_cheaper(monkeypatch):
+    """The default collapse of the binary tree into 8-wide nodes is the SAH-optimal forest per node (dynamic
+    programming, bvh8_build.cpp), which also forms the leaves; MCRT_BVH_COLLAPSE / MCRT_BVH_SLOTS = greedy select
+    r01's largest-area-first collapse and greedy slot assignment.  Tree shape is not a parity requirement, the hits
+    are: both trees answer the brute force's hits, and the optimal one is smaller and cheaper by its own measure."""
+    v, idx = soup(6000, 9)
+    rays = random_rays(150, np.zeros(3), np.full(3, 10.0), 13)
+    want = port.intersect(port.mesh_triangles([(v, idx, 0, None)]), rays)
+    stats = {}
+    for mode in ("optimal", "greedy"):
+        monkeypatch.setenv("MCRT_BVH_COLLAPSE", mode)
+        monkeypatch.setenv("MCRT_BVH_SLOTS", mode)
+        nodes, tris = rr.host_bvh(v, idx)
+        assert np.array_equal(np.sort(tris[:, 7].view(np.int32)), np.arange(idx.shape[0]))
+        got, visited = _emulate(nodes, tris, rays)
+        assert np.array_equal(got["primid"], want["primid"]), mode
+        hit = want["shapeid"] >= 0
+        assert np.array_equal(got["uvwt"][hit, 3].view(np.uint32), want["uvwt"][hit, 3].view(np.uint32)), mode
+        stats[mode] = (nodes.shape[0], _wide_sah(nodes, tris), visited)
+    print(stats)
+    assert stats["optimal"][0] < stats["greedy"][0]
+    assert stats["optimal"][1] < stats["greedy"][1]
+    assert stats["optimal"][2] <= stats["greedy"][2] * 1.05
+
+
 def test_cpp_adaptor_compiles_against_reference_header_and_fails_loudly_without_gpu():
     """include/radeon_rays_b200.hpp (the IntersectionApi adaptor a maintainer adds to the engine) against
     the reference's own radeon_rays.h; without a CUDA device Create() must throw, not fall back."""
