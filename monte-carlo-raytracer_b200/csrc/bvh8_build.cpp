@@ -19,6 +19,7 @@
 #include <limits>
 #include <stdexcept>
 #include <thread>
+#include <chrono>
 
 namespace mcrt {
 namespace {
@@ -353,8 +354,10 @@ static void build_core(Builder& B, const std::vector<float>& tri, const std::vec
     // ---- 2. binary build
     B.nodes.assign(2 * N, Node2());
     B.max_threads = opt.num_threads > 0 ? opt.num_threads : (int)std::max(1u, std::thread::hardware_concurrency());
+    auto T0 = std::chrono::steady_clock::now();
     int root = B.alloc_node();
     B.build_range(root, 0, (int)N, 0);
+    auto T1 = std::chrono::steady_clock::now();
     const std::vector<Node2>& n2 = B.nodes;
 
     // ---- 3/4. collapse to 8-wide, breadth-first, emitting nodes and triangles
@@ -426,6 +429,8 @@ static void build_core(Builder& B, const std::vector<float>& tri, const std::vec
             }
         }
     }
+    auto T2 = std::chrono::steady_clock::now();
+    if (std::getenv("MCRT_BUILD_TRACE")) fprintf(stderr, "binary %.3f s, dp %.3f s\n", std::chrono::duration<double>(T1 - T0).count(), std::chrono::duration<double>(T2 - T1).count());
     std::vector<uint8_t> leaf_child((size_t)num_n2, 0);   // binary node emitted as ONE leaf child (its whole range)
     for (int ni = 0; ni < num_n2; ++ni) leaf_child[(size_t)ni] = n2[(size_t)ni].count > 0;
     std::vector<std::pair<int, int>> todo;                // (binary node, slots) during the expansion of one wide node
@@ -499,30 +504,36 @@ static void build_core(Builder& B, const std::vector<float>& tri, const std::vec
         // the assignment with the largest total score (subset DP over the 8 slots: child i takes a free slot of every
         // set of i occupied slots); the greedy loop below then only fills in what a NaN score left open
         if (opt.optimal_slots) {
+            // pull form, branch-free: best[M] for a set M of i + 1 occupied slots = max over its members sl of
+            // best[M without sl] + score[i][sl] (child i is the last one placed); sets are visited in increasing order,
+            // and M without sl < M
             float best[256];
             int8_t from[256];
-            for (int m = 0; m < 256; ++m) {
-                best[m] = -std::numeric_limits<float>::infinity();
-                from[m] = -1;
-            }
+            const float ninf = -std::numeric_limits<float>::infinity();
             best[0] = 0.f;
-            for (int m = 0; m < 256; ++m) {
-                const int i = __builtin_popcount((unsigned)m);
-                if (i >= nch || !(best[m] > -std::numeric_limits<float>::infinity())) continue;
-                for (int sl = 0; sl < 8; ++sl) {
-                    if (m & (1 << sl)) continue;
-                    const float v = best[m] + score[i][sl];
-                    if (v > best[m | (1 << sl)]) {
-                        best[m | (1 << sl)] = v;
-                        from[m | (1 << sl)] = (int8_t)sl;
+            from[0] = -1;
+            for (int m = 1; m < 256; ++m) {
+                const int i = __builtin_popcount((unsigned)m) - 1;
+                float bv = ninf;
+                int bsl = -1;
+                if (i < nch) {
+                    for (int sl = 0; sl < 8; ++sl) {
+                        const bool member = (m >> sl) & 1;
+                        const float v = member ? best[m & ~(1 << sl)] + score[i][sl] : ninf;
+                        const bool better = v > bv;
+                        bv = better ? v : bv;
+                        bsl = better ? sl : bsl;
                     }
                 }
+                best[m] = bv;
+                from[m] = (int8_t)bsl;
             }
             int bm = -1;
             for (int m = 0; m < 256; ++m)
                 if (__builtin_popcount((unsigned)m) == nch && from[m] >= 0 && (bm < 0 || best[m] > best[bm])) bm = m;
             for (int i = nch - 1; i >= 0 && bm > 0; --i) {
                 const int sl = from[bm];
+                if (sl < 0) break;
                 slot_of[i] = sl;
                 child_in_slot[sl] = i;
                 bm &= ~(1 << sl);
@@ -624,6 +635,7 @@ static void build_core(Builder& B, const std::vector<float>& tri, const std::vec
         std::memcpy(&words[18], q[5], 8);   // qhi_z
         W.insert(W.end(), words, words + 20);
     }
+    if (std::getenv("MCRT_BUILD_TRACE")) fprintf(stderr, "emit %.3f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - T2).count());
     out.num_nodes = (int64_t)wide_src.size();
     out.num_tris = (int64_t)(out.triangles.size() / 12);
     out.level_offsets.clear();      // breadth-first emission: depths are non-decreasing
