@@ -135,7 +135,7 @@ int main(int argc, char** argv) {
         uint32_t ng0 = 0, ng1 = 0x80000000u;
         for (;;) {
             uint32_t tg0 = 0, tg1 = 0;
-            if (gcull && (taken || argv[4][9] != '2') && ng1 > 0x00FFFFFFu && gmin > closest) ng1 &= 0x00FFFFFFu;
+            if (gcull && (taken || argv[4][9] == 0) && ng1 > 0x00FFFFFFu && gmin > closest) ng1 &= 0x00FFFFFFu;
             if (ng1 > 0x00FFFFFFu) {
                 const uint32_t hits = ng1;
                 const int bit = 31 - __builtin_clz(hits);
@@ -182,6 +182,19 @@ int main(int argc, char** argv) {
                 ng0 = node[4];
                 gmin = newmin;
                 taken = false;
+                if (argc > 4 && !std::strcmp(argv[4], "groupcull3")) {
+                    // the cheapest conservative form: only the child in the ray's own octant slot (bit 31, visited first
+                    // whenever it is hit) is left out, and the float is truncated to its upper 16 bits (it would travel
+                    // in the 16 spare bits of the stack entry's second word)
+                    const uint32_t inner_hits = hitmask >> 24;
+                    gmin = 3e38f;
+                    for (int b2 = 0; b2 < 7; ++b2)
+                        if ((inner_hits >> b2) & 1u) gmin = std::fmin(gmin, nt[b2]);
+                    uint32_t gb;
+                    std::memcpy(&gb, &gmin, 4);
+                    gb &= 0xFFFF0000u;
+                    std::memcpy(&gmin, &gb, 4);
+                }
                 if (argc > 4 && !std::strcmp(argv[4], "groupcull2")) {
                     const uint32_t inner_hits = hitmask >> 24;
                     gmin = 3e38f;
