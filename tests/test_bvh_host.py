@@ -83,6 +83,25 @@ def test_degenerate_inputs():
         rr.host_bvh(v, np.zeros((0, 3), np.int32))
 
 
+@pytest.mark.parametrize("mode", ["optimal", "greedy"])
+def test_small_triangle_counts_every_triangle_in_exactly_one_leaf(mode, monkeypatch):
+    """1 .. 29 triangles and a few counts around the 8 x 8 boundaries: the collapse (either kind) must hand every
+    triangle to exactly one leaf, with boxes that enclose it -- the scene-is-one-leaf root, the 2- and 3-triangle
+    leaves and the partly filled nodes are all in this range."""
+    monkeypatch.setenv("MCRT_BVH_COLLAPSE", mode)
+    monkeypatch.setenv("MCRT_BVH_SLOTS", mode)
+    for n in list(range(1, 30)) + [63, 64, 65, 100, 257]:
+        v, idx = soup(n, n)
+        nodes, tris = rr.host_bvh(v, idx)
+        seen = []
+        for ni, s, leaf, lo, hi, ref in bvh8_emul.walk_tree(nodes, tris):
+            if leaf:
+                seen += ref
+        assert sorted(seen) == list(range(n)), n
+        assert np.array_equal(np.sort(tris[:, 7].view(np.int32)), np.arange(n)), n
+        bvh8_emul.subtree_bounds(nodes, tris)
+
+
 def _emulate(nodes, tris, rays):
     rec = np.zeros(tris.shape[0], dtype=port.TRI)
     rec_view = rec.view(np.float32).reshape(-1, 12)
