@@ -546,6 +546,31 @@ def write_pfm(path, image, width, height):
         f.write(np.ascontiguousarray(rgb, "<f4").tobytes())
 
 
+def write_png(path, image, width, height):
+    """Engine::takeScreenshot (source/engine/Engine.cpp:180-204) without the GL framebuffer: the float4[P] image the
+    display pass would draw (normally "TonemappedImageCL"), converted as an RGBA8 framebuffer converts it -- clamp to
+    [0, 1], x 255, round to nearest; NaN -> 0 -- and saved as an 8-bit RGBA PNG, rows top to bottom as write_pfm
+    orders them.  Alpha is written opaque (the reference reads back the window's alpha, which the GUI leaves at 1).
+    Encoder: zlib + the three mandatory chunks, no image library needed."""
+    import struct
+    import zlib
+    img = np.asarray(image, np.float32).reshape(height, width, -1)
+    rgba = np.empty((height, width, 4), np.uint8)
+    rgb = np.nan_to_num(img[:, :, :3], nan=0.0, posinf=1.0, neginf=0.0)
+    rgba[:, :, :3] = np.rint(np.clip(rgb, 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+    rgba[:, :, 3] = 255
+    raw = np.concatenate([np.zeros((height, 1), np.uint8), rgba.reshape(height, width * 4)], axis=1).tobytes()
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n")
+        f.write(chunk(b"IHDR", struct.pack(">IIBBBBB", width, height, 8, 6, 0, 0, 0)))
+        f.write(chunk(b"IDAT", zlib.compress(raw, 6)))
+        f.write(chunk(b"IEND", b""))
+
+
 def make_pt_pipeline(api, scene, width, height, max_depth, fused=True, use_taa=True, refit=False, acc_type="fatbvh"):
     """PathTracingApp::startPathTracing's PT pipeline (:248-255) without denoise / tonemap / display."""
     rts = RTScene(api, scene, refit=refit, acc_type=acc_type)
